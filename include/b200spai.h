@@ -1,0 +1,160 @@
+/*
+ * b200spai.h -- C ABI of libb200spai.so: the B200 (sm_100a) implementation of the learned-SPAI
+ * solve path of Adversarr/LearningSparsePreconditioner4GPU.
+ *
+ * The reference has no FFI of its own: its hot path is Python that calls torch / torch_geometric /
+ * scipy and, for the timed solve, the external pymathprim extension.  Each entry point below cites
+ * the reference interface it stands in for (paths relative to the reference root).  INTEGRATION.md
+ * shows the ctypes binding a maintainer adds on the reference side.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative b200spai_status otherwise; the message for the
+ *     calling thread is available from b200spai_last_error().  No C++ exception crosses the boundary.
+ *   - "_dev" pointers are CUDA device pointers on the current device, "_host" pointers are host
+ *     memory (pinned memory makes the copies asynchronous).  Callers own every buffer they pass; a
+ *     handle owns only its internal workspaces and device copies, released by the matching _destroy.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  All work is
+ *     enqueued on it; functions that return scalars to the host synchronise that stream once.
+ *   - one handle = one device; handles are not thread-safe, distinct handles are independent.
+ *   - indices are int32 inside CSR structures (nnz < 2^31), int64 in edge lists (edge_index layout
+ *     of the reference: row 0 = row index, row 1 = column index, neural_cg/data.py:442-450).
+ */
+#ifndef B200SPAI_H_
+#define B200SPAI_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  B200SPAI_OK = 0,
+  B200SPAI_ERR_CUDA = -1,      /* a CUDA runtime call failed */
+  B200SPAI_ERR_ARG = -2,       /* invalid argument */
+  B200SPAI_ERR_UNSORTED = -3,  /* edge list not row-major / column-ascending / duplicate-free */
+  B200SPAI_ERR_NO_DEVICE = -4, /* no sm_100-class CUDA device */
+  B200SPAI_ERR_BREAKDOWN = -5  /* PCG breakdown (p.q <= 0 or NaN) -- reported in the result, not fatal */
+} b200spai_status;
+
+typedef struct b200spai_csr_s* b200spai_csr_t;     /* fp64 CSR matrix resident in HBM */
+typedef struct b200spai_pcg_s* b200spai_pcg_t;     /* PCG solver bound to A (and optionally G) */
+typedef struct b200spai_graph_s* b200spai_graph_t; /* GNN topology: target-sorted edge list */
+typedef struct b200spai_gnn_s* b200spai_gnn_t;     /* GNN weights + activations workspace */
+
+const char* b200spai_last_error(void);
+int b200spai_version(void);
+/* Device query: name (<= 127 chars), SM count, compute capability major*10+minor. */
+int b200spai_device_info(char* name128, int* sm_count, int* cc);
+
+/* ------------------------------------------------------------------------------------------------
+ * CSR matrices.  Stand in for the scipy.sparse.csr_matrix objects the reference hands to its solver
+ * (neural_cg/utils/validate.py:116-117: pcg(A, ...), ext_spai=(spai, epsilon)).
+ * ---------------------------------------------------------------------------------------------- */
+/* Copy a CSR matrix (indptr[n_rows+1], indices[nnz] sorted within rows, data[nnz]) into HBM. */
+int b200spai_csr_create_host(int32_t n_rows, int32_t n_cols, int64_t nnz, const int32_t* indptr_host,
+                             const int32_t* indices_host, const double* data_host, void* stream,
+                             b200spai_csr_t* out);
+int b200spai_csr_create_dev(int32_t n_rows, int32_t n_cols, int64_t nnz, const int32_t* indptr_dev,
+                            const int32_t* indices_dev, const double* data_dev, void* stream,
+                            b200spai_csr_t* out);
+/* B = A^T as a new CSR matrix with ascending column order inside rows (deterministic; replaces
+ * csr_matrix(spai.T), validate.py:176). */
+int b200spai_csr_transpose(b200spai_csr_t a, void* stream, b200spai_csr_t* out);
+int b200spai_csr_shape(b200spai_csr_t a, int32_t* n_rows, int32_t* n_cols, int64_t* nnz);
+/* Copy back (any pointer may be NULL to skip it). */
+int b200spai_csr_download(b200spai_csr_t a, int32_t* indptr_host, int32_t* indices_host, double* data_host,
+                          void* stream);
+/* Raw device views (valid until destroy). */
+int b200spai_csr_device_ptrs(b200spai_csr_t a, const int32_t** indptr_dev, const int32_t** indices_dev,
+                             const double** data_dev);
+int b200spai_csr_destroy(b200spai_csr_t a);
+/* y = A x (scipy csr @ vector; the csr_matvec under validate.py:182,197).  kernel: 0 = auto,
+ * 1 = sub-warp-per-row kernel, 2 = TMA-staged streaming kernel. */
+int b200spai_spmv(b200spai_csr_t a, const double* x_dev, double* y_dev, int kernel, void* stream);
+/* diag[i] = A[i,i] (0 where absent)  (A.diagonal(), validate.py:286). */
+int b200spai_csr_diagonal(b200spai_csr_t a, double* diag_dev, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Edge list -> masked CSR on the device.  Replaces to_csr_cpu (neural_cg/utils/validate.py:22-51)
+ * = make_bsr_from_coo_inds (neural_cg/data.py:134-156) + apply_dbc_masking (data.py:159-170):
+ * blocks expanded to scalars, rows/cols of masked DOFs zeroed, unit diagonal added there, entries
+ * that are exactly zero afterwards dropped (only when a mask is given), indices sorted.
+ * values are fp32 [E,b,b] row-major (the GNN output or Data.matrix_values) and are widened to fp64.
+ * mask is fp32 [N*b] or NULL.  edge_index must be row-major / column-ascending / duplicate-free
+ * (what the reference's datasets produce); otherwise B200SPAI_ERR_UNSORTED.
+ * ---------------------------------------------------------------------------------------------- */
+int b200spai_edges_to_csr(int64_t num_nodes, int64_t num_edges, int32_t block_size, const int64_t* edge_index_dev,
+                          const float* values_dev, const float* mask_dev, void* stream, b200spai_csr_t* out);
+
+/* ------------------------------------------------------------------------------------------------
+ * PCG.  Replaces pymathprim.linalg.PreconditionedConjugateGradient as the reference calls it
+ * (validate.py:73-80,110-117,145-156) with the semantics of the in-tree scipy definition
+ * (validate.py:163-201 + scipy.sparse.linalg.cg): x0 = 0, stop when ||r||_2 < rtol*||b||_2 tested
+ * before each iteration on the recurrence residual, iterations = completed updates, fp64.
+ * ---------------------------------------------------------------------------------------------- */
+typedef enum {
+  B200SPAI_PRECOND_NONE = 0,            /* "none"            z = r                                   */
+  B200SPAI_PRECOND_DIAGONAL = 1,        /* "diagonal"        z = r / diag(A)          (:235-264)     */
+  B200SPAI_PRECOND_EXT_SPAI = 2,        /* "ext_spai"        z = G (G^T r) + eps r    (:173-182)     */
+  B200SPAI_PRECOND_EXT_SPAI_SCALED = 3  /* "ext_spai_scaled" z = G((G^T r)/d) + eps r/d (:276-287)   */
+} b200spai_precond;
+
+typedef struct {
+  int32_t iterations;     /* completed CG updates (the reference's callback count) */
+  int32_t converged;      /* 1 if ||r|| < rtol*||b|| was reached */
+  int32_t breakdown;      /* 1 if p.q <= 0 or a NaN appeared (M or A not SPD) */
+  int32_t reserved;
+  double b_norm;          /* ||b||_2 */
+  double final_residual;  /* ||r||_2 of the recurrence residual at exit */
+  float solve_ms;         /* device time of the solve (CUDA events on `stream`) */
+  float setup_ms;         /* device time of the last preconditioner setup (upload/transpose of G) */
+} b200spai_pcg_result;
+
+/* Binds a solver to A (not copied; must outlive the solver). */
+int b200spai_pcg_create(b200spai_csr_t a, b200spai_pcg_t* out);
+/* Attach G (the `ext_spai=(spai, epsilon)` argument, validate.py:117).  G^T is built on the device.
+ * The solver keeps references to g (must outlive it) and owns G^T. */
+int b200spai_pcg_set_spai(b200spai_pcg_t s, b200spai_csr_t g, double epsilon, void* stream);
+/* mode: 0 = auto, 1 = stream-enqueued kernels with a device-side done flag polled every few
+ * iterations, 2 = one CUDA graph with a device-driven WHILE node (no host involvement at all). */
+int b200spai_pcg_set_mode(b200spai_pcg_t s, int mode);
+/* Solve A x = b.  x_dev is overwritten (x0 = 0).  resid_hist_dev: NULL or max_iter+1 doubles
+ * receiving ||r_k|| (k = 0..iterations).  max_iter <= 0 means n (validate.py:100-101). */
+int b200spai_pcg_solve_dev(b200spai_pcg_t s, int precond, const double* b_dev, double* x_dev, double rtol,
+                           int32_t max_iter, double* resid_hist_dev, void* stream, b200spai_pcg_result* result);
+/* Same with host vectors: copies b in, x (and the history, if not NULL) out inside the call. */
+int b200spai_pcg_solve_host(b200spai_pcg_t s, int precond, const double* b_host, double* x_host, double rtol,
+                            int32_t max_iter, double* resid_hist_host, void* stream, b200spai_pcg_result* result);
+/* z = M r for the attached preconditioner (test hook for the operator of validate.py:182). */
+int b200spai_pcg_apply_precond(b200spai_pcg_t s, int precond, const double* r_dev, double* z_dev, void* stream);
+/* Kernel-launch counter since creation (for bench.py's gpu_launches). */
+int b200spai_pcg_launch_count(b200spai_pcg_t s, int64_t* launches);
+int b200spai_pcg_destroy(b200spai_pcg_t s);
+
+/* ------------------------------------------------------------------------------------------------
+ * GNN.  Replaces NodeEdgeProcessing.forward (neural_cg/nn/gnns.py:77-97) with MPLayer
+ * (neural_cg/nn/basic_layers.py:145-225) and FeedForward (:73-109) at the default architecture of
+ * config/gnn.yaml: 16 features, 2-layer MLPs (3 Linear), GELU(erf), LayerNorm pre-norm on the three
+ * MP MLPs, 4 residual MP layers, sum aggregation at edge_index[1].
+ * ---------------------------------------------------------------------------------------------- */
+/* One-off per topology: stable sort of the edges by target node (edge_index[1]) and segment offsets. */
+int b200spai_graph_create(int64_t num_nodes, int64_t num_edges, const int64_t* edge_index_dev, void* stream,
+                          b200spai_graph_t* out);
+int b200spai_graph_destroy(b200spai_graph_t g);
+/* Weights as one fp32 blob in the canonical order documented in DESIGN.md ("GNN weight blob");
+ * python side: neural_cg.nn.gnns.pack_state_dict.  node_in/edge_in = input feature counts,
+ * block_size b -> b*b decoder outputs, num_layers = MP layers. */
+int b200spai_gnn_create(int32_t node_in, int32_t edge_in, int32_t block_size, int32_t num_layers,
+                        const float* blob_host, int64_t blob_len, b200spai_gnn_t* out);
+int b200spai_gnn_destroy(b200spai_gnn_t m);
+/* G_out[E,b,b] (caller's edge order) = workspace.forward(x, edge_index, edge_attr) (workspace.py:92-94).
+ * node_out_dev: NULL or [N,16] final node features. */
+int b200spai_gnn_forward(b200spai_gnn_t m, b200spai_graph_t g, const float* x_dev, const float* edge_attr_dev,
+                         float* g_out_dev, float* node_out_dev, void* stream);
+int b200spai_gnn_launch_count(b200spai_gnn_t m, int64_t* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SPAI_H_ */

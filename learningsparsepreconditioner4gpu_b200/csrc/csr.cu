@@ -1,0 +1,388 @@
+// CSR container, row-block partition, transpose and SpMV dispatch.
+#include <cub/cub.cuh>
+
+#include <cstdlib>
+#include <mutex>
+
+#include "csr.h"
+
+namespace b200spai {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string& msg) { g_last_error = msg; }
+const std::string& last_error() { return g_last_error; }
+
+int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+static constexpr int PAD = 16;  // elements of slack behind every CSR array (bulk-copy over-read)
+
+int csr_alloc(int n_rows, int n_cols, long long nnz, b200spai_csr_s** out) {
+  B2_ARG(n_rows >= 0 && n_cols >= 0 && nnz >= 0, "csr_alloc: negative size");
+  B2_ARG(nnz < 2147483647LL - 64, "csr_alloc: nnz must fit int32");
+  auto* a = new b200spai_csr_s();
+  a->n_rows = n_rows;
+  a->n_cols = n_cols;
+  a->nnz = nnz;
+  int rc = dev_alloc(&a->rowptr, (size_t)n_rows + 1 + PAD);
+  if (!rc) rc = dev_alloc(&a->col, (size_t)nnz + PAD);
+  if (!rc) rc = dev_alloc(&a->val, (size_t)nnz + PAD);
+  if (rc) {
+    csr_free(a);
+    return rc;
+  }
+  // define the padding (never used arithmetically, but keeps compute-sanitizer initcheck quiet)
+  cudaMemset(a->rowptr + n_rows + 1, 0, PAD * sizeof(int));
+  cudaMemset(a->col + nnz, 0, PAD * sizeof(int));
+  cudaMemset(a->val + nnz, 0, PAD * sizeof(double));
+  *out = a;
+  return 0;
+}
+
+void csr_free(b200spai_csr_s* a) {
+  if (!a) return;
+  cudaFree(a->rowptr);
+  cudaFree(a->col);
+  cudaFree(a->val);
+  cudaFree(a->blk[0]);
+  cudaFree(a->blk[1]);
+  delete a;
+}
+
+// ---- row-block partition -----------------------------------------------------------------------
+// Block k starts at the first row r with key(r) = rowptr[r] + weight*r >= k*target, so a block holds
+// < target entries (not counting its last row) and <= target/weight rows.
+__global__ void partition_bounds_kernel(const int* __restrict__ rowptr, int n_rows, long long target, int weight,
+                                        int nblk, int* __restrict__ bounds) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > nblk) return;
+  const long long want = (long long)k * target;
+  int lo = 0, hi = n_rows;
+  while (lo < hi) {
+    int mid = lo + ((hi - lo) >> 1);
+    long long key = (long long)__ldg(rowptr + mid) + (long long)weight * mid;
+    if (key >= want) hi = mid; else lo = mid + 1;
+  }
+  bounds[k] = (k == nblk) ? n_rows : lo;
+}
+
+__global__ void partition_pack_kernel(const int* __restrict__ rowptr, const int* __restrict__ bounds, int nblk,
+                                      int4* __restrict__ blk) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= nblk) return;
+  int r0 = bounds[k], r1 = bounds[k + 1];
+  blk[k] = make_int4(r0, __ldg(rowptr + r0), r1, __ldg(rowptr + r1));
+}
+
+int build_row_blocks(const int* rowptr, int n_rows, long long nnz, long long target, int weight, int4** blk_out,
+                     int* nblk_out, cudaStream_t stream) {
+  const long long total = nnz + (long long)weight * n_rows;
+  const int nblk = (int)((total + target - 1) / target);
+  *nblk_out = nblk;
+  if (nblk == 0) return dev_alloc(blk_out, 1);
+  int* bounds = nullptr;
+  B2_TRY(dev_alloc(&bounds, (size_t)nblk + 1));
+  B2_TRY(dev_alloc(blk_out, (size_t)nblk));
+  partition_bounds_kernel<<<(nblk + 1 + 255) / 256, 256, 0, stream>>>(rowptr, n_rows, target, weight, nblk, bounds);
+  partition_pack_kernel<<<(nblk + 255) / 256, 256, 0, stream>>>(rowptr, bounds, nblk, *blk_out);
+  B2_LAUNCH_CHECK();
+  B2_CUDA(cudaStreamSynchronize(stream));
+  cudaFree(bounds);
+  return 0;
+}
+
+static long long partition_target(int which) { return which == 0 ? StreamCfg<2048>::TARGET : StreamCfg<1024>::TARGET; }
+
+int csr_ensure_partition(b200spai_csr_s* A, int which, cudaStream_t stream) {
+  if (A->blk[which]) return 0;
+  return build_row_blocks(A->rowptr, A->n_rows, A->nnz, partition_target(which), 2, &A->blk[which], &A->nblk[which], stream);
+}
+
+// ---- SpMV dispatch -------------------------------------------------------------------------------
+static int stream_cfg_from_env() {
+  static int cfg = -1;
+  if (cfg < 0) {
+    const char* e = getenv("B200SPAI_STREAM_CFG");
+    cfg = e ? atoi(e) : 0;
+    if (cfg < 0 || cfg > 3) cfg = 0;
+  }
+  return cfg;
+}
+
+int spmv_auto_kernel(const b200spai_csr_s* A) {
+  static int forced = -1;
+  if (forced < 0) {
+    const char* e = getenv("B200SPAI_SPMV_KERNEL");
+    forced = e ? atoi(e) : 0;
+  }
+  if (forced == 1 || forced == 2) return forced;
+  // the streaming kernel needs enough row blocks to occupy the chip; tiny systems take the vector kernel
+  return (A->nnz >= (1LL << 18)) ? 2 : 1;
+}
+
+template <int VEC, int MODE>
+static int launch_vector(b200spai_csr_s* A, const SpmvArgs& args, cudaStream_t stream) {
+  constexpr int RPW = 32 / VEC;
+  const long long warps_needed = ((long long)A->n_rows + 2 * RPW - 1) / (2 * RPW);
+  long long ctas = (warps_needed + 7) / 8;
+  const long long cap = (long long)sm_count() * 8;
+  if (ctas > cap) ctas = cap;
+  if (ctas < 1) ctas = 1;
+  spmv_vector_kernel<VEC, MODE><<<(int)ctas, 256, 0, stream>>>(A->view(), args);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int MODE>
+static int launch_vector_mode(b200spai_csr_s* A, const SpmvArgs& args, cudaStream_t stream) {
+  const double m = A->n_rows ? (double)A->nnz / A->n_rows : 1.0;
+  if (m <= 2.5) return launch_vector<2, MODE>(A, args, stream);
+  if (m <= 5.0) return launch_vector<4, MODE>(A, args, stream);
+  if (m <= 10.0) return launch_vector<8, MODE>(A, args, stream);
+  if (m <= 24.0) return launch_vector<16, MODE>(A, args, stream);
+  return launch_vector<32, MODE>(A, args, stream);
+}
+
+template <int CAP, int STAGES, int MODE>
+static int launch_stream(b200spai_csr_s* A, const SpmvArgs& args, cudaStream_t stream) {
+  constexpr int which = (CAP == 2048) ? 0 : 1;
+  B2_TRY(csr_ensure_partition(A, which, stream));
+  const int smem = StreamCfg<CAP>::smem_bytes(STAGES);
+  auto kern = spmv_stream_kernel<CAP, STAGES, MODE>;
+  static int ctas_per_sm = 0;  // per instantiation
+  if (ctas_per_sm == 0) {
+    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int occ = 0;
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 256, smem));
+    ctas_per_sm = occ > 0 ? occ : 1;
+  }
+  int grid = sm_count() * ctas_per_sm;
+  if (grid > A->nblk[which]) grid = A->nblk[which];
+  if (grid < 1) grid = 1;
+  kern<<<grid, 256, smem, stream>>>(A->view(), A->blk[which], A->nblk[which], args);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int MODE>
+static int launch_stream_mode(b200spai_csr_s* A, const SpmvArgs& args, cudaStream_t stream) {
+  switch (stream_cfg_from_env()) {
+    case 1: return launch_stream<2048, 2, MODE>(A, args, stream);
+    case 2: return launch_stream<1024, 4, MODE>(A, args, stream);
+    case 3: return launch_stream<1024, 2, MODE>(A, args, stream);
+    default: return launch_stream<2048, 3, MODE>(A, args, stream);
+  }
+}
+
+template <int MODE>
+static int spmv_launch_mode(b200spai_csr_s* A, const SpmvArgs& args, int kernel, cudaStream_t stream) {
+  if (kernel == 0) kernel = spmv_auto_kernel(A);
+  if (kernel == 2) return launch_stream_mode<MODE>(A, args, stream);
+  return launch_vector_mode<MODE>(A, args, stream);
+}
+
+int spmv_launch(b200spai_csr_s* A, const SpmvArgs& args, int mode, int kernel, cudaStream_t stream) {
+  switch (mode) {
+    case SPMV_PLAIN: return spmv_launch_mode<SPMV_PLAIN>(A, args, kernel, stream);
+    case SPMV_SCALE: return spmv_launch_mode<SPMV_SCALE>(A, args, kernel, stream);
+    case SPMV_AXPY_DOT: return spmv_launch_mode<SPMV_AXPY_DOT>(A, args, kernel, stream);
+    case SPMV_DOT: return spmv_launch_mode<SPMV_DOT>(A, args, kernel, stream);
+  }
+  set_error("spmv_launch: bad mode");
+  return B200SPAI_ERR_ARG;
+}
+
+// ---- transpose ------------------------------------------------------------------------------------
+__global__ void expand_rows_kernel(const int* __restrict__ rowptr, int n_rows, int* __restrict__ rowidx) {
+  // one warp per row
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= n_rows) return;
+  const int s = rowptr[w], e = rowptr[w + 1];
+  for (int k = s + lane; k < e; k += 32) rowidx[k] = (int)w;
+}
+
+__global__ void iota_kernel(int* p, long long n) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = (int)i;
+}
+
+__global__ void count_cols_kernel(const int* __restrict__ col, long long nnz, int* __restrict__ cnt) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nnz) atomicAdd(cnt + col[i] + 1, 1);  // integer counts: order-independent
+}
+
+__global__ void gather_transposed_kernel(const int* __restrict__ perm, const int* __restrict__ rowidx,
+                                         const double* __restrict__ val, long long nnz, int* __restrict__ colT,
+                                         double* __restrict__ valT) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nnz) return;
+  const int src = perm[i];
+  colT[i] = rowidx[src];
+  valT[i] = val[src];
+}
+
+static int csr_transpose_impl(b200spai_csr_s* A, cudaStream_t stream, b200spai_csr_s** out) {
+  b200spai_csr_s* T = nullptr;
+  B2_TRY(csr_alloc(A->n_cols, A->n_rows, A->nnz, &T));
+  const long long nnz = A->nnz;
+  const int tb = 256;
+  B2_CUDA(cudaMemsetAsync(T->rowptr, 0, ((size_t)A->n_cols + 1) * sizeof(int), stream));
+  if (nnz > 0) {
+    int *rowidx = nullptr, *iota = nullptr, *keys_out = nullptr, *perm = nullptr;
+    B2_TRY(dev_alloc(&rowidx, nnz));
+    B2_TRY(dev_alloc(&iota, nnz));
+    B2_TRY(dev_alloc(&keys_out, nnz));
+    B2_TRY(dev_alloc(&perm, nnz));
+    const long long warps = A->n_rows;
+    expand_rows_kernel<<<(unsigned)((warps * 32 + tb - 1) / tb), tb, 0, stream>>>(A->rowptr, A->n_rows, rowidx);
+    iota_kernel<<<(unsigned)((nnz + tb - 1) / tb), tb, 0, stream>>>(iota, nnz);
+    count_cols_kernel<<<(unsigned)((nnz + tb - 1) / tb), tb, 0, stream>>>(A->col, nnz, T->rowptr);
+    B2_LAUNCH_CHECK();
+    // stable LSD radix sort of (column, position): within a column, ascending original position = ascending row
+    int end_bit = 1;
+    while (end_bit < 31 && (1LL << end_bit) < (long long)A->n_cols) ++end_bit;
+    size_t tmp_bytes = 0;
+    B2_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, A->col, keys_out, iota, perm, (int)nnz, 0, end_bit, stream));
+    size_t scan_bytes = 0;
+    B2_CUDA(cub::DeviceScan::InclusiveSum(nullptr, scan_bytes, T->rowptr, T->rowptr, A->n_cols + 1, stream));
+    void* tmp = nullptr;
+    B2_CUDA(cudaMalloc(&tmp, (tmp_bytes > scan_bytes ? tmp_bytes : scan_bytes) + 16));
+    B2_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, A->col, keys_out, iota, perm, (int)nnz, 0, end_bit, stream));
+    B2_CUDA(cub::DeviceScan::InclusiveSum(tmp, scan_bytes, T->rowptr, T->rowptr, A->n_cols + 1, stream));
+    gather_transposed_kernel<<<(unsigned)((nnz + tb - 1) / tb), tb, 0, stream>>>(perm, rowidx, A->val, nnz, T->col, T->val);
+    B2_LAUNCH_CHECK();
+    B2_CUDA(cudaStreamSynchronize(stream));
+    cudaFree(tmp);
+    cudaFree(rowidx);
+    cudaFree(iota);
+    cudaFree(keys_out);
+    cudaFree(perm);
+  }
+  *out = T;
+  return 0;
+}
+
+__global__ void diagonal_kernel(CsrView A, double* __restrict__ diag) {
+  int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= A.n_rows) return;
+  double d = 0.0;
+  for (int k = A.rowptr[row]; k < A.rowptr[row + 1]; ++k)
+    if (A.col[k] == row) d += A.val[k];
+  diag[row] = d;
+}
+
+}  // namespace b200spai
+
+using namespace b200spai;
+
+// =================================================================================================
+// C ABI
+// =================================================================================================
+extern "C" {
+
+const char* b200spai_last_error(void) { return last_error().c_str(); }
+int b200spai_version(void) { return 100; }
+
+int b200spai_device_info(char* name128, int* sm, int* cc) {
+  int dev = 0;
+  B2_CUDA(cudaGetDevice(&dev));
+  cudaDeviceProp p;
+  B2_CUDA(cudaGetDeviceProperties(&p, dev));
+  if (name128) snprintf(name128, 128, "%s", p.name);
+  if (sm) *sm = p.multiProcessorCount;
+  if (cc) *cc = p.major * 10 + p.minor;
+  return 0;
+}
+
+static int csr_create_common(int32_t n_rows, int32_t n_cols, int64_t nnz, const int32_t* indptr, const int32_t* indices,
+                             const double* data, cudaMemcpyKind kind, void* stream, b200spai_csr_t* out) {
+  B2_ARG(out != nullptr, "csr_create: out is NULL");
+  B2_ARG(indptr && (nnz == 0 || (indices && data)), "csr_create: NULL array");
+  b200spai_csr_s* a = nullptr;
+  B2_TRY(csr_alloc(n_rows, n_cols, nnz, &a));
+  cudaStream_t st = as_stream(stream);
+  B2_CUDA(cudaMemcpyAsync(a->rowptr, indptr, ((size_t)n_rows + 1) * sizeof(int), kind, st));
+  if (nnz > 0) {
+    B2_CUDA(cudaMemcpyAsync(a->col, indices, (size_t)nnz * sizeof(int), kind, st));
+    B2_CUDA(cudaMemcpyAsync(a->val, data, (size_t)nnz * sizeof(double), kind, st));
+  }
+  if (kind == cudaMemcpyHostToDevice) B2_CUDA(cudaStreamSynchronize(st));  // caller may free host arrays
+  *out = a;
+  return 0;
+}
+
+int b200spai_csr_create_host(int32_t n_rows, int32_t n_cols, int64_t nnz, const int32_t* indptr, const int32_t* indices,
+                             const double* data, void* stream, b200spai_csr_t* out) {
+  return csr_create_common(n_rows, n_cols, nnz, indptr, indices, data, cudaMemcpyHostToDevice, stream, out);
+}
+
+int b200spai_csr_create_dev(int32_t n_rows, int32_t n_cols, int64_t nnz, const int32_t* indptr, const int32_t* indices,
+                            const double* data, void* stream, b200spai_csr_t* out) {
+  return csr_create_common(n_rows, n_cols, nnz, indptr, indices, data, cudaMemcpyDeviceToDevice, stream, out);
+}
+
+int b200spai_csr_transpose(b200spai_csr_t a, void* stream, b200spai_csr_t* out) {
+  B2_ARG(a && out, "csr_transpose: NULL handle");
+  return csr_transpose_impl(a, as_stream(stream), out);
+}
+
+int b200spai_csr_shape(b200spai_csr_t a, int32_t* n_rows, int32_t* n_cols, int64_t* nnz) {
+  B2_ARG(a, "csr_shape: NULL handle");
+  if (n_rows) *n_rows = a->n_rows;
+  if (n_cols) *n_cols = a->n_cols;
+  if (nnz) *nnz = a->nnz;
+  return 0;
+}
+
+int b200spai_csr_download(b200spai_csr_t a, int32_t* indptr, int32_t* indices, double* data, void* stream) {
+  B2_ARG(a, "csr_download: NULL handle");
+  cudaStream_t st = as_stream(stream);
+  if (indptr) B2_CUDA(cudaMemcpyAsync(indptr, a->rowptr, ((size_t)a->n_rows + 1) * sizeof(int), cudaMemcpyDeviceToHost, st));
+  if (indices && a->nnz) B2_CUDA(cudaMemcpyAsync(indices, a->col, (size_t)a->nnz * sizeof(int), cudaMemcpyDeviceToHost, st));
+  if (data && a->nnz) B2_CUDA(cudaMemcpyAsync(data, a->val, (size_t)a->nnz * sizeof(double), cudaMemcpyDeviceToHost, st));
+  B2_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int b200spai_csr_device_ptrs(b200spai_csr_t a, const int32_t** indptr, const int32_t** indices, const double** data) {
+  B2_ARG(a, "csr_device_ptrs: NULL handle");
+  if (indptr) *indptr = a->rowptr;
+  if (indices) *indices = a->col;
+  if (data) *data = a->val;
+  return 0;
+}
+
+int b200spai_csr_destroy(b200spai_csr_t a) {
+  csr_free(a);
+  return 0;
+}
+
+int b200spai_spmv(b200spai_csr_t a, const double* x, double* y, int kernel, void* stream) {
+  B2_ARG(a && x && y, "spmv: NULL argument");
+  B2_ARG(kernel >= 0 && kernel <= 2, "spmv: kernel must be 0, 1 or 2");
+  if (a->n_rows == 0) return 0;
+  SpmvArgs args{};
+  args.x = x;
+  args.y = y;
+  return spmv_launch(a, args, SPMV_PLAIN, kernel, as_stream(stream));
+}
+
+int b200spai_csr_diagonal(b200spai_csr_t a, double* diag, void* stream) {
+  B2_ARG(a && diag, "csr_diagonal: NULL argument");
+  if (a->n_rows == 0) return 0;
+  diagonal_kernel<<<(a->n_rows + 255) / 256, 256, 0, as_stream(stream)>>>(a->view(), diag);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,37 @@
+// Device-resident CSR matrix + SpMV dispatch (internal header).
+#pragma once
+#include "spmv.cuh"
+
+struct b200spai_csr_s {
+  int n_rows = 0, n_cols = 0;
+  long long nnz = 0;
+  // device arrays, padded so that 16-byte bulk copies may over-read by up to 8 elements
+  int* rowptr = nullptr;
+  int* col = nullptr;
+  double* val = nullptr;
+  // streaming partition (built lazily per CAP): {r0, lo, r1, hi} per row block
+  int4* blk[2] = {nullptr, nullptr};
+  int nblk[2] = {0, 0};
+  int max_row_len = -1;
+  double mean_row_len = 0.0;
+
+  b200spai::CsrView view() const { return b200spai::CsrView{n_rows, rowptr, col, val}; }
+};
+
+namespace b200spai {
+
+// Allocate an empty matrix with padded arrays.
+int csr_alloc(int n_rows, int n_cols, long long nnz, b200spai_csr_s** out);
+void csr_free(b200spai_csr_s* a);
+
+// kernel: 0 auto, 1 vector, 2 stream.  `mode` selects the epilogue.
+int spmv_launch(b200spai_csr_s* A, const SpmvArgs& args, int mode, int kernel, cudaStream_t stream);
+// number of kernel launches spmv_launch performs (always 1; partition build is one-off)
+int csr_ensure_partition(b200spai_csr_s* A, int which, cudaStream_t stream);
+// Contiguous row blocks {r0, rowptr[r0], r1, rowptr[r1]} balanced on rowptr[r] + weight*r (one-off, synchronises).
+int build_row_blocks(const int* rowptr, int n_rows, long long nnz, long long target, int weight, int4** blk_out,
+                     int* nblk_out, cudaStream_t stream);
+// Resolve the kernel the auto policy picks (1 or 2).
+int spmv_auto_kernel(const b200spai_csr_s* A);
+
+}  // namespace b200spai

@@ -1,0 +1,299 @@
+// GNN inference (NodeEdgeProcessing, neural_cg/nn/gnns.py:77-97) as six fused kernels.
+//
+//   node_enc                       thread per node:   x0 = MLP(x)                       (gnns.py:83)
+//   mp layer 0 (+ edge encoder)    thread per edge:   e = MLP(edge_attr) on the fly     (gnns.py:84)
+//   mp layer 1..L-1                thread per edge, CTA per block of target nodes       (basic_layers.py:193-225)
+//   decoder                        thread per edge:   G = MLP([e, x[row], x[col]])      (gnns.py:88-95)
+//
+// Data layout in HBM (all fp32):
+//   * edges live in TARGET-SORTED order (stable sort by edge_index[1], built once per topology by
+//     b200spai_graph_create): position p has source src[p], target dst[p], original id perm[p]; the edges
+//     of target node i are the contiguous segment segptr[i]..segptr[i+1], in ascending original order --
+//     exactly the order in which the CPU scatter_add_ of the reference accumulates them.
+//   * edge features: tiles of 32 edges, [tile][4 chunks][32 lanes][4 floats], so a thread-per-edge warp
+//     reads/writes 512 contiguous bytes per instruction; updated in place.
+//   * node features: [N][16] row-major, ping-pong between layers (the edge MLP must see the OLD ones).
+//
+// One MP-layer kernel does, per block of whole target nodes (<= 56 nodes, ~224 edges):
+//   gather x[dst], x[src], e -> LayerNorm statistics of the 48-vector (shared by both MLPs) ->
+//   msg MLP and edge MLP (LayerNorm affine folded into the first Linear on the host) ->
+//   e += edge MLP (in place) ; messages to shared memory -> ordered segmented sum per target node
+//   (no atomics, deterministic) -> node MLP (LayerNorm16 + 3 Linear) -> x_out = x_in + node MLP.
+// The [E,48] concatenations, the [E,16] messages and the aggregate never touch HBM.
+//
+// Arithmetic is fp32 FFMA on purpose: the parity bar is 1e-5 relative on G, which TF32 tensor-core
+// math (10-bit mantissa) cannot meet, and the GEMMs are K<=48, N=16.
+#include <cub/cub.cuh>
+
+#include "csr.h"
+
+namespace b200spai {
+
+constexpr int F = 16;                // hidden width (config/gnn.yaml gnn_features)
+constexpr int MP_THREADS = 256;
+constexpr int NB_TARGET = 224;       // node-block target on key = segptr[r] + 4 r
+constexpr int NB_MAXN = 64;          // >= NB_TARGET / 4 nodes per block
+constexpr int MLP16 = 3 * (F * F + F);        // 816 floats: three 16x16 Linear (+bias)
+constexpr int MLP48 = 48 * F + F + 2 * (F * F + F);  // 1328 floats: 48->16, 16->16, 16->16
+constexpr int LAYER_FLOATS = 2 * MLP48 + MLP16;      // msg, edge, node
+
+}  // namespace b200spai
+
+struct b200spai_graph_s {
+  long long N = 0, E = 0;
+  int *perm = nullptr, *src = nullptr, *dst = nullptr, *segptr = nullptr;
+  int4* nb = nullptr;
+  int nnb = 0;
+  float *ef = nullptr, *x0 = nullptr, *x1 = nullptr;
+};
+
+struct b200spai_gnn_s {
+  int node_in = 0, edge_in = 0, b = 1, bb = 1, L = 4;
+  float* blob = nullptr;
+  long long blob_len = 0;
+  long long launches = 0;
+  const float* w_node_enc() const { return blob; }
+  const float* w_edge_enc() const { return blob + b200spai::MLP16; }
+  const float* w_layer(int l) const { return blob + 2 * b200spai::MLP16 + (long long)l * b200spai::LAYER_FLOATS; }
+  const float* w_dec() const { return blob + 2 * b200spai::MLP16 + (long long)L * b200spai::LAYER_FLOATS; }
+  static long long expected_len(int L) { return 2 * b200spai::MLP16 + (long long)L * b200spai::LAYER_FLOATS + b200spai::MLP48; }
+};
+
+namespace b200spai {
+
+// ---- graph preprocessing -------------------------------------------------------------------------
+__global__ void graph_keys_kernel(const long long* __restrict__ row, const long long* __restrict__ col, long long E,
+                                  long long N, int* __restrict__ keys, int* __restrict__ iota, int* __restrict__ bad) {
+  long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  const long long r = row[e], c = col[e];
+  if (r < 0 || r >= N || c < 0 || c >= N) atomicOr(bad, 1);
+  keys[e] = (int)c;
+  iota[e] = (int)e;
+}
+
+__global__ void graph_src_kernel(const long long* __restrict__ row, const int* __restrict__ perm, long long E,
+                                 int* __restrict__ src) {
+  long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < E) src[p] = (int)row[perm[p]];
+}
+
+__global__ void graph_segptr_kernel(const int* __restrict__ dst, long long E, long long N, int* __restrict__ segptr) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > N) return;
+  long long lo = 0, hi = E;
+  while (lo < hi) {
+    long long mid = lo + ((hi - lo) >> 1);
+    if (dst[mid] >= i) hi = mid; else lo = mid + 1;
+  }
+  segptr[i] = (int)lo;
+}
+
+static void graph_free(b200spai_graph_s* g) {
+  if (!g) return;
+  cudaFree(g->perm);
+  cudaFree(g->src);
+  cudaFree(g->dst);
+  cudaFree(g->segptr);
+  cudaFree(g->nb);
+  cudaFree(g->ef);
+  cudaFree(g->x0);
+  cudaFree(g->x1);
+  delete g;
+}
+
+static int graph_create_impl(long long N, long long E, const long long* edge_index, cudaStream_t st, b200spai_graph_s** out) {
+  B2_ARG(N >= 0 && E >= 0 && N < 2147483647LL && E < 2147483647LL - 64, "graph_create: sizes must fit int32");
+  auto* g = new b200spai_graph_s();
+  g->N = N;
+  g->E = E;
+  const long long Epad = ((E + 31) / 32) * 32;
+  int rc = dev_alloc(&g->perm, (size_t)E);
+  if (!rc) rc = dev_alloc(&g->src, (size_t)E);
+  if (!rc) rc = dev_alloc(&g->dst, (size_t)E);
+  if (!rc) rc = dev_alloc(&g->segptr, (size_t)N + 1);
+  if (!rc) rc = dev_alloc(&g->ef, (size_t)Epad * F);
+  if (!rc) rc = dev_alloc(&g->x0, (size_t)N * F);
+  if (!rc) rc = dev_alloc(&g->x1, (size_t)N * F);
+  int *keys = nullptr, *iota = nullptr, *bad = nullptr;
+  void* tmp = nullptr;
+  if (!rc) rc = dev_alloc(&keys, (size_t)E);
+  if (!rc) rc = dev_alloc(&iota, (size_t)E);
+  if (!rc) rc = dev_alloc(&bad, 1);
+  auto cleanup = [&]() {
+    cudaFree(keys);
+    cudaFree(iota);
+    cudaFree(bad);
+    cudaFree(tmp);
+  };
+  if (rc) {
+    cleanup();
+    graph_free(g);
+    return rc;
+  }
+  const int tb = 256;
+  const long long* row = edge_index;
+  const long long* col = edge_index + E;
+  cudaMemsetAsync(bad, 0, sizeof(int), st);
+  int h_bad = 0;
+  cudaError_t e = cudaSuccess;
+  if (E > 0) {
+    graph_keys_kernel<<<(unsigned)((E + tb - 1) / tb), tb, 0, st>>>(row, col, E, N, keys, iota, bad);
+    int end_bit = 1;
+    while (end_bit < 31 && (1LL << end_bit) < N) ++end_bit;
+    size_t tmp_bytes = 0;
+    e = cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, g->dst, iota, g->perm, (int)E, 0, end_bit, st);
+    if (e == cudaSuccess) e = cudaMalloc(&tmp, tmp_bytes + 16);
+    if (e == cudaSuccess) e = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, g->dst, iota, g->perm, (int)E, 0, end_bit, st);
+    if (e == cudaSuccess) graph_src_kernel<<<(unsigned)((E + tb - 1) / tb), tb, 0, st>>>(row, g->perm, E, g->src);
+  }
+  if (e == cudaSuccess) {
+    graph_segptr_kernel<<<(unsigned)((N + 1 + tb - 1) / tb), tb, 0, st>>>(g->dst, E, N, g->segptr);
+    e = cudaMemcpyAsync(&h_bad, bad, sizeof(int), cudaMemcpyDeviceToHost, st);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error(std::string("graph_create: ") + cudaGetErrorString(e));
+    cleanup();
+    graph_free(g);
+    return B200SPAI_ERR_CUDA;
+  }
+  cleanup();
+  if (h_bad) {
+    set_error("graph_create: edge_index out of range");
+    graph_free(g);
+    return B200SPAI_ERR_ARG;
+  }
+  rc = build_row_blocks(g->segptr, (int)N, E, NB_TARGET, 4, &g->nb, &g->nnb, st);
+  if (rc) {
+    graph_free(g);
+    return rc;
+  }
+  *out = g;
+  return 0;
+}
+
+}  // namespace b200spai
+
+#include "gnn_kernels.cuh"
+
+using namespace b200spai;
+
+extern "C" {
+
+int b200spai_graph_create(int64_t num_nodes, int64_t num_edges, const int64_t* edge_index_dev, void* stream,
+                          b200spai_graph_t* out) {
+  B2_ARG(out && (edge_index_dev || num_edges == 0), "graph_create: NULL argument");
+  return graph_create_impl(num_nodes, num_edges, reinterpret_cast<const long long*>(edge_index_dev), as_stream(stream), out);
+}
+
+int b200spai_graph_destroy(b200spai_graph_t g) {
+  graph_free(g);
+  return 0;
+}
+
+int b200spai_gnn_create(int32_t node_in, int32_t edge_in, int32_t block_size, int32_t num_layers, const float* blob_host,
+                        int64_t blob_len, b200spai_gnn_t* out) {
+  B2_ARG(out && blob_host, "gnn_create: NULL argument");
+  B2_ARG(node_in >= 1 && node_in <= F, "gnn_create: node_in must be in [1,16]");
+  B2_ARG(edge_in >= 1 && edge_in <= F, "gnn_create: edge_in must be in [1,16]");
+  B2_ARG(block_size >= 1 && block_size <= 4, "gnn_create: block_size must be in [1,4]");
+  B2_ARG(num_layers >= 1 && num_layers <= 64, "gnn_create: num_layers must be in [1,64]");
+  B2_ARG(blob_len == b200spai_gnn_s::expected_len(num_layers), "gnn_create: weight blob has the wrong length");
+  auto* m = new b200spai_gnn_s();
+  m->node_in = node_in;
+  m->edge_in = edge_in;
+  m->b = block_size;
+  m->bb = block_size * block_size;
+  m->L = num_layers;
+  m->blob_len = blob_len;
+  if (dev_alloc(&m->blob, (size_t)blob_len)) {
+    delete m;
+    return B200SPAI_ERR_CUDA;
+  }
+  cudaError_t e = cudaMemcpy(m->blob, blob_host, (size_t)blob_len * sizeof(float), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    set_error(std::string("gnn_create: ") + cudaGetErrorString(e));
+    cudaFree(m->blob);
+    delete m;
+    return B200SPAI_ERR_CUDA;
+  }
+  *out = m;
+  return 0;
+}
+
+int b200spai_gnn_destroy(b200spai_gnn_t m) {
+  if (!m) return 0;
+  cudaFree(m->blob);
+  delete m;
+  return 0;
+}
+
+int b200spai_gnn_forward(b200spai_gnn_t m, b200spai_graph_t g, const float* x_dev, const float* edge_attr_dev,
+                         float* g_out_dev, float* node_out_dev, void* stream) {
+  B2_ARG(m && g && x_dev && (edge_attr_dev || g->E == 0) && (g_out_dev || g->E == 0), "gnn_forward: NULL argument");
+  cudaStream_t st = as_stream(stream);
+  const long long N = g->N, E = g->E;
+  if (N == 0) return 0;
+  static int occ_first = 0, occ_rest = 0, occ_dec = 0;
+  if (!occ_first) {
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_first, gnn_mp_kernel<true>, MP_THREADS, 0));
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_rest, gnn_mp_kernel<false>, MP_THREADS, 0));
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_dec, gnn_dec_kernel, 256, 0));
+    if (occ_first < 1) occ_first = 1;
+    if (occ_rest < 1) occ_rest = 1;
+    if (occ_dec < 1) occ_dec = 1;
+  }
+  const int sms = sm_count();
+  {
+    long long ctas = (N + 255) / 256;
+    if (ctas > (long long)sms * 4) ctas = (long long)sms * 4;
+    gnn_node_enc_kernel<<<(int)ctas, 256, 0, st>>>(x_dev, m->node_in, N, m->w_node_enc(), g->x0);
+  }
+  float* xin = g->x0;
+  float* xout = g->x1;
+  for (int l = 0; l < m->L; ++l) {
+    MpParams P{};
+    P.src = g->src;
+    P.dst = g->dst;
+    P.segptr = g->segptr;
+    P.perm = g->perm;
+    P.nb = g->nb;
+    P.nnb = g->nnb;
+    P.ef = g->ef;
+    P.xin = xin;
+    P.xout = xout;
+    P.w_layer = m->w_layer(l);
+    P.w_eenc = m->w_edge_enc();
+    P.edge_attr = edge_attr_dev;
+    P.edge_in = m->edge_in;
+    int grid = sms * (l == 0 ? occ_first : occ_rest);
+    if (grid > g->nnb) grid = g->nnb;
+    if (grid < 1) grid = 1;
+    if (l == 0)
+      gnn_mp_kernel<true><<<grid, MP_THREADS, 0, st>>>(P);
+    else
+      gnn_mp_kernel<false><<<grid, MP_THREADS, 0, st>>>(P);
+    float* t = xin;
+    xin = xout;
+    xout = t;
+  }
+  if (E > 0) {
+    long long ctas = (E + 255) / 256;
+    if (ctas > (long long)sms * occ_dec) ctas = (long long)sms * occ_dec;
+    gnn_dec_kernel<<<(int)ctas, 256, 0, st>>>(g->src, g->dst, g->perm, g->ef, xin, m->w_dec(), E, m->bb, g_out_dev);
+  }
+  B2_LAUNCH_CHECK();
+  if (node_out_dev) B2_CUDA(cudaMemcpyAsync(node_out_dev, xin, (size_t)N * F * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  m->launches += 2 + m->L;
+  return 0;
+}
+
+int b200spai_gnn_launch_count(b200spai_gnn_t m, int64_t* launches) {
+  B2_ARG(m && launches, "gnn_launch_count: NULL argument");
+  *launches = m->launches;
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,272 @@
+// Device code of the GNN (included by gnn.cu after the constants and structs).
+#pragma once
+
+namespace b200spai {
+
+// nn.GELU() default = exact erf form (neural_cg/nn/basic_layers.py:21-22)
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
+
+// y[j] = bias[j] + sum_k x[k] * W[k][j];  W [K][16] and bias [16] in shared memory (16-byte aligned).
+// Every lane reads the same addresses (broadcast LDS.128), 4 weights per load, 16 FFMA per k.
+template <int K>
+__device__ __forceinline__ void dense16(const float* W, const float* bias, const float (&x)[K], float (&y)[F]) {
+  const float4* b4 = reinterpret_cast<const float4*>(bias);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float4 v = b4[q];
+    y[4 * q + 0] = v.x;
+    y[4 * q + 1] = v.y;
+    y[4 * q + 2] = v.z;
+    y[4 * q + 3] = v.w;
+  }
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const float4* w4 = reinterpret_cast<const float4*>(W + k * F);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float4 w = w4[q];
+      y[4 * q + 0] = fmaf(x[k], w.x, y[4 * q + 0]);
+      y[4 * q + 1] = fmaf(x[k], w.y, y[4 * q + 1]);
+      y[4 * q + 2] = fmaf(x[k], w.z, y[4 * q + 2]);
+      y[4 * q + 3] = fmaf(x[k], w.w, y[4 * q + 3]);
+    }
+  }
+}
+
+// FeedForward with 3 Linear layers and GELU in between (basic_layers.py:103-109, num_layers = 2).
+// Weight block layout: W1[K][16], b1[16], W2[16][16], b2[16], W3[16][16], b3[16].
+template <int K>
+__device__ __forceinline__ void mlp3(const float* W, const float (&x)[K], float (&out)[F]) {
+  float h1[F], h2[F];
+  dense16<K>(W, W + K * F, x, h1);
+#pragma unroll
+  for (int j = 0; j < F; ++j) h1[j] = gelu_erf(h1[j]);
+  const float* W2 = W + K * F + F;
+  dense16<F>(W2, W2 + F * F, h1, h2);
+#pragma unroll
+  for (int j = 0; j < F; ++j) h2[j] = gelu_erf(h2[j]);
+  const float* W3 = W2 + F * F + F;
+  dense16<F>(W3, W3 + F * F, h2, out);
+}
+
+__device__ __forceinline__ void load16(const float* p, float* dst) {
+  const float4* p4 = reinterpret_cast<const float4*>(p);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float4 v = __ldg(p4 + q);
+    dst[4 * q + 0] = v.x;
+    dst[4 * q + 1] = v.y;
+    dst[4 * q + 2] = v.z;
+    dst[4 * q + 3] = v.w;
+  }
+}
+
+// tile-transposed edge-feature address of (edge position p, 4-float chunk q)
+__device__ __forceinline__ float4* ef_chunk(float* ef, long long p, int q) {
+  return reinterpret_cast<float4*>(ef) + (((p >> 5) * 4 + q) * 32 + (p & 31));
+}
+
+// ---- node encoder ----------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) gnn_node_enc_kernel(const float* __restrict__ x, int node_in, long long N,
+                                                           const float* __restrict__ w, float* __restrict__ xout) {
+  __shared__ __align__(16) float s_w[MLP16];
+  for (int i = threadIdx.x; i < MLP16; i += blockDim.x) s_w[i] = w[i];
+  __syncthreads();
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += stride) {
+    float a[F], o[F];
+#pragma unroll
+    for (int k = 0; k < F; ++k) a[k] = (k < node_in) ? __ldg(x + i * node_in + k) : 0.0f;
+    mlp3<F>(s_w, a, o);
+    float4* o4 = reinterpret_cast<float4*>(xout + i * F);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) o4[q] = make_float4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+  }
+}
+
+// ---- message-passing layer ---------------------------------------------------------------------------
+struct MpParams {
+  const int* src;
+  const int* dst;
+  const int* segptr;
+  const int* perm;
+  const int4* nb;
+  int nnb;
+  float* ef;
+  const float* xin;
+  float* xout;
+  const float* w_layer;
+  const float* w_eenc;
+  const float* edge_attr;
+  int edge_in;
+};
+
+template <bool FIRST>
+__global__ void __launch_bounds__(MP_THREADS, 2) gnn_mp_kernel(MpParams P) {
+  __shared__ __align__(16) float s_w[LAYER_FLOATS + (FIRST ? MLP16 : 0)];
+  __shared__ float s_msg[MP_THREADS][F + 1];
+  __shared__ float s_agg[NB_MAXN][F];
+  __shared__ float s_h[NB_MAXN][F];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < LAYER_FLOATS; i += MP_THREADS) s_w[i] = P.w_layer[i];
+  if (FIRST)
+    for (int i = tid; i < MLP16; i += MP_THREADS) s_w[LAYER_FLOATS + i] = P.w_eenc[i];
+  __syncthreads();
+  const float* w_msg = s_w;
+  const float* w_edge = s_w + MLP48;
+  const float* w_node = s_w + 2 * MLP48;
+
+  for (int kb = blockIdx.x; kb < P.nnb; kb += gridDim.x) {
+    const int4 info = P.nb[kb];
+    const int n0 = info.x, e_lo = info.y, n1 = info.z, e_hi = info.w;
+    const int nn = n1 - n0;
+    for (int i = tid; i < nn * F; i += MP_THREADS) (&s_agg[0][0])[i] = 0.0f;
+    __syncthreads();
+
+    for (int c_lo = e_lo; c_lo < e_hi; c_lo += MP_THREADS) {
+      const int p = c_lo + tid;
+      if (p < e_hi) {
+        float v[48];  // [x_i = x[dst], x_j = x[src], e]  (basic_layers.py:216-222)
+        const int d = __ldg(P.dst + p), s = __ldg(P.src + p);
+        load16(P.xin + (long long)d * F, v);
+        load16(P.xin + (long long)s * F, v + 16);
+        if (FIRST) {  // edge encoder fused: e = MLP(edge_attr[original edge])  (gnns.py:84)
+          float a[F], e0[F];
+          const long long eo = __ldg(P.perm + p);
+#pragma unroll
+          for (int k = 0; k < F; ++k) a[k] = (k < P.edge_in) ? __ldg(P.edge_attr + eo * P.edge_in + k) : 0.0f;
+          mlp3<F>(s_w + LAYER_FLOATS, a, e0);
+#pragma unroll
+          for (int k = 0; k < F; ++k) v[32 + k] = e0[k];
+        } else {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float4 t = *ef_chunk(P.ef, p, q);
+            v[32 + 4 * q + 0] = t.x;
+            v[32 + 4 * q + 1] = t.y;
+            v[32 + 4 * q + 2] = t.z;
+            v[32 + 4 * q + 3] = t.w;
+          }
+        }
+        float ev[F];
+#pragma unroll
+        for (int k = 0; k < F; ++k) ev[k] = v[32 + k];
+        // LayerNorm(48) statistics, shared by msg_mlp and edge_mlp (their affines are folded into W1/b1)
+        float mean = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 48; ++k) mean += v[k];
+        mean *= (1.0f / 48.0f);
+        float var = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 48; ++k) {
+          const float c = v[k] - mean;
+          var = fmaf(c, c, var);
+        }
+        const float rstd = 1.0f / sqrtf(var * (1.0f / 48.0f) + 1e-5f);
+#pragma unroll
+        for (int k = 0; k < 48; ++k) v[k] = (v[k] - mean) * rstd;
+        float o[F];
+        mlp3<48>(w_msg, v, o);
+#pragma unroll
+        for (int j = 0; j < F; ++j) s_msg[tid][j] = o[j];
+        mlp3<48>(w_edge, v, o);  // edge update sees the OLD node features (basic_layers.py:208)
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          *ef_chunk(P.ef, p, q) = make_float4(ev[4 * q] + o[4 * q], ev[4 * q + 1] + o[4 * q + 1],
+                                              ev[4 * q + 2] + o[4 * q + 2], ev[4 * q + 3] + o[4 * q + 3]);
+      }
+      __syncthreads();
+      // ordered segmented sum: thread (node, channel) adds its node's messages of this chunk in edge order
+      {
+        const int c = tid & 15;
+        for (int nl = tid >> 4; nl < nn; nl += MP_THREADS / 16) {
+          int sb = __ldg(P.segptr + n0 + nl), se = __ldg(P.segptr + n0 + nl + 1);
+          sb = max(sb, c_lo);
+          se = min(se, c_lo + MP_THREADS);
+          float acc = s_agg[nl][c];
+          for (int q = sb; q < se; ++q) acc += s_msg[q - c_lo][c];
+          s_agg[nl][c] = acc;
+        }
+      }
+      __syncthreads();
+    }
+
+    // node update: x_out = x_in + node_mlp(LayerNorm16(agg))   (basic_layers.py:203-206,224-225)
+    {
+      const int j = tid & 15;
+      const int nn_pad = (nn + 1) & ~1;  // both half-warps of a warp take the same number of trips
+      for (int nl = tid >> 4; nl < nn_pad; nl += MP_THREADS / 16) {
+        const bool act = nl < nn;
+        const int nr = act ? nl : 0;
+        float a[F];
+        float mean = 0.0f;
+#pragma unroll
+        for (int k = 0; k < F; ++k) {
+          a[k] = s_agg[nr][k];
+          mean += a[k];
+        }
+        mean *= (1.0f / 16.0f);
+        float var = 0.0f;
+#pragma unroll
+        for (int k = 0; k < F; ++k) {
+          const float c = a[k] - mean;
+          var = fmaf(c, c, var);
+        }
+        const float rstd = 1.0f / sqrtf(var * (1.0f / 16.0f) + 1e-5f);
+        float h = w_node[F * F + j];
+#pragma unroll
+        for (int k = 0; k < F; ++k) h = fmaf((a[k] - mean) * rstd, w_node[k * F + j], h);
+        __syncwarp();
+        if (act) s_h[nr][j] = gelu_erf(h);
+        __syncwarp();
+        const float* W2 = w_node + F * F + F;
+        h = W2[F * F + j];
+#pragma unroll
+        for (int k = 0; k < F; ++k) h = fmaf(s_h[nr][k], W2[k * F + j], h);
+        __syncwarp();
+        if (act) s_agg[nr][j] = gelu_erf(h);
+        __syncwarp();
+        const float* W3 = W2 + F * F + F;
+        h = W3[F * F + j];
+#pragma unroll
+        for (int k = 0; k < F; ++k) h = fmaf(s_agg[nr][k], W3[k * F + j], h);
+        if (act) {
+          const long long idx = (long long)(n0 + nl) * F + j;
+          P.xout[idx] = __ldg(P.xin + idx) + h;
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---- decoder ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256, 2) gnn_dec_kernel(const int* __restrict__ src, const int* __restrict__ dst,
+                                                          const int* __restrict__ perm, float* ef,
+                                                          const float* __restrict__ x, const float* __restrict__ w,
+                                                          long long E, int bb, float* __restrict__ gout) {
+  __shared__ __align__(16) float s_w[MLP48];
+  for (int i = threadIdx.x; i < MLP48; i += blockDim.x) s_w[i] = w[i];
+  __syncthreads();
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < E; p += stride) {
+    float v[48], o[F];  // [edge, x[edge_index[0]], x[edge_index[1]]]  (gnns.py:88-90)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float4 t = *ef_chunk(ef, p, q);
+      v[4 * q + 0] = t.x;
+      v[4 * q + 1] = t.y;
+      v[4 * q + 2] = t.z;
+      v[4 * q + 3] = t.w;
+    }
+    load16(x + (long long)__ldg(src + p) * F, v + 16);
+    load16(x + (long long)__ldg(dst + p) * F, v + 32);
+    mlp3<48>(s_w, v, o);
+    const long long eo = __ldg(perm + p);
+#pragma unroll
+    for (int j = 0; j < F; ++j)
+      if (j < bb) gout[eo * bb + j] = o[j];
+  }
+}
+
+}  // namespace b200spai

@@ -1,0 +1,502 @@
+// Preconditioned conjugate gradients, fp64, with every scalar kept on the device.
+//
+// Recurrence = scipy.sparse.linalg.cg as called by the reference (neural_cg/utils/validate.py:163-201):
+//   r = b, x = 0; loop { if ||r|| < rtol*||b|| stop; z = M r; rho = r.z; p = z + (rho/rho_prev) p;
+//                        q = A p; alpha = rho / p.q; x += alpha p; r -= alpha q }
+// One iteration is 5 kernels for the SPAI preconditioner (4 for none/diagonal):
+//   K1  t = G^T r                       (SpMV over the precomputed transposed layout, no atomics)
+//   K2  z = G t + eps r ; rho = r.z     (SpMV, fused axpy + dot; last CTA: beta = rho/rho_prev)
+//   K3  p = z + beta p
+//   K4  q = A p ; pq = p.q              (SpMV, fused dot; last CTA: alpha = rho/pq)
+//   K5  x += alpha p ; r -= alpha q ; rr = r.r   (last CTA: iter++, history, convergence flag)
+// No scalar ever visits the host during the loop.  Two drivers:
+//   mode 1 (stream): iterations are enqueued in chunks; every kernel starts with `if (done) return`,
+//           and the host looks at a done flag copied to pinned memory two chunks behind the GPU.
+//   mode 2 (graph):  one CUDA graph = init kernel + a WHILE conditional node whose body is the 5
+//           kernels; K5's last CTA sets the loop condition (cudaGraphSetConditional).  One launch
+//           per solve, no host involvement until the result is read.
+#include "csr.h"
+
+using namespace b200spai;
+
+struct b200spai_pcg_s {
+  b200spai_csr_s* A = nullptr;
+  b200spai_csr_s* G = nullptr;
+  b200spai_csr_s* GT = nullptr;  // owned
+  double eps = 0.0;
+  int n = 0;
+  double *r = nullptr, *z = nullptr, *p = nullptr, *q = nullptr, *t = nullptr, *d = nullptr, *bw = nullptr, *xw = nullptr;
+  bool have_d = false;
+  PcgScalars* sc = nullptr;
+  double* partials = nullptr;
+  unsigned* ticket = nullptr;
+  double* hist = nullptr;
+  long long hist_cap = 0;
+  PcgScalars* h_in = nullptr;   // pinned
+  PcgScalars* h_out = nullptr;  // pinned
+  int* h_done = nullptr;        // pinned [2]
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_chunk[2] = {nullptr, nullptr};
+  cudaStream_t body_stream = nullptr, cap_stream = nullptr;  // graphs are captured on private streams
+  int mode = 0;
+  long long launches = 0;
+  float setup_ms = 0.f;
+  cudaGraphExec_t exec[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaGraph_t graph[4] = {nullptr, nullptr, nullptr, nullptr};
+  unsigned long long cond[4] = {0, 0, 0, 0};
+  int launches_per_iter[4] = {0, 0, 0, 0};
+};
+
+namespace b200spai {
+
+static constexpr int VTHREADS = 256;
+static constexpr int MAX_PARTIALS = 8192;
+
+static int vec_grid(int n) {
+  long long g = ((long long)n + VTHREADS * 4 - 1) / (VTHREADS * 4);
+  const long long cap = (long long)sm_count() * 8;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+__global__ void __launch_bounds__(VTHREADS) pcg_init_kernel(const double* __restrict__ b, double* __restrict__ x,
+                                                            double* __restrict__ r, int n, PcgScalars* sc,
+                                                            double* partials, unsigned* ticket, double* hist) {
+  __shared__ double red[34];
+  double acc = 0.0;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double v = b[i];
+    r[i] = v;
+    x[i] = 0.0;
+    acc += v * v;
+  }
+  double cta = block_sum(acc, red);
+  double total;
+  if (grid_sum_last(cta, partials, ticket, red, total) && threadIdx.x == 0) {
+    const double bn = sqrt(total);
+    sc->bnorm = bn;
+    sc->atol = fmax(0.0, sc->rtol * bn);
+    sc->rr = total;
+    sc->rho = sc->rho_prev = sc->pq = sc->alpha = sc->beta = 0.0;
+    sc->iter = 0;
+    sc->breakdown = 0;
+    const int zero_rhs = (bn == 0.0) || !(bn == bn);
+    sc->done = zero_rhs;
+    sc->converged = (bn == 0.0);
+    if (!(bn == bn)) sc->breakdown = 1;
+    hist[0] = bn;
+  }
+}
+
+// z = r (d == nullptr) or z = r / d ; rho = r.z
+__global__ void __launch_bounds__(VTHREADS) pcg_jacobi_kernel(const double* __restrict__ r, const double* __restrict__ d,
+                                                              double* __restrict__ z, int n, PcgScalars* sc,
+                                                              double* partials, unsigned* ticket) {
+  __shared__ double red[34];
+  if (sc->done) return;
+  double acc = 0.0;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double rv = r[i];
+    const double zv = d ? rv / d[i] : rv;
+    z[i] = zv;
+    acc += rv * zv;
+  }
+  double cta = block_sum(acc, red);
+  double total;
+  if (grid_sum_last(cta, partials, ticket, red, total) && threadIdx.x == 0) pcg_final_scalar(sc, FINAL_RHO, total);
+}
+
+__global__ void __launch_bounds__(VTHREADS) pcg_update_p_kernel(const double* __restrict__ z, double* __restrict__ p,
+                                                                int n, const PcgScalars* sc) {
+  if (sc->done) return;
+  const bool first = (sc->iter == 0);
+  const double beta = sc->beta;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double zv = z[i];
+    // scipy: p *= beta; p += z  (two roundings, reproduced: no fma contraction)
+    p[i] = first ? zv : __dadd_rn(__dmul_rn(p[i], beta), zv);
+  }
+}
+
+__global__ void __launch_bounds__(VTHREADS) pcg_update_xr_kernel(double* __restrict__ x, double* __restrict__ r,
+                                                                 const double* __restrict__ p, const double* __restrict__ q,
+                                                                 int n, PcgScalars* sc, double* partials, unsigned* ticket,
+                                                                 double* hist) {
+  __shared__ double red[34];
+  if (sc->done) return;
+  const double alpha = sc->alpha;
+  double acc = 0.0;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    // scipy: x += alpha*p ; r -= alpha*q  (product rounded, then add)
+    x[i] = __dadd_rn(x[i], __dmul_rn(alpha, p[i]));
+    const double rv = __dsub_rn(r[i], __dmul_rn(alpha, q[i]));
+    r[i] = rv;
+    acc += rv * rv;
+  }
+  double cta = block_sum(acc, red);
+  double total;
+  if (grid_sum_last(cta, partials, ticket, red, total) && threadIdx.x == 0) {
+    if (sc->breakdown || !(total == total)) {
+      sc->breakdown = 1;
+      sc->done = 1;
+    } else {
+      sc->rr = total;
+      sc->rho_prev = sc->rho;
+      const int it = sc->iter + 1;
+      sc->iter = it;
+      const double nrm = sqrt(total);
+      hist[it] = nrm;
+      if (nrm < sc->atol) {
+        sc->done = 1;
+        sc->converged = 1;
+      } else if (it >= sc->max_iter) {
+        sc->done = 1;
+      }
+    }
+    if (sc->use_cond) cudaGraphSetConditional((cudaGraphConditionalHandle)sc->cond_handle, sc->done ? 0u : 1u);
+  }
+}
+
+static int ensure_hist(b200spai_pcg_s* s, long long need) {
+  if (need <= s->hist_cap) return 0;
+  cudaFree(s->hist);
+  s->hist = nullptr;
+  B2_TRY(dev_alloc(&s->hist, (size_t)need));
+  s->hist_cap = need;
+  for (int i = 0; i < 4; ++i) {  // graphs bake the history pointer
+    if (s->exec[i]) cudaGraphExecDestroy(s->exec[i]);
+    if (s->graph[i]) cudaGraphDestroy(s->graph[i]);
+    s->exec[i] = nullptr;
+    s->graph[i] = nullptr;
+  }
+  return 0;
+}
+
+static int ensure_diag(b200spai_pcg_s* s, cudaStream_t st) {
+  if (s->have_d) return 0;
+  B2_TRY(dev_alloc(&s->d, (size_t)s->n));
+  B2_TRY(b200spai_csr_diagonal(s->A, s->d, st));
+  s->have_d = true;
+  return 0;
+}
+
+// z = M r (+ rho = r.z when sc != nullptr)
+static int enqueue_precond(b200spai_pcg_s* s, int precond, const double* r, double* z, PcgScalars* sc, cudaStream_t st,
+                           int* nlaunch) {
+  if (precond == B200SPAI_PRECOND_NONE || precond == B200SPAI_PRECOND_DIAGONAL) {
+    B2_ARG(sc != nullptr, "jacobi preconditioner needs the scalar block");
+    pcg_jacobi_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(r, precond == B200SPAI_PRECOND_DIAGONAL ? s->d : nullptr, z,
+                                                           s->n, sc, s->partials, s->ticket);
+    B2_LAUNCH_CHECK();
+    *nlaunch += 1;
+    return 0;
+  }
+  const bool scaled = (precond == B200SPAI_PRECOND_EXT_SPAI_SCALED);
+  SpmvArgs a1{};
+  a1.x = r;
+  a1.y = s->t;
+  a1.d = scaled ? s->d : nullptr;
+  a1.sc = sc;
+  B2_TRY(spmv_launch(s->GT, a1, scaled ? SPMV_SCALE : SPMV_PLAIN, 0, st));
+  SpmvArgs a2{};
+  a2.x = s->t;
+  a2.y = z;
+  a2.aux = r;
+  a2.d = scaled ? s->d : nullptr;
+  a2.eps = s->eps;
+  a2.partials = s->partials;
+  a2.ticket = s->ticket;
+  a2.sc = sc;
+  a2.final_op = FINAL_RHO;
+  B2_TRY(spmv_launch(s->G, a2, SPMV_AXPY_DOT, 0, st));
+  *nlaunch += 2;
+  return 0;
+}
+
+static int enqueue_iteration(b200spai_pcg_s* s, int precond, double* x, cudaStream_t st, int* nlaunch) {
+  B2_TRY(enqueue_precond(s, precond, s->r, s->z, s->sc, st, nlaunch));
+  pcg_update_p_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(s->z, s->p, s->n, s->sc);
+  SpmvArgs a{};
+  a.x = s->p;
+  a.y = s->q;
+  a.partials = s->partials;
+  a.ticket = s->ticket;
+  a.sc = s->sc;
+  a.final_op = FINAL_PQ;
+  B2_TRY(spmv_launch(s->A, a, SPMV_DOT, 0, st));
+  pcg_update_xr_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(x, s->r, s->p, s->q, s->n, s->sc, s->partials, s->ticket,
+                                                            s->hist);
+  B2_LAUNCH_CHECK();
+  *nlaunch += 3;
+  return 0;
+}
+
+static int build_graph(b200spai_pcg_s* s, int precond, cudaStream_t st) {
+  if (s->exec[precond]) return 0;
+  // make sure lazily built partitions exist before capture (their build synchronises)
+  if (spmv_auto_kernel(s->A) == 2) {
+    SpmvArgs warm{};
+    warm.x = s->p;
+    warm.y = s->q;
+    B2_TRY(spmv_launch(s->A, warm, SPMV_PLAIN, 0, st));
+    if (precond >= B200SPAI_PRECOND_EXT_SPAI) {
+      warm.x = s->r;
+      warm.y = s->t;
+      if (spmv_auto_kernel(s->GT) == 2) B2_TRY(spmv_launch(s->GT, warm, SPMV_PLAIN, 0, st));
+      warm.x = s->t;
+      warm.y = s->z;
+      if (spmv_auto_kernel(s->G) == 2) B2_TRY(spmv_launch(s->G, warm, SPMV_PLAIN, 0, st));
+    }
+    B2_CUDA(cudaStreamSynchronize(st));
+  }
+  cudaGraph_t graph = nullptr;
+  cudaStream_t cs = s->cap_stream;  // the caller's stream may be the legacy default stream (not capturable)
+  B2_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeRelaxed));
+  pcg_init_kernel<<<vec_grid(s->n), VTHREADS, 0, cs>>>(s->bw, s->xw, s->r, s->n, s->sc, s->partials, s->ticket, s->hist);
+  cudaStreamCaptureStatus status;
+  const cudaGraphNode_t* deps = nullptr;
+  size_t ndeps = 0;
+  B2_CUDA(cudaStreamGetCaptureInfo(cs, &status, nullptr, &graph, &deps, &ndeps));
+  cudaGraphConditionalHandle handle;
+  B2_CUDA(cudaGraphConditionalHandleCreate(&handle, graph, 1, cudaGraphCondAssignDefault));
+  cudaGraphNodeParams cp = {};
+  cp.type = cudaGraphNodeTypeConditional;
+  cp.conditional.handle = handle;
+  cp.conditional.type = cudaGraphCondTypeWhile;
+  cp.conditional.size = 1;
+  cudaGraphNode_t cnode;
+  B2_CUDA(cudaGraphAddNode(&cnode, graph, deps, ndeps, &cp));
+  cudaGraph_t body = cp.conditional.phGraph_out[0];
+  B2_CUDA(cudaStreamUpdateCaptureDependencies(cs, &cnode, 1, cudaStreamSetCaptureDependencies));
+  int nl = 0;
+  B2_CUDA(cudaStreamBeginCaptureToGraph(s->body_stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+  int rc = enqueue_iteration(s, precond, s->xw, s->body_stream, &nl);
+  cudaGraph_t body_out = nullptr;
+  cudaError_t e1 = cudaStreamEndCapture(s->body_stream, &body_out);
+  cudaGraph_t full = nullptr;
+  cudaError_t e2 = cudaStreamEndCapture(cs, &full);
+  if (rc) return rc;
+  B2_CUDA(e1);
+  B2_CUDA(e2);
+  cudaGraphExec_t exec = nullptr;
+  B2_CUDA(cudaGraphInstantiate(&exec, full, 0));
+  s->graph[precond] = full;
+  s->exec[precond] = exec;
+  s->cond[precond] = (unsigned long long)handle;
+  s->launches_per_iter[precond] = nl;
+  return 0;
+}
+
+static int solve_impl(b200spai_pcg_s* s, int precond, const double* b, double* x, double rtol, int max_iter,
+                      double* hist_out, cudaStream_t st, b200spai_pcg_result* res) {
+  B2_ARG(s && b && x && res, "pcg_solve: NULL argument");
+  B2_ARG(precond >= 0 && precond <= 3, "pcg_solve: unknown preconditioner");
+  if (precond >= B200SPAI_PRECOND_EXT_SPAI) B2_ARG(s->G && s->GT, "pcg_solve: ext_spai needs b200spai_pcg_set_spai first");
+  if (precond == B200SPAI_PRECOND_DIAGONAL || precond == B200SPAI_PRECOND_EXT_SPAI_SCALED) B2_TRY(ensure_diag(s, st));
+  if (max_iter <= 0) max_iter = s->n;
+  B2_TRY(ensure_hist(s, (long long)max_iter + 1));
+  int mode = s->mode;
+  if (mode == 0) mode = 2;
+
+  PcgScalars init{};
+  init.rtol = rtol;
+  init.max_iter = max_iter;
+  if (mode == 2) {
+    B2_TRY(build_graph(s, precond, st));
+    init.use_cond = 1;
+    init.cond_handle = s->cond[precond];
+  }
+  *s->h_in = init;
+  B2_CUDA(cudaEventRecord(s->ev0, st));
+  B2_CUDA(cudaMemcpyAsync(s->sc, s->h_in, sizeof(PcgScalars), cudaMemcpyHostToDevice, st));
+  if (mode == 2) {
+    B2_CUDA(cudaMemcpyAsync(s->bw, b, (size_t)s->n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    B2_CUDA(cudaGraphLaunch(s->exec[precond], st));
+    B2_CUDA(cudaMemcpyAsync(x, s->xw, (size_t)s->n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  } else {
+    pcg_init_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(b, x, s->r, s->n, s->sc, s->partials, s->ticket, s->hist);
+    B2_LAUNCH_CHECK();
+    s->launches += 1;
+    const int CH = 8;
+    int slot = 0;
+    long long enq = 0;
+    bool first = true;
+    s->h_done[0] = s->h_done[1] = 0;
+    while (true) {
+      int nl = 0;
+      for (int c = 0; c < CH; ++c) B2_TRY(enqueue_iteration(s, precond, x, st, &nl));
+      s->launches += nl;
+      enq += CH;
+      B2_CUDA(cudaMemcpyAsync(s->h_done + slot, &s->sc->done, sizeof(int), cudaMemcpyDeviceToHost, st));
+      B2_CUDA(cudaEventRecord(s->ev_chunk[slot], st));
+      slot ^= 1;
+      if (first) {
+        first = false;
+        if (enq < (long long)max_iter + CH) continue;
+      }
+      B2_CUDA(cudaEventSynchronize(s->ev_chunk[slot]));
+      if (s->h_done[slot]) break;
+      if (enq >= (long long)max_iter + 2 * CH) break;
+    }
+  }
+  B2_CUDA(cudaEventRecord(s->ev1, st));
+  B2_CUDA(cudaMemcpyAsync(s->h_out, s->sc, sizeof(PcgScalars), cudaMemcpyDeviceToHost, st));
+  B2_CUDA(cudaStreamSynchronize(st));
+  const PcgScalars& o = *s->h_out;
+  if (mode == 2) s->launches += 1 + (long long)s->launches_per_iter[precond] * (o.iter > 0 ? o.iter : 1);
+  res->iterations = o.iter;
+  res->converged = o.converged;
+  res->breakdown = o.breakdown;
+  res->reserved = mode;
+  res->b_norm = o.bnorm;
+  res->final_residual = sqrt(o.rr);
+  res->setup_ms = s->setup_ms;
+  B2_CUDA(cudaEventElapsedTime(&res->solve_ms, s->ev0, s->ev1));
+  if (hist_out)
+    B2_CUDA(cudaMemcpyAsync(hist_out, s->hist, ((size_t)o.iter + 1) * sizeof(double), cudaMemcpyDefault, st));
+  B2_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+}  // namespace b200spai
+
+extern "C" {
+
+int b200spai_pcg_create(b200spai_csr_t a, b200spai_pcg_t* out) {
+  B2_ARG(a && out, "pcg_create: NULL argument");
+  B2_ARG(a->n_rows == a->n_cols, "pcg_create: A must be square");
+  auto* s = new b200spai_pcg_s();
+  s->A = a;
+  s->n = a->n_rows;
+  const size_t n = (size_t)s->n;
+  int rc = 0;
+  for (double** v : {&s->r, &s->z, &s->p, &s->q, &s->t, &s->bw, &s->xw})
+    if (!rc) rc = dev_alloc(v, n);
+  if (!rc) rc = dev_alloc(&s->sc, 1);
+  if (!rc) rc = dev_alloc(&s->partials, MAX_PARTIALS);
+  if (!rc) rc = dev_alloc(&s->ticket, 1);
+  if (rc) {
+    b200spai_pcg_destroy(s);
+    return rc;
+  }
+  B2_CUDA(cudaMemset(s->ticket, 0, sizeof(unsigned)));
+  B2_CUDA(cudaMemset(s->sc, 0, sizeof(PcgScalars)));
+  B2_CUDA(cudaMemset(s->p, 0, n * sizeof(double)));
+  B2_CUDA(cudaMallocHost((void**)&s->h_in, sizeof(PcgScalars)));
+  B2_CUDA(cudaMallocHost((void**)&s->h_out, sizeof(PcgScalars)));
+  B2_CUDA(cudaMallocHost((void**)&s->h_done, 2 * sizeof(int)));
+  B2_CUDA(cudaEventCreate(&s->ev0));
+  B2_CUDA(cudaEventCreate(&s->ev1));
+  B2_CUDA(cudaEventCreateWithFlags(&s->ev_chunk[0], cudaEventDisableTiming));
+  B2_CUDA(cudaEventCreateWithFlags(&s->ev_chunk[1], cudaEventDisableTiming));
+  B2_CUDA(cudaStreamCreateWithFlags(&s->body_stream, cudaStreamNonBlocking));
+  B2_CUDA(cudaStreamCreateWithFlags(&s->cap_stream, cudaStreamNonBlocking));
+  *out = s;
+  return 0;
+}
+
+int b200spai_pcg_set_spai(b200spai_pcg_t s, b200spai_csr_t g, double epsilon, void* stream) {
+  B2_ARG(s && g, "pcg_set_spai: NULL argument");
+  B2_ARG(g->n_rows == s->n && g->n_cols == s->n, "pcg_set_spai: G must have A's shape");
+  cudaStream_t st = as_stream(stream);
+  cudaEvent_t e0, e1;
+  B2_CUDA(cudaEventCreate(&e0));
+  B2_CUDA(cudaEventCreate(&e1));
+  B2_CUDA(cudaEventRecord(e0, st));
+  if (s->GT) csr_free(s->GT);
+  s->GT = nullptr;
+  for (int i = 2; i < 4; ++i) {  // SPAI graphs bake G's pointers
+    if (s->exec[i]) cudaGraphExecDestroy(s->exec[i]);
+    if (s->graph[i]) cudaGraphDestroy(s->graph[i]);
+    s->exec[i] = nullptr;
+    s->graph[i] = nullptr;
+  }
+  B2_TRY(b200spai_csr_transpose(g, stream, &s->GT));
+  s->G = g;
+  s->eps = epsilon;
+  B2_CUDA(cudaEventRecord(e1, st));
+  B2_CUDA(cudaEventSynchronize(e1));
+  B2_CUDA(cudaEventElapsedTime(&s->setup_ms, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  return 0;
+}
+
+int b200spai_pcg_set_mode(b200spai_pcg_t s, int mode) {
+  B2_ARG(s && mode >= 0 && mode <= 2, "pcg_set_mode: mode must be 0, 1 or 2");
+  s->mode = mode;
+  return 0;
+}
+
+int b200spai_pcg_solve_dev(b200spai_pcg_t s, int precond, const double* b, double* x, double rtol, int32_t max_iter,
+                           double* hist, void* stream, b200spai_pcg_result* result) {
+  return solve_impl(s, precond, b, x, rtol, max_iter, hist, as_stream(stream), result);
+}
+
+int b200spai_pcg_solve_host(b200spai_pcg_t s, int precond, const double* b_host, double* x_host, double rtol,
+                            int32_t max_iter, double* hist_host, void* stream, b200spai_pcg_result* result) {
+  B2_ARG(s && b_host && x_host && result, "pcg_solve_host: NULL argument");
+  cudaStream_t st = as_stream(stream);
+  double *bd = nullptr, *xd = nullptr;
+  B2_TRY(dev_alloc(&bd, (size_t)s->n));
+  B2_TRY(dev_alloc(&xd, (size_t)s->n));
+  B2_CUDA(cudaMemcpyAsync(bd, b_host, (size_t)s->n * sizeof(double), cudaMemcpyHostToDevice, st));
+  int rc = solve_impl(s, precond, bd, xd, rtol, max_iter, hist_host, st, result);
+  if (!rc) {
+    cudaError_t e = cudaMemcpyAsync(x_host, xd, (size_t)s->n * sizeof(double), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) {
+      set_error(std::string("pcg_solve_host: copy back failed: ") + cudaGetErrorString(e));
+      rc = B200SPAI_ERR_CUDA;
+    }
+  }
+  cudaFree(bd);
+  cudaFree(xd);
+  return rc;
+}
+
+int b200spai_pcg_apply_precond(b200spai_pcg_t s, int precond, const double* r, double* z, void* stream) {
+  B2_ARG(s && r && z, "pcg_apply_precond: NULL argument");
+  B2_ARG(precond >= B200SPAI_PRECOND_EXT_SPAI && precond <= 3 && s->G, "pcg_apply_precond: SPAI preconditioner not set");
+  cudaStream_t st = as_stream(stream);
+  if (precond == B200SPAI_PRECOND_EXT_SPAI_SCALED) B2_TRY(ensure_diag(s, st));
+  int nl = 0;
+  B2_TRY(enqueue_precond(s, precond, r, z, nullptr, st, &nl));
+  s->launches += nl;
+  return 0;
+}
+
+int b200spai_pcg_launch_count(b200spai_pcg_t s, int64_t* launches) {
+  B2_ARG(s && launches, "pcg_launch_count: NULL argument");
+  *launches = s->launches;
+  return 0;
+}
+
+int b200spai_pcg_destroy(b200spai_pcg_t s) {
+  if (!s) return 0;
+  for (int i = 0; i < 4; ++i) {
+    if (s->exec[i]) cudaGraphExecDestroy(s->exec[i]);
+    if (s->graph[i]) cudaGraphDestroy(s->graph[i]);
+  }
+  if (s->GT) csr_free(s->GT);
+  for (double* v : {s->r, s->z, s->p, s->q, s->t, s->d, s->bw, s->xw, s->partials, s->hist}) cudaFree(v);
+  cudaFree(s->sc);
+  cudaFree(s->ticket);
+  if (s->h_in) cudaFreeHost(s->h_in);
+  if (s->h_out) cudaFreeHost(s->h_out);
+  if (s->h_done) cudaFreeHost(s->h_done);
+  if (s->ev0) cudaEventDestroy(s->ev0);
+  if (s->ev1) cudaEventDestroy(s->ev1);
+  if (s->ev_chunk[0]) cudaEventDestroy(s->ev_chunk[0]);
+  if (s->ev_chunk[1]) cudaEventDestroy(s->ev_chunk[1]);
+  if (s->body_stream) cudaStreamDestroy(s->body_stream);
+  if (s->cap_stream) cudaStreamDestroy(s->cap_stream);
+  delete s;
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,269 @@
+// CSR SpMV kernels (fp64 values, int32 indices) with fused PCG epilogues.
+//
+// Two kernels, both persistent (grid = SM count x resident CTAs) and both deterministic:
+//
+//  * spmv_vector_kernel  -- a sub-warp of VEC lanes per row, direct global loads, two row batches in
+//    flight per warp.  Robust baseline; used for tiny matrices and very irregular ones.
+//  * spmv_stream_kernel  -- the B200 path.  Rows are pre-partitioned (once per matrix) into row
+//    blocks of <= CAP non-zeros.  CSR values / column indices / row pointers of a block are
+//    *contiguous* in HBM, so each block is staged into shared memory with three 1-D TMA bulk copies
+//    (cp.async.bulk + mbarrier complete_tx), STAGES blocks deep, with an L2 evict-first policy so the
+//    streamed matrix does not displace the vectors that are gathered out of L2.  A staged block is
+//    consumed in two passes: (A) nnz-parallel  prod[k] = val[k] * x[col[k]]  (coalesced smem reads,
+//    all gathers independent), (B) row-parallel  y[row] = sum(prod[rowptr..])  + fused epilogue.
+//    Blocks are dealt to CTAs round-robin, so all CTAs sweep the matrix as one wavefront and the
+//    gathered window of x stays L2/L1 resident.
+//
+// Epilogues (MODE):   PLAIN      y = Ax
+//                     SCALE      y = (Ax) / d                          t = (G^T r)/d   (scaled SPAI)
+//                     AXPY_DOT   y = Ax + eps*aux [/ d];  dot = aux.y    z = G t + eps r; rho = r.z
+//                     DOT        y = Ax;  dot = x.y                     q = A p; pq = p.q
+// The dot is reduced deterministically (fixed per-CTA order, then the last CTA sums the per-CTA
+// partials in index order) and the last CTA also performs the scalar update (beta / alpha).
+#pragma once
+#include "common.cuh"
+
+namespace b200spai {
+
+struct PcgScalars {
+  double rho, rho_prev, pq, rr, alpha, beta, bnorm, atol, rtol;
+  int iter, done, converged, breakdown, max_iter;
+  int use_cond;
+  unsigned long long cond_handle;
+};
+
+struct CsrView {
+  int n_rows;
+  const int* rowptr;
+  const int* col;
+  const double* val;
+};
+
+enum { SPMV_PLAIN = 0, SPMV_SCALE = 1, SPMV_AXPY_DOT = 2, SPMV_DOT = 3 };
+enum { FINAL_NONE = 0, FINAL_RHO = 1, FINAL_PQ = 2 };
+
+struct SpmvArgs {
+  const double* x;
+  double* y;
+  const double* aux;  // AXPY_DOT: the vector added with eps and dotted with y
+  const double* d;    // optional diagonal (divide), SCALE and AXPY_DOT
+  double eps;
+  double* partials;
+  unsigned* ticket;
+  PcgScalars* sc;
+  int final_op;
+};
+
+__device__ __forceinline__ void pcg_final_scalar(PcgScalars* sc, int final_op, double total) {
+  if (final_op == FINAL_RHO) {
+    sc->rho = total;
+    sc->beta = (sc->iter > 0) ? total / sc->rho_prev : 0.0;
+  } else if (final_op == FINAL_PQ) {
+    sc->pq = total;
+    if (!(total > 0.0) || !(sc->rho == sc->rho)) {  // p.q <= 0 or NaN: not SPD / breakdown
+      sc->breakdown = 1;
+      sc->alpha = 0.0;
+    } else {
+      sc->alpha = sc->rho / total;
+    }
+  }
+}
+
+template <int MODE>
+__device__ __forceinline__ double spmv_prefetch_aux(const SpmvArgs& a, int row) {
+  if (MODE == SPMV_AXPY_DOT) return a.aux[row];
+  if (MODE == SPMV_DOT) return a.x[row];
+  return 0.0;
+}
+
+template <int MODE>
+__device__ __forceinline__ void spmv_row_epilogue(const SpmvArgs& a, int row, double sum, double auxv, double& dot) {
+  double yv = sum;
+  if (MODE == SPMV_SCALE) {
+    yv = sum / a.d[row];
+  } else if (MODE == SPMV_AXPY_DOT) {
+    double e = a.eps * auxv;
+    if (a.d) e = e / a.d[row];
+    yv = sum + e;
+    dot += auxv * yv;
+  } else if (MODE == SPMV_DOT) {
+    dot += auxv * yv;
+  }
+  a.y[row] = yv;
+}
+
+template <int MODE>
+__device__ __forceinline__ void spmv_finish_dot(const SpmvArgs& a, double dot, double* red) {
+  if (MODE == SPMV_AXPY_DOT || MODE == SPMV_DOT) {
+    double cta = block_sum(dot, red);
+    double total;
+    if (grid_sum_last(cta, a.partials, a.ticket, red, total)) {
+      if (threadIdx.x == 0 && a.sc) pcg_final_scalar(a.sc, a.final_op, total);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Kernel 1: sub-warp per row
+// ------------------------------------------------------------------------------------------------
+template <int VEC, int MODE>
+__global__ void __launch_bounds__(256) spmv_vector_kernel(CsrView A, SpmvArgs a) {
+  __shared__ double red[34];
+  if (a.sc && a.sc->done) return;
+  constexpr int RPW = 32 / VEC;  // rows per warp per batch
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / VEC, sl = lane % VEC;
+  const long long warp_g = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  const long long stride = nwarps * RPW;
+  double dot = 0.0;
+  for (long long rb = warp_g * RPW; rb < A.n_rows; rb += 2 * stride) {
+    const long long row0 = rb + sub, row1 = rb + stride + sub;
+    const bool v0 = row0 < A.n_rows, v1 = row1 < A.n_rows;
+    int s0 = 0, e0 = 0, s1 = 0, e1 = 0;
+    if (v0) { s0 = __ldg(A.rowptr + row0); e0 = __ldg(A.rowptr + row0 + 1); }
+    if (v1) { s1 = __ldg(A.rowptr + row1); e1 = __ldg(A.rowptr + row1 + 1); }
+    double aux0 = 0.0, aux1 = 0.0;
+    if (sl == 0) {
+      if (v0) aux0 = spmv_prefetch_aux<MODE>(a, (int)row0);
+      if (v1) aux1 = spmv_prefetch_aux<MODE>(a, (int)row1);
+    }
+    double sum0 = 0.0, sum1 = 0.0;
+    int k0 = s0 + sl, k1 = s1 + sl;
+    while (k0 < e0 || k1 < e1) {
+      double p0 = 0.0, p1 = 0.0;
+      if (k0 < e0) p0 = __ldg(A.val + k0) * __ldg(a.x + __ldg(A.col + k0));
+      if (k1 < e1) p1 = __ldg(A.val + k1) * __ldg(a.x + __ldg(A.col + k1));
+      sum0 += p0;
+      sum1 += p1;
+      k0 += VEC;
+      k1 += VEC;
+    }
+#pragma unroll
+    for (int o = VEC / 2; o > 0; o >>= 1) {
+      sum0 += __shfl_xor_sync(0xffffffffu, sum0, o);
+      sum1 += __shfl_xor_sync(0xffffffffu, sum1, o);
+    }
+    if (sl == 0) {
+      if (v0) spmv_row_epilogue<MODE>(a, (int)row0, sum0, aux0, dot);
+      if (v1) spmv_row_epilogue<MODE>(a, (int)row1, sum1, aux1, dot);
+    }
+  }
+  spmv_finish_dot<MODE>(a, dot, red);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Kernel 2: TMA-staged streaming kernel
+// ------------------------------------------------------------------------------------------------
+template <int CAP>
+struct StreamCfg {
+  static constexpr int SLACK = CAP / 8;          // rows up to SLACK long never overflow a block
+  static constexpr int TARGET = CAP - SLACK;     // partition target on key(r) = rowptr[r] + 2 r
+  static constexpr int RCAP = CAP / 2 + 1;       // max rows per block + 1
+  static constexpr int VALS = CAP + 8;           // staged doubles (alignment slack both ends)
+  static constexpr int COLS = CAP + 8;
+  static constexpr int RPTR = ((RCAP + 8 + 3) / 4) * 4;
+  static constexpr int STAGE_BYTES = VALS * 8 + COLS * 4 + RPTR * 4;
+  static constexpr int smem_bytes(int stages) { return stages * STAGE_BYTES + stages * 16 /*hdr*/ + stages * 8 + 34 * 8; }
+};
+
+template <int CAP, int STAGES, int MODE>
+__global__ void __launch_bounds__(256) spmv_stream_kernel(CsrView A, const int4* __restrict__ blk, int nblk, SpmvArgs a) {
+  using C = StreamCfg<CAP>;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  if (a.sc && a.sc->done) return;
+  double* s_vals = reinterpret_cast<double*>(smem_raw);                              // [STAGES][VALS]
+  int* s_cols = reinterpret_cast<int*>(smem_raw + STAGES * C::VALS * 8);             // [STAGES][COLS]
+  int* s_rptr = s_cols + STAGES * C::COLS;                                           // [STAGES][RPTR]
+  int4* s_hdr = reinterpret_cast<int4*>(s_rptr + STAGES * C::RPTR);                  // [STAGES]
+  uint64_t* s_full = reinterpret_cast<uint64_t*>(s_hdr + STAGES);                    // [STAGES]
+  double* red = reinterpret_cast<double*>(s_full + STAGES);                          // [34]
+
+  const int tid = threadIdx.x;
+  const int G = gridDim.x;
+  const int first = blockIdx.x;
+  const int n_items = (first < nblk) ? (nblk - first + G - 1) / G : 0;
+  uint64_t policy = 0;
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) mbar_init(s_full + s, 1);
+    mbar_fence_init();
+    policy = policy_evict_first();
+  }
+  __syncthreads();
+
+  // producer state (thread 0 only): block descriptor of the next item to issue, prefetched
+  int issue_j = 0;
+  int4 next_info = make_int4(0, 0, 0, 0);
+  if (tid == 0 && n_items > 0) next_info = __ldg(blk + first);
+
+  auto issue = [&](int j) {  // thread 0: stage item j into slot j % STAGES
+    const int slot = j % STAGES;
+    const int4 info = next_info;
+    if (j + 1 < n_items) next_info = __ldg(blk + first + (long long)(j + 1) * G);
+    s_hdr[slot] = info;
+    const int lo = info.y, hi = info.w, r0 = info.x, r1 = info.z;
+    const int cnt = hi - lo;
+    if (cnt > CAP || cnt <= 0) {  // long block or all-empty rows: processed from global memory
+      mbar_arrive(s_full + slot);
+      return;
+    }
+    const int a_lo = lo & ~3;
+    const int n4 = (hi - a_lo + 3) & ~3;
+    const int ra = r0 & ~3;
+    const int nr4 = (r1 + 1 - ra + 3) & ~3;
+    mbar_arrive_expect_tx(s_full + slot, (uint32_t)(n4 * 12 + nr4 * 4));
+    bulk_g2s(s_vals + slot * C::VALS, A.val + a_lo, (uint32_t)n4 * 8, s_full + slot, policy);
+    bulk_g2s(s_cols + slot * C::COLS, A.col + a_lo, (uint32_t)n4 * 4, s_full + slot, policy);
+    bulk_g2s(s_rptr + slot * C::RPTR, A.rowptr + ra, (uint32_t)nr4 * 4, s_full + slot, policy);
+  };
+
+  if (tid == 0) {
+    for (; issue_j < STAGES - 1 && issue_j < n_items; ++issue_j) issue(issue_j);
+  }
+
+  double dot = 0.0;
+  for (int i = 0; i < n_items; ++i) {
+    const int slot = i % STAGES;
+    if (tid == 0 && issue_j < n_items) {
+      issue(issue_j);
+      ++issue_j;
+    }
+    mbar_wait(s_full + slot, (uint32_t)((i / STAGES) & 1));
+    const int4 info = s_hdr[slot];
+    const int r0 = info.x, lo = info.y, r1 = info.z, hi = info.w;
+    const int cnt = hi - lo;
+    if (cnt > 0 && cnt <= CAP) {
+      double* vals = s_vals + slot * C::VALS + (lo & 3);
+      const int* cols = s_cols + slot * C::COLS + (lo & 3);
+      const int* rptr = s_rptr + slot * C::RPTR + (r0 & 3);
+      // pass A: products, nnz-parallel
+      for (int k = tid; k < cnt; k += 256) vals[k] = vals[k] * __ldg(a.x + cols[k]);
+      __syncthreads();
+      // pass B: row sums, row-parallel
+      for (int rr = tid; rr < r1 - r0; rr += 256) {
+        const int row = r0 + rr;
+        const double auxv = spmv_prefetch_aux<MODE>(a, row);
+        const int s = rptr[rr] - lo, e = rptr[rr + 1] - lo;
+        double sum = 0.0;
+        for (int k = s; k < e; ++k) sum += vals[k];
+        spmv_row_epilogue<MODE>(a, row, sum, auxv, dot);
+      }
+    } else {
+      // long block (a row longer than the stage capacity) or a block of empty rows: warp per row
+      // straight from global memory
+      const int lane = tid & 31, warp = tid >> 5;
+      for (int row = r0 + warp; row < r1; row += 8) {
+        const int s = __ldg(A.rowptr + row), e = __ldg(A.rowptr + row + 1);
+        double sum = 0.0;
+        for (int k = s + lane; k < e; k += 32) sum += __ldg(A.val + k) * __ldg(a.x + __ldg(A.col + k));
+        sum = warp_sum(sum);
+        if (lane == 0) spmv_row_epilogue<MODE>(a, row, sum, spmv_prefetch_aux<MODE>(a, row), dot);
+      }
+    }
+    fence_proxy_async();  // order this thread's generic smem accesses before the slot's next TMA fill
+    __syncthreads();
+  }
+  spmv_finish_dot<MODE>(a, dot, red);
+}
+
+}  // namespace b200spai

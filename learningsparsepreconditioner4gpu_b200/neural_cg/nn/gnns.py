@@ -1,0 +1,229 @@
+"""Host-side mirror of ``neural_cg/nn/gnns.py``: ``NodeEdgeProcessing`` with the reference's constructor
+signature (gnns.py:10-32) and ``state_dict`` key names, whose ``forward`` runs the
+hand-written sm_100a kernels through the C ABI (``b200spai_gnn_forward``) instead of torch/PyG ops.
+
+The parameters live in ordinary ``nn.Linear`` / ``nn.LayerNorm`` modules so that checkpoints of the
+reference load unchanged (``load_state_dict``) and random initialisation consumes the torch RNG in the
+same order (``self.apply(weight_init)``, gnns.py:75).  Those modules are never *called*: ``forward`` packs
+their weights into one fp32 blob (``pack_state_dict``) and hands device pointers to the library.  There
+is no eager fallback -- without a CUDA device ``forward`` raises.
+
+Supported architecture = the reference's config/gnn.yaml: 16 features, ``num_layers: 2`` MLPs (3 Linear),
+GELU, ``pre_norm: none`` on encoders/decoder, ``pre_norm: layer`` on the three MP MLPs, residuals on,
+``aggr: add``; node/edge input widths <= 16, block size <= 4, any number of MP layers.  Anything else
+raises ``NotImplementedError`` at construction.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional, Union
+
+import numpy as np
+import torch
+from torch import nn
+
+from ... import _lib
+from ..utils.weight_init import weight_init
+from .basic_layers import FeedForward, MPLayer
+
+F = 16
+MLP16 = 3 * (F * F + F)
+MLP48 = 48 * F + F + 2 * (F * F + F)
+LAYER_FLOATS = 2 * MLP48 + MLP16
+
+
+def blob_length(num_layers: int) -> int:
+    return 2 * MLP16 + num_layers * LAYER_FLOATS + MLP48
+
+
+def _mlp_block(sd: Dict[str, torch.Tensor], prefix: str, k_pad: int, out_pad: int = F) -> np.ndarray:
+    """One FeedForward as [W1^T (k_pad x 16), b1, W2^T, b2, W3^T (16 x 16, zero-padded outputs), b3] in fp32.
+    A LayerNorm pre-norm (weight g, bias c) is folded into the first Linear in float64:
+        W1'[k][j] = g[k] * W1[j][k],   b1'[j] = b1[j] + sum_k c[k] * W1[j][k]
+    so the kernel only has to apply (v - mean) * rstd."""
+    W1 = sd[prefix + "lift.0.weight"].detach().double().cpu().numpy()  # [16, in]
+    b1 = sd[prefix + "lift.0.bias"].detach().double().cpu().numpy()
+    if prefix + "pre_norm.weight" in sd:
+        g = sd[prefix + "pre_norm.weight"].detach().double().cpu().numpy()
+        c = sd[prefix + "pre_norm.bias"].detach().double().cpu().numpy()
+        b1 = b1 + W1 @ c
+        W1 = W1 * g[None, :]
+    W2 = sd[prefix + "body.0.0.weight"].detach().double().cpu().numpy()
+    b2 = sd[prefix + "body.0.0.bias"].detach().double().cpu().numpy()
+    W3 = sd[prefix + "proj.0.weight"].detach().double().cpu().numpy()  # [out, 16]
+    b3 = sd[prefix + "proj.0.bias"].detach().double().cpu().numpy()
+    assert W1.shape[0] == F and W2.shape == (F, F) and W3.shape[1] == F and W1.shape[1] <= k_pad and W3.shape[0] <= out_pad
+    W1t = np.zeros((k_pad, F))
+    W1t[: W1.shape[1]] = W1.T
+    W3t = np.zeros((F, out_pad))
+    W3t[:, : W3.shape[0]] = W3.T
+    b3p = np.zeros(out_pad)
+    b3p[: b3.shape[0]] = b3
+    return np.concatenate([W1t.ravel(), b1, W2.T.ravel(), b2, W3t.ravel(), b3p]).astype(np.float32)
+
+
+def pack_state_dict(sd: Dict[str, torch.Tensor], num_layers: int, prefix: str = "") -> np.ndarray:
+    """The "GNN weight blob" of include/b200spai.h (b200spai_gnn_create): node_enc, edge_enc,
+    per layer [msg_mlp, edge_mlp, node_mlp], edge_dec."""
+    parts = [_mlp_block(sd, prefix + "node_enc.", F), _mlp_block(sd, prefix + "edge_enc.", F)]
+    for k in range(num_layers):
+        p = f"{prefix}mp_layers.{k}."
+        parts += [_mlp_block(sd, p + "msg_mlp.", 48), _mlp_block(sd, p + "edge_mlp.", 48), _mlp_block(sd, p + "node_mlp.", F)]
+    parts.append(_mlp_block(sd, prefix + "edge_dec.", 48))
+    blob = np.ascontiguousarray(np.concatenate(parts), dtype=np.float32)
+    assert blob.size == blob_length(num_layers)
+    return blob
+
+
+def _check_mlp(cfg: dict, pre_norm: str, what: str):
+    ok = (str(cfg.get("pre_norm", "none")).lower() in pre_norm and int(cfg["hidden_channels"]) == F
+          and int(cfg["num_layers"]) == 2 and cfg.get("activation", "gelu") == "gelu"
+          and cfg.get("out_activation", "none") == "none")
+    if not ok:
+        raise NotImplementedError(f"{what}={dict(cfg)}: the CUDA path implements the reference default only "
+                                  f"(hidden 16, num_layers 2, gelu, pre_norm in {pre_norm})")
+
+
+class DeviceGraph:
+    """Per-topology preprocessing (b200spai_graph_create): target-sorted edges, segment offsets, workspaces."""
+
+    def __init__(self, edge_index: torch.Tensor, num_nodes: int):
+        _lib.require_cuda()
+        assert edge_index.is_cuda and edge_index.dtype == torch.int64 and edge_index.dim() == 2 and edge_index.shape[0] == 2
+        self._lib = _lib.load()
+        self.num_nodes, self.num_edges = int(num_nodes), int(edge_index.shape[1])
+        ei = edge_index.contiguous()
+        self._h = C.c_void_p()
+        _lib.check(self._lib.b200spai_graph_create(self.num_nodes, self.num_edges, C.c_void_p(ei.data_ptr()),
+                                                   C.c_void_p(torch.cuda.current_stream().cuda_stream), C.byref(self._h)),
+                   "graph_create")
+        self.key = (ei.data_ptr(), self.num_nodes, self.num_edges)
+
+    def close(self):
+        if self._h:
+            self._lib.b200spai_graph_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class NodeEdgeProcessing(nn.Module):
+    def __init__(
+        self,
+        node_in_features: int,
+        node_out_features: Union[int, None],
+        node_encoder: dict,
+        node_decoder: dict,
+        edge_in_features: int,
+        edge_out_features: int,
+        edge_encoder: dict,
+        edge_decoder: dict,
+        num_mp_layers: int,
+        node_features: int,
+        edge_features: int,
+        node_residual: bool,
+        edge_residual: bool,
+        node_mlp: dict,
+        edge_mlp: dict,
+        msg_mlp: dict,
+        msg_norm: bool,
+        aggr: str = "add",
+    ):
+        super().__init__()
+        if node_out_features is not None:
+            raise NotImplementedError("node decoder: the workspaces always pass node_out_features=None (workspace.py:72)")
+        if not (node_features == F and edge_features == F and node_residual and edge_residual and aggr == "add"):
+            raise NotImplementedError("the CUDA path implements 16 features, residual MP layers and aggr='add'")
+        if not (1 <= node_in_features <= F and 1 <= edge_in_features <= F and 1 <= edge_out_features <= F):
+            raise NotImplementedError("input/output widths must be in [1,16]")
+        for cfg, pn, what in ((node_encoder, ("none",), "node_encoder"), (edge_encoder, ("none",), "edge_encoder"),
+                              (edge_decoder, ("none",), "edge_decoder"),
+                              (node_mlp, ("layer", "layernorm", "layer_norm"), "node_mlp"),
+                              (edge_mlp, ("layer", "layernorm", "layer_norm"), "edge_mlp"),
+                              (msg_mlp, ("layer", "layernorm", "layer_norm"), "msg_mlp")):
+            _check_mlp(cfg, pn, what)
+        # same registration order as the reference (gnns.py:34-74) -> same RNG consumption, same keys
+        self.node_enc = FeedForward(in_channels=node_in_features, out_channels=node_features, **node_encoder)
+        self.node_dec = nn.Identity()
+        self.edge_enc = FeedForward(in_channels=edge_in_features, out_channels=edge_features, **edge_encoder)
+        self.edge_dec = FeedForward(in_channels=edge_features + 2 * node_features, out_channels=edge_out_features, **edge_decoder)
+        self.mp_layers = nn.ModuleList()
+        for _ in range(num_mp_layers):
+            self.mp_layers.append(MPLayer(node_channels=node_features, edge_channels=edge_features,
+                                          node_residual=node_residual, edge_residual=edge_residual, node_mlp=node_mlp,
+                                          edge_mlp=edge_mlp, msg_mlp=msg_mlp, aggr=aggr, msg_norm=msg_norm))
+        self.apply(weight_init)
+        self.node_in, self.edge_in, self.edge_out = node_in_features, edge_in_features, edge_out_features
+        self.num_mp_layers = num_mp_layers
+        self._engine = None
+        self._engine_version = None
+        self._graph: Optional[DeviceGraph] = None
+
+    # ---- device engine ------------------------------------------------------------------------------
+    def _weights_version(self):
+        return tuple((p.data_ptr(), p._version) for p in self.parameters())
+
+    def _get_engine(self):
+        ver = self._weights_version()
+        if self._engine is None or ver != self._engine_version:
+            self.release_engine()
+            lib = _lib.load()
+            blob = pack_state_dict(self.state_dict(), self.num_mp_layers)
+            b = int(round(self.edge_out ** 0.5))
+            if b * b != self.edge_out:
+                raise NotImplementedError("edge_out_features must be block_size**2")
+            h = C.c_void_p()
+            _lib.check(lib.b200spai_gnn_create(self.node_in, self.edge_in, b, self.num_mp_layers,
+                                               C.c_void_p(blob.ctypes.data), blob.size, C.byref(h)), "gnn_create")
+            self._engine, self._engine_version = h, ver
+        return self._engine
+
+    def release_engine(self):
+        if self._engine is not None:
+            _lib.load().b200spai_gnn_destroy(self._engine)
+            self._engine = None
+
+    def graph_for(self, edge_index: torch.Tensor, num_nodes: int) -> DeviceGraph:
+        """Topology preprocessing is cached on the identity of the edge_index tensor (fixed-topology
+        datasets reuse one graph for every sample)."""
+        key = (edge_index.data_ptr(), int(num_nodes), int(edge_index.shape[1]))
+        if self._graph is None or self._graph.key != key:
+            self._graph = DeviceGraph(edge_index, num_nodes)
+        return self._graph
+
+    @property
+    def launches(self) -> int:
+        if self._engine is None:
+            return 0
+        v = C.c_int64()
+        _lib.check(_lib.load().b200spai_gnn_launch_count(self._engine, C.byref(v)), "gnn_launch_count")
+        return v.value
+
+    @torch.no_grad()
+    def forward(self, node_attr: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor,
+                graph: Optional[DeviceGraph] = None):
+        _lib.require_cuda()
+        if not (node_attr.is_cuda and edge_index.is_cuda and edge_attr.is_cuda):
+            raise _lib.B200SpaiError("NodeEdgeProcessing.forward needs CUDA tensors: there is no CPU path")
+        N, E = node_attr.shape[0], edge_index.shape[1]
+        assert node_attr.shape[1] == self.node_in and edge_attr.shape == (E, self.edge_in)
+        graph = graph or self.graph_for(edge_index, N)
+        x = node_attr.detach().to(torch.float32).contiguous()
+        ea = edge_attr.detach().to(torch.float32).contiguous()
+        edge_out = torch.empty((E, self.edge_out), dtype=torch.float32, device=x.device)
+        node_out = torch.empty((N, F), dtype=torch.float32, device=x.device)
+        lib = _lib.load()
+        _lib.check(lib.b200spai_gnn_forward(self._get_engine(), graph._h, C.c_void_p(x.data_ptr()), C.c_void_p(ea.data_ptr()),
+                                            C.c_void_p(edge_out.data_ptr()), C.c_void_p(node_out.data_ptr()),
+                                            C.c_void_p(torch.cuda.current_stream().cuda_stream)), "gnn_forward")
+        return node_out, edge_out
+
+    def __del__(self):
+        try:
+            self.release_engine()
+        except Exception:
+            pass

@@ -1,0 +1,197 @@
+"""GPU parity tests for the CSR / SpMV / PCG part of the path, through the C ABI (ctypes).
+
+Bars: sparsity patterns bit-exact; SpMV within fp64 summation-order noise (1e-13 relative to
+|A||x|); PCG iteration count within +-1 of the reference's scipy solve (golden) and residual
+history within 1e-6 relative over the first iterations / 5 % relative later (histories of two
+correctly rounded CG runs drift apart with the iteration count)."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import torch
+
+from conftest import GOLDEN_CASES, golden_csr, load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    from learningsparsepreconditioner4gpu_b200 import device
+
+    return device
+
+
+def _rand_csr(n, m, density, seed, irregular=False):
+    rng = np.random.default_rng(seed)
+    A = sp.random(n, m, density=density, format="csr", random_state=rng, dtype=np.float64)
+    if irregular:  # a few very long rows and some empty rows
+        L = sp.random(4, m, density=0.6, format="csr", random_state=rng, dtype=np.float64)
+        A = sp.vstack([A[: n // 2], L, sp.csr_matrix((3, m)), A[n // 2:]]).tocsr()
+    A.sort_indices()
+    return A
+
+
+@pytest.mark.parametrize("kernel", [1, 2])
+@pytest.mark.parametrize("shape", [(1, 1, 1.0), (37, 53, 0.3), (5000, 5000, 0.003), (20000, 20000, 0.0008)])
+def test_spmv_matches_scipy(kernel, shape):
+    d = _dev()
+    n, m, dens = shape
+    A = _rand_csr(n, m, dens, seed=n, irregular=n >= 5000)
+    x = np.random.default_rng(1).standard_normal(A.shape[1])
+    Ad = d.DeviceCSR.from_scipy(A)
+    y = Ad.matvec(torch.from_numpy(x).cuda(), kernel=kernel).cpu().numpy()
+    ref = A @ x
+    scale = abs(A) @ abs(x) + 1e-300
+    assert np.max(np.abs(y - ref) / scale) < 1e-13
+
+
+def test_spmv_long_rows_stream_kernel():
+    d = _dev()
+    rng = np.random.default_rng(3)
+    # rows far longer than the 2048-entry stage -> long-block path; plus empty rows
+    A = sp.vstack([sp.random(3, 9000, density=0.9, format="csr", random_state=rng), sp.csr_matrix((5, 9000)),
+                   sp.random(2000, 9000, density=0.002, format="csr", random_state=rng)]).tocsr()
+    A.sort_indices()
+    x = rng.standard_normal(9000)
+    y = d.DeviceCSR.from_scipy(A).matvec(torch.from_numpy(x).cuda(), kernel=2).cpu().numpy()
+    assert np.max(np.abs(y - A @ x) / (abs(A) @ abs(x) + 1e-300)) < 1e-13
+
+
+def test_roundtrip_and_transpose_bit_exact():
+    d = _dev()
+    A = _rand_csr(3000, 2500, 0.004, seed=5, irregular=True)
+    Ad = d.DeviceCSR.from_scipy(A)
+    B = Ad.to_scipy()
+    assert np.array_equal(B.indptr, A.indptr) and np.array_equal(B.indices, A.indices) and np.array_equal(B.data, A.data)
+    T = Ad.transpose().to_scipy()
+    R = sp.csr_matrix(A.T)
+    R.sort_indices()
+    assert T.shape == R.shape
+    assert np.array_equal(T.indptr, R.indptr) and np.array_equal(T.indices, R.indices) and np.array_equal(T.data, R.data)
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_edges_to_csr_bit_exact(name):
+    """Device to_csr_cpu == the reference's to_csr_cpu (golden), pattern and values bit for bit."""
+    d = _dev()
+    g = load_golden(name)
+    ei = torch.from_numpy(g["raw_edge_index"]).cuda()
+    N = g["mask"].shape[0]
+    mask = torch.from_numpy(g["mask"]).cuda()
+    for vals, key, m in ((g["matrix_values"], "A", mask), (g["matrix_values"], "A_nomask", None), (g["G"], "G", mask)):
+        got = d.DeviceCSR.from_edges(ei, torch.from_numpy(vals).cuda(), N, m).to_scipy()
+        ref = golden_csr(g, key)
+        assert np.array_equal(got.indptr, ref.indptr), (name, key)
+        assert np.array_equal(got.indices, ref.indices), (name, key)
+        assert np.array_equal(got.data, ref.data), (name, key)
+
+
+def test_edges_to_csr_rejects_unsorted():
+    d = _dev()
+    from learningsparsepreconditioner4gpu_b200._lib import B200SpaiError
+
+    ei = torch.tensor([[0, 1, 0], [0, 1, 1]], dtype=torch.int64).cuda()
+    with pytest.raises(B200SpaiError):
+        d.DeviceCSR.from_edges(ei, torch.ones(3).cuda(), 2, None)
+
+
+def test_edges_to_csr_creates_missing_masked_diagonal():
+    d = _dev()
+    from oracle.assemble import to_csr_cpu
+
+    ei = torch.tensor([[0, 0, 1, 2, 2], [0, 1, 2, 0, 2]], dtype=torch.int64)  # row 1 has no diagonal
+    vals = torch.tensor([2.0, 1.0, 3.0, 1.0, 4.0])
+    mask = torch.tensor([[1.0], [0.0], [1.0]])
+    ref = to_csr_cpu(ei, vals.view(-1, 1, 1), 3, mask)
+    got = d.DeviceCSR.from_edges(ei.cuda(), vals.cuda(), 3, mask.cuda()).to_scipy()
+    assert np.array_equal(got.indptr, ref.indptr) and np.array_equal(got.indices, ref.indices) and np.array_equal(got.data, ref.data)
+
+
+@pytest.mark.parametrize("mode", [1, 2])
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_pcg_matches_reference_iterations(name, mode):
+    d = _dev()
+    from oracle import pcg as opcg
+
+    g = load_golden(name)
+    A, G = golden_csr(g, "A"), golden_csr(g, "G")
+    eps = float(g["epsilon"])
+    gt = g["mask"].reshape(-1).astype(np.float64)
+    b = A @ gt
+    Ad, Gd = d.DeviceCSR.from_scipy(A), d.DeviceCSR.from_scipy(G)
+    solver = d.DevicePCG(Ad, mode=mode)
+    solver.set_spai(Gd, eps)
+    for kind, key in (("ext_spai", "iters_pcg"), ("none", "iters_cg"), ("ext_spai_scaled", "iters_pcg_scaled")):
+        x, res, hist = solver.solve(torch.from_numpy(b).cuda(), kind, rtol=1e-6, history=True)
+        ref_it = int(g[key])
+        assert abs(res.iterations - ref_it) <= 1, (name, kind, res.iterations, ref_it)
+        assert res.breakdown == 0
+        _, its, ohist = opcg.pcg_restated(A, b, opcg.make_preconditioner(kind, A, G, eps), rtol=1e-6)
+        h = hist.cpu().numpy()
+        k = min(len(h), len(ohist))
+        early = min(k, 20)
+        assert np.allclose(h[:early], ohist[:early], rtol=1e-6), (name, kind)
+        if ref_it < A.shape[0]:  # converged runs: full history within 5 % and the solution agrees
+            assert np.allclose(h[:k], ohist[:k], rtol=5e-2), (name, kind)
+            assert res.converged == 1
+            if kind == "ext_spai":
+                assert np.allclose(x.cpu().numpy(), g["x_solution"], rtol=1e-5, atol=1e-7 * np.abs(g["x_solution"]).max())
+    assert solver.launches > 0
+
+
+def test_precond_operator_matches_scipy_definition():
+    d = _dev()
+    g = load_golden("poisson_b1")
+    A, G = golden_csr(g, "A"), golden_csr(g, "G")
+    eps = float(g["epsilon"])
+    solver = d.DevicePCG(d.DeviceCSR.from_scipy(A))
+    solver.set_spai(d.DeviceCSR.from_scipy(G), eps)
+    r = np.random.default_rng(0).standard_normal(A.shape[0])
+    z = solver.apply_precond(torch.from_numpy(r).cuda(), "ext_spai").cpu().numpy()
+    ref = G @ (sp.csr_matrix(G.T) @ r) + eps * r
+    assert np.allclose(z, ref, rtol=1e-12, atol=1e-14)
+    zs = solver.apply_precond(torch.from_numpy(r).cuda(), "ext_spai_scaled").cpu().numpy()
+    dd = A.diagonal()
+    assert np.allclose(zs, G @ ((sp.csr_matrix(G.T) @ r) / dd) + eps * r / dd, rtol=1e-12, atol=1e-14)
+
+
+def test_plugin_api_host_buffers_and_zero_rhs():
+    from learningsparsepreconditioner4gpu_b200.linalg import PreconditionedConjugateGradient as pcg
+
+    g = load_golden("heat_b1")
+    A, G = golden_csr(g, "A"), golden_csr(g, "G")
+    b = A @ g["mask"].reshape(-1).astype(np.float64)
+    x = np.zeros_like(b)
+    solver = pcg(A, device="cuda", preconditioner="ext_spai", dtype=np.float64)
+    iters, t_prec, t_solve = solver(b.copy(), x, 1e-6, A.shape[0], ext_spai=(G, float(g["epsilon"])), record_history=True)
+    assert abs(iters - int(g["iters_pcg"])) <= 1 and t_solve > 0 and t_prec >= 0
+    assert np.linalg.norm(b - A @ x) < 1e-5 * np.linalg.norm(b)
+    assert len(solver.history) == iters + 1
+    x0 = np.ones_like(b)
+    iters0, _, _ = pcg(A, preconditioner="none")(np.zeros_like(b), x0, 1e-6, 0)
+    assert iters0 == 0 and not x0.any()
+    with pytest.raises(ValueError):
+        pcg(A, device="cpu")
+    with pytest.raises(ValueError):
+        pcg(A, preconditioner="ic")
+
+
+def test_pcg_large_poisson_property():
+    """Full-size-style property: residual really is below rtol*||b|| and both drivers agree."""
+    d = _dev()
+    from learningsparsepreconditioner4gpu_b200 import datagen as dg
+
+    s = dg.poisson3d(48, jitter=0.2, seed=3, device="cuda")
+    vals = (s.values / s.values.abs().mean()).to(torch.float32)
+    mask = torch.ones(s.num_nodes, 1, device="cuda")
+    mask[:200] = 0
+    A = d.DeviceCSR.from_edges(s.edge_index, vals, s.num_nodes, mask)
+    b = A.matvec(mask.reshape(-1).double())
+    its = []
+    for mode in (1, 2):
+        solver = d.DevicePCG(A, mode=mode)
+        x, res, hist = solver.solve(b, "diagonal", rtol=1e-8, history=True)
+        r = b - A.matvec(x)
+        assert res.converged == 1 and float(r.norm() / b.norm()) < 2e-8
+        assert hist.shape[0] == res.iterations + 1
+        its.append(res.iterations)
+    assert its[0] == its[1]
