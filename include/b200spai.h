@@ -128,6 +128,12 @@ int b200spai_pcg_solve_host(b200spai_pcg_t s, int precond, const double* b_host,
                             int32_t max_iter, double* resid_hist_host, void* stream, b200spai_pcg_result* result);
 /* z = M r for the attached preconditioner (test hook for the operator of validate.py:182). */
 int b200spai_pcg_apply_precond(b200spai_pcg_t s, int precond, const double* r_dev, double* z_dev, void* stream);
+/* Measurement hook: run exactly `iterations` PCG updates from x0 = 0 (no convergence test) as individually
+ * enqueued kernels with a CUDA event between them, and return the mean device time per kernel class:
+ * kernel_ms5 = {t = G^T r, z = G t + eps r (+ r.z), p update, q = A p (+ p.q), x/r update (+ r.r)}
+ * (for none/diagonal slot 0 is 0 and slot 1 is the Jacobi kernel).  Used by bench.py's roofline. */
+int b200spai_pcg_profile_iterations(b200spai_pcg_t s, int precond, const double* b_dev, double* x_dev,
+                                    int32_t iterations, float* kernel_ms5, void* stream);
 /* Kernel-launch counter since creation (for bench.py's gpu_launches). */
 int b200spai_pcg_launch_count(b200spai_pcg_t s, int64_t* launches);
 int b200spai_pcg_destroy(b200spai_pcg_t s);
@@ -153,6 +159,11 @@ int b200spai_gnn_destroy(b200spai_gnn_t m);
 int b200spai_gnn_forward(b200spai_gnn_t m, b200spai_graph_t g, const float* x_dev, const float* edge_attr_dev,
                          float* g_out_dev, float* node_out_dev, void* stream);
 int b200spai_gnn_launch_count(b200spai_gnn_t m, int64_t* launches);
+/* GraphSpmv (neural_cg/nn/basic_layers.py:112-142), the fp32 edge-list operator AATPE (:228-261) is built
+ * from: y[N,b] = mask * (A x) with values [E,b,b] in the caller's edge order; transpose != 0 applies A^T
+ * (aggregation at edge_index[1]).  Deterministic: per target, edges are summed in ascending edge order. */
+int b200spai_graph_spmv_f32(b200spai_graph_t g, int32_t block_size, const float* values_dev, const float* x_dev,
+                            const float* mask_dev, int32_t transpose, float* y_dev, void* stream);
 
 #ifdef __cplusplus
 }

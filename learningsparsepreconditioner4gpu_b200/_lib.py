@@ -41,6 +41,7 @@ SIGNATURES = {
     "b200spai_pcg_solve_dev": [c_vp, C.c_int, c_vp, c_vp, c_f64, c_i32, c_vp, c_vp, C.POINTER(PcgResult)],
     "b200spai_pcg_solve_host": [c_vp, C.c_int, c_vp, c_vp, c_f64, c_i32, c_vp, c_vp, C.POINTER(PcgResult)],
     "b200spai_pcg_apply_precond": [c_vp, C.c_int, c_vp, c_vp, c_vp],
+    "b200spai_pcg_profile_iterations": [c_vp, C.c_int, c_vp, c_vp, c_i32, C.POINTER(C.c_float), c_vp],
     "b200spai_pcg_launch_count": [c_vp, C.POINTER(c_i64)],
     "b200spai_pcg_destroy": [c_vp],
     "b200spai_graph_create": [c_i64, c_i64, c_vp, c_vp, C.POINTER(c_vp)],
@@ -49,6 +50,7 @@ SIGNATURES = {
     "b200spai_gnn_destroy": [c_vp],
     "b200spai_gnn_forward": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp],
     "b200spai_gnn_launch_count": [c_vp, C.POINTER(c_i64)],
+    "b200spai_graph_spmv_f32": [c_vp, c_i32, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp],
 }
 
 _lib = None

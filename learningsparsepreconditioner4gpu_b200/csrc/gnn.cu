@@ -42,6 +42,9 @@ constexpr int LAYER_FLOATS = 2 * MLP48 + MLP16;      // msg, edge, node
 struct b200spai_graph_s {
   long long N = 0, E = 0;
   int *perm = nullptr, *src = nullptr, *dst = nullptr, *segptr = nullptr;
+  // row-sorted view (GraphSpmv without transpose aggregates at edge_index[0]): position p is original edge
+  // rperm[p], its column is rcol[p]; rows own rsegptr[i]..rsegptr[i+1]
+  int *rperm = nullptr, *rcol = nullptr, *rsegptr = nullptr;
   int4* nb = nullptr;
   int nnb = 0;
   float *ef = nullptr, *x0 = nullptr, *x1 = nullptr;
@@ -95,6 +98,9 @@ static void graph_free(b200spai_graph_s* g) {
   cudaFree(g->src);
   cudaFree(g->dst);
   cudaFree(g->segptr);
+  cudaFree(g->rperm);
+  cudaFree(g->rcol);
+  cudaFree(g->rsegptr);
   cudaFree(g->nb);
   cudaFree(g->ef);
   cudaFree(g->x0);
@@ -112,6 +118,9 @@ static int graph_create_impl(long long N, long long E, const long long* edge_ind
   if (!rc) rc = dev_alloc(&g->src, (size_t)E);
   if (!rc) rc = dev_alloc(&g->dst, (size_t)E);
   if (!rc) rc = dev_alloc(&g->segptr, (size_t)N + 1);
+  if (!rc) rc = dev_alloc(&g->rperm, (size_t)E);
+  if (!rc) rc = dev_alloc(&g->rcol, (size_t)E);
+  if (!rc) rc = dev_alloc(&g->rsegptr, (size_t)N + 1);
   if (!rc) rc = dev_alloc(&g->ef, (size_t)Epad * F);
   if (!rc) rc = dev_alloc(&g->x0, (size_t)N * F);
   if (!rc) rc = dev_alloc(&g->x1, (size_t)N * F);
@@ -146,6 +155,19 @@ static int graph_create_impl(long long N, long long E, const long long* edge_ind
     if (e == cudaSuccess) e = cudaMalloc(&tmp, tmp_bytes + 16);
     if (e == cudaSuccess) e = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, g->dst, iota, g->perm, (int)E, 0, end_bit, st);
     if (e == cudaSuccess) graph_src_kernel<<<(unsigned)((E + tb - 1) / tb), tb, 0, st>>>(row, g->perm, E, g->src);
+    // the same, keyed on the row (identity permutation for the reference's row-major edge lists)
+    if (e == cudaSuccess) {
+      graph_keys_kernel<<<(unsigned)((E + tb - 1) / tb), tb, 0, st>>>(col, row, E, N, keys, iota, bad);
+      e = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, g->src /*scratch*/, iota, g->rperm, (int)E, 0, end_bit, st);
+    }
+    if (e == cudaSuccess) {
+      // g->src was used as scratch for the sorted row keys: segment offsets first, then restore it
+      graph_segptr_kernel<<<(unsigned)((N + 1 + tb - 1) / tb), tb, 0, st>>>(g->src, E, N, g->rsegptr);
+      graph_src_kernel<<<(unsigned)((E + tb - 1) / tb), tb, 0, st>>>(col, g->rperm, E, g->rcol);
+      graph_src_kernel<<<(unsigned)((E + tb - 1) / tb), tb, 0, st>>>(row, g->perm, E, g->src);
+    }
+  } else {
+    cudaMemsetAsync(g->rsegptr, 0, ((size_t)N + 1) * sizeof(int), st);
   }
   if (e == cudaSuccess) {
     graph_segptr_kernel<<<(unsigned)((N + 1 + tb - 1) / tb), tb, 0, st>>>(g->dst, E, N, g->segptr);
@@ -287,6 +309,24 @@ int b200spai_gnn_forward(b200spai_gnn_t m, b200spai_graph_t g, const float* x_de
   B2_LAUNCH_CHECK();
   if (node_out_dev) B2_CUDA(cudaMemcpyAsync(node_out_dev, xin, (size_t)N * F * sizeof(float), cudaMemcpyDeviceToDevice, st));
   m->launches += 2 + m->L;
+  return 0;
+}
+
+int b200spai_graph_spmv_f32(b200spai_graph_t g, int32_t block_size, const float* values_dev, const float* x_dev,
+                            const float* mask_dev, int32_t transpose, float* y_dev, void* stream) {
+  B2_ARG(g && x_dev && y_dev && (values_dev || g->E == 0), "graph_spmv_f32: NULL argument");
+  B2_ARG(block_size >= 1 && block_size <= 4, "graph_spmv_f32: block_size must be in [1,4]");
+  const long long rows = g->N * block_size;
+  if (rows == 0) return 0;
+  const int tb = 256;
+  const unsigned grid = (unsigned)((rows + tb - 1) / tb);
+  if (transpose)
+    graph_spmv_f32_kernel<true><<<grid, tb, 0, as_stream(stream)>>>(g->segptr, g->perm, g->src, g->N, block_size, values_dev,
+                                                                    x_dev, mask_dev, y_dev);
+  else
+    graph_spmv_f32_kernel<false><<<grid, tb, 0, as_stream(stream)>>>(g->rsegptr, g->rperm, g->rcol, g->N, block_size,
+                                                                     values_dev, x_dev, mask_dev, y_dev);
+  B2_LAUNCH_CHECK();
   return 0;
 }
 

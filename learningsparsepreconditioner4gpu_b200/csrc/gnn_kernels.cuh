@@ -269,4 +269,28 @@ __global__ void __launch_bounds__(256, 2) gnn_dec_kernel(const int* __restrict__
   }
 }
 
+// ---- GraphSpmv (neural_cg/nn/basic_layers.py:112-142) ----------------------------------------------
+// y[t] = mask[t] * sum over the edges aggregated at target t of  A_e x[other]   (TRANSPOSE: A_e^T x[other]).
+// One thread per scalar row (t, i); edges of a target are visited in ascending original order, i.e. the
+// order in which the reference's CPU scatter_add_ accumulates them.  fp32 like the reference operator.
+template <bool TRANSPOSE>
+__global__ void __launch_bounds__(256) graph_spmv_f32_kernel(const int* __restrict__ segptr, const int* __restrict__ perm,
+                                                             const int* __restrict__ other, long long N, int b,
+                                                             const float* __restrict__ vals, const float* __restrict__ x,
+                                                             const float* __restrict__ mask, float* __restrict__ y) {
+  const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= N * b) return;
+  const long long t = row / b;
+  const int i = (int)(row - t * b);
+  float acc = 0.0f;
+  for (int p = segptr[t]; p < segptr[t + 1]; ++p) {
+    const float* blk = vals + (long long)perm[p] * b * b;
+    const float* xo = x + (long long)other[p] * b;
+    float r = 0.0f;
+    for (int j = 0; j < b; ++j) r = __fadd_rn(r, __fmul_rn(TRANSPOSE ? blk[j * b + i] : blk[i * b + j], xo[j]));
+    acc = __fadd_rn(acc, r);
+  }
+  y[row] = mask ? acc * mask[row] : acc;
+}
+
 }  // namespace b200spai

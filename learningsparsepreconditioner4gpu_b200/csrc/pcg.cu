@@ -15,6 +15,8 @@
 //   mode 2 (graph):  one CUDA graph = init kernel + a WHILE conditional node whose body is the 5
 //           kernels; K5's last CTA sets the loop condition (cudaGraphSetConditional).  One launch
 //           per solve, no host involvement until the result is read.
+#include <vector>
+
 #include "csr.h"
 
 using namespace b200spai;
@@ -467,6 +469,76 @@ int b200spai_pcg_apply_precond(b200spai_pcg_t s, int precond, const double* r, d
   int nl = 0;
   B2_TRY(enqueue_precond(s, precond, r, z, nullptr, st, &nl));
   s->launches += nl;
+  return 0;
+}
+
+int b200spai_pcg_profile_iterations(b200spai_pcg_t s, int precond, const double* b, double* x, int32_t iterations,
+                                    float* kernel_ms5, void* stream) {
+  B2_ARG(s && b && x && kernel_ms5 && iterations > 0, "pcg_profile_iterations: bad argument");
+  B2_ARG(precond >= 0 && precond <= 3, "pcg_profile_iterations: unknown preconditioner");
+  if (precond >= B200SPAI_PRECOND_EXT_SPAI) B2_ARG(s->G && s->GT, "pcg_profile_iterations: set_spai first");
+  cudaStream_t st = as_stream(stream);
+  if (precond == B200SPAI_PRECOND_DIAGONAL || precond == B200SPAI_PRECOND_EXT_SPAI_SCALED) B2_TRY(ensure_diag(s, st));
+  B2_TRY(ensure_hist(s, (long long)iterations + 1));
+  const bool spai = precond >= B200SPAI_PRECOND_EXT_SPAI;
+  PcgScalars init{};
+  init.rtol = 0.0;  // never converges: exactly `iterations` updates are timed
+  init.max_iter = iterations;
+  *s->h_in = init;
+  B2_CUDA(cudaMemcpyAsync(s->sc, s->h_in, sizeof(PcgScalars), cudaMemcpyHostToDevice, st));
+  pcg_init_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(b, x, s->r, s->n, s->sc, s->partials, s->ticket, s->hist);
+  B2_LAUNCH_CHECK();
+  // one warm-up iteration builds the lazily created row partitions outside the timed events
+  {
+    int nl = 0;
+    B2_TRY(enqueue_iteration(s, precond, x, st, &nl));
+    *s->h_in = init;
+    B2_CUDA(cudaMemcpyAsync(s->sc, s->h_in, sizeof(PcgScalars), cudaMemcpyHostToDevice, st));
+    pcg_init_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(b, x, s->r, s->n, s->sc, s->partials, s->ticket, s->hist);
+  }
+  const int per = 6;  // event before each of the 5 kernels + one after the last
+  std::vector<cudaEvent_t> ev((size_t)iterations * per);
+  for (auto& e : ev) B2_CUDA(cudaEventCreate(&e));
+  for (int it = 0; it < iterations; ++it) {
+    cudaEvent_t* e = ev.data() + (size_t)it * per;
+    int nl = 0;
+    B2_CUDA(cudaEventRecord(e[0], st));
+    if (spai) {
+      const bool scaled = (precond == B200SPAI_PRECOND_EXT_SPAI_SCALED);
+      SpmvArgs a1{};
+      a1.x = s->r; a1.y = s->t; a1.d = scaled ? s->d : nullptr; a1.sc = s->sc;
+      B2_TRY(spmv_launch(s->GT, a1, scaled ? SPMV_SCALE : SPMV_PLAIN, 0, st));
+      B2_CUDA(cudaEventRecord(e[1], st));
+      SpmvArgs a2{};
+      a2.x = s->t; a2.y = s->z; a2.aux = s->r; a2.d = scaled ? s->d : nullptr; a2.eps = s->eps;
+      a2.partials = s->partials; a2.ticket = s->ticket; a2.sc = s->sc; a2.final_op = FINAL_RHO;
+      B2_TRY(spmv_launch(s->G, a2, SPMV_AXPY_DOT, 0, st));
+    } else {
+      B2_CUDA(cudaEventRecord(e[1], st));
+      B2_TRY(enqueue_precond(s, precond, s->r, s->z, s->sc, st, &nl));
+    }
+    B2_CUDA(cudaEventRecord(e[2], st));
+    pcg_update_p_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(s->z, s->p, s->n, s->sc);
+    B2_CUDA(cudaEventRecord(e[3], st));
+    SpmvArgs a{};
+    a.x = s->p; a.y = s->q; a.partials = s->partials; a.ticket = s->ticket; a.sc = s->sc; a.final_op = FINAL_PQ;
+    B2_TRY(spmv_launch(s->A, a, SPMV_DOT, 0, st));
+    B2_CUDA(cudaEventRecord(e[4], st));
+    pcg_update_xr_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(x, s->r, s->p, s->q, s->n, s->sc, s->partials, s->ticket,
+                                                              s->hist);
+    B2_CUDA(cudaEventRecord(e[5], st));
+  }
+  B2_LAUNCH_CHECK();
+  B2_CUDA(cudaStreamSynchronize(st));
+  for (int k = 0; k < 5; ++k) kernel_ms5[k] = 0.f;
+  for (int it = 0; it < iterations; ++it)
+    for (int k = 0; k < 5; ++k) {
+      float ms = 0.f;
+      B2_CUDA(cudaEventElapsedTime(&ms, ev[(size_t)it * per + k], ev[(size_t)it * per + k + 1]));
+      kernel_ms5[k] += ms / iterations;
+    }
+  for (auto& e : ev) cudaEventDestroy(e);
+  s->launches += (long long)iterations * (spai ? 5 : 4);
   return 0;
 }
 

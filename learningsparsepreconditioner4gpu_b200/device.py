@@ -186,6 +186,14 @@ class DevicePCG:
                    "pcg_apply_precond")
         return z
 
+    def profile_iterations(self, b: torch.Tensor, precond: str = "ext_spai", iterations: int = 20):
+        """Mean device ms per kernel class over `iterations` updates: [G^T r, G t (+rho), p, A p (+pq), x/r (+rr)]."""
+        x = torch.empty_like(b)
+        ms = (C.c_float * 5)()
+        _lib.check(self._lib.b200spai_pcg_profile_iterations(self._h, PRECOND[precond], _ptr(b.contiguous()), _ptr(x),
+                                                             int(iterations), ms, _stream()), "pcg_profile_iterations")
+        return [float(v) for v in ms]
+
     @property
     def launches(self) -> int:
         v = C.c_int64()

@@ -1,0 +1,187 @@
+"""Host-side mirror of ``neural_cg/workspace.py``: ``SimpleTrainingWorkspace`` with the reference's
+constructor signature (:27-50), attributes (``gnn``, ``epsilon``, ``block_size``, ``spai_preconditioner``)
+and inference methods (``forward`` :92-94, ``inference_step`` :195-205, ``precondition`` :207-211,
+``log_converge_batch`` :114-143, ``log_converge_v2`` :145-166).
+
+Differences, all forced by the environment or the scope:
+* a plain ``nn.Module`` (Lightning is absent): ``log`` / ``log_dict`` collect into ``self.logged``,
+  ``save_hyperparameters`` fills ``self.hparams``; checkpoints are plain ``state_dict``s with the reference's keys;
+* the GNN forward, CSR assembly and PCG run in libb200spai.so; convergence checks always solve on "cuda"
+  (a "cpu" entry in ``check_devices`` is mapped to "cuda" with a warning) with the methods the library has;
+* training (``training_step``, losses, optimisers) is out of scope: the ``loss`` / ``optimizer`` /
+  ``scheduler`` configs are accepted and stored so that the reference's YAML splats in unchanged;
+* additions: ``inference_step_device`` (G stays in HBM) and ``solve`` (GNN -> G -> PCG, end to end on the device).
+"""
+from __future__ import annotations
+
+import warnings
+from time import time
+from typing import Any, Dict, List, Optional, Union
+
+import numpy as np
+import torch
+from scipy.sparse import csr_matrix
+from torch import nn
+
+from ..device import DeviceCSR, DevicePCG
+from .nn.basic_layers import AATPE
+from .nn.gnns import NodeEdgeProcessing
+from .utils.validate import get_cg_iter_time, get_pcg_iter_time, to_csr_cpu, to_csr_device, to_numpy
+
+
+def _cfg_get(cfg, key, default=None):
+    if cfg is None:
+        return default
+    if isinstance(cfg, dict):
+        return cfg.get(key, default)
+    return getattr(cfg, key, default)
+
+
+class _WorkspaceBase(nn.Module):
+    """What the two workspaces share: construction, logging stand-ins, the per-sample convergence probe."""
+
+    def __init__(self, batch_size: int, batch_less: bool, block_size: int, test_max_iter: int, optimizer, scheduler, loss,
+                 inspect_norms: bool, check_converge: bool, check_methods: List[str], check_devices: List[str],
+                 node_features: int, edge_features: int, gnn, epsilon: float, *args, **kwargs):
+        super().__init__()
+        self.hparams: Dict[str, Any] = dict(
+            batch_size=batch_size, batch_less=batch_less, block_size=block_size, test_max_iter=test_max_iter,
+            optimizer=optimizer, scheduler=scheduler, loss=loss, inspect_norms=inspect_norms, check_converge=check_converge,
+            check_methods=check_methods, check_devices=check_devices, node_features=node_features,
+            edge_features=edge_features, gnn=gnn, epsilon=epsilon, **kwargs)
+        self.block_size = block_size
+        self.optimizer_cfg = optimizer
+        self.scheduler_cfg = scheduler
+        self.epsilon = epsilon
+        self.test_max_iter = test_max_iter
+        self.loss_name = _cfg_get(loss, "name")
+        self.gnn = NodeEdgeProcessing(node_in_features=node_features, node_out_features=None,
+                                      edge_in_features=edge_features, edge_out_features=block_size * block_size,
+                                      **dict(gnn))
+        self.enable_inspect_norms = inspect_norms
+        self.spai_preconditioner = AATPE(self.epsilon)
+        self.check_converge = check_converge
+        self.check_methods: List[str] = list(check_methods or [])
+        self.check_devices: List[str] = list(check_devices or [])
+        self.has_pymathprim = False  # the solver is libb200spai; kept for callers that inspect it
+        self.logged: Dict[str, Any] = {}
+
+    # ---- Lightning stand-ins -----------------------------------------------------------------------------
+    def log(self, name: str, value, **kwargs) -> None:
+        self.logged[name] = float(value)
+
+    def log_dict(self, values: Dict[str, Any], **kwargs) -> None:
+        for k, v in values.items():
+            self.log(k, v)
+
+    def training_step(self, batch, batch_idx: int):
+        raise NotImplementedError("training is outside the B200 solve path (SURVEY.md §8f rank 4); "
+                                  "train with the reference and load the state_dict here")
+
+    # ---- the model -----------------------------------------------------------------------------------------
+    def forward(self, node_attr, edge_index, edge_attr):
+        _, boo_entry = self.gnn(node_attr, edge_index, edge_attr)
+        return boo_entry.reshape(-1, self.block_size, self.block_size)  # [nE, b, b]
+
+    def _devices(self) -> List[str]:
+        out = []
+        for d in self.check_devices:
+            if d != "cuda":
+                warnings.warn(f"check_devices entry {d!r} is solved on 'cuda': this build has no CPU solver", stacklevel=3)
+            if "cuda" not in out:
+                out.append("cuda")
+        return out
+
+    def _pcg(self, A, r, L, device, repeat):
+        return get_pcg_iter_time(A, r, L, self.epsilon, device=device, repeat=repeat)
+
+    def log_converge_v2(self, L, A, r, repeat, prefix: str):
+        stats: Dict[str, float] = {}
+        for device in self._devices():
+            for method in self.check_methods:
+                if method not in ("none", "diagonal"):
+                    continue  # ic / ainv / fsai: reference comparison baselines (pymathprim), not in this path
+                avg_iter, _, avg_solve = get_cg_iter_time(A, r, repeat=repeat, method=method, device=device)
+                stats[f"{prefix}/{device}_{method}_iter"] = stats.get(f"{prefix}/{device}_{method}_iter", 0) + avg_iter
+                stats[f"{prefix}/{device}_{method}_solve"] = stats.get(f"{prefix}/{device}_{method}_solve", 0) + avg_solve
+            avg_iter, _, avg_solve = self._pcg(A, r, L, device, repeat)
+            stats[f"{prefix}/{device}_neural_iter"] = avg_iter
+            stats[f"{prefix}/{device}_neural_solve"] = avg_solve
+        self.log_dict(stats, batch_size=1)
+        return stats
+
+    def _export_factor(self, L: csr_matrix, batch) -> csr_matrix:
+        return L
+
+    def log_converge_batch(self, boo_entry: torch.Tensor, batch, prefix: str, repeat=1):
+        """Split the block-diagonal batch by ``ptr`` and solve every sample on its own (workspace.py:137-143)."""
+        if not self.check_converge:
+            return None
+        ptr = batch.ptr.detach().cpu().numpy().tolist()
+        n = ptr[-1] * self.block_size
+        L = self._export_factor(to_csr_cpu(batch.edge_index, boo_entry, n, batch.mask, dtype=np.float64), batch)
+        A = to_csr_cpu(batch.edge_index, batch.matrix_values, n, batch.mask, dtype=np.float64)
+        r = to_numpy(batch.mask).flatten().astype(np.float64, copy=True)
+        all_stats = []
+        for b, e in zip(ptr[:-1], ptr[1:]):
+            b, e = b * self.block_size, e * self.block_size
+            all_stats.append(self.log_converge_v2(csr_matrix(L[b:e, b:e]), csr_matrix(A[b:e, b:e]), r[b:e], repeat, prefix))
+        return all_stats
+
+    def _log_norms(self, boo_entry: torch.Tensor, bsize: int, prefix: str):
+        if self.enable_inspect_norms:
+            self.log(f"{prefix}/boo_entry_norm", torch.linalg.norm(boo_entry), batch_size=1)
+
+    # ---- device-resident additions ---------------------------------------------------------------------------
+    @torch.no_grad()
+    def inference_step_device(self, sample) -> DeviceCSR:
+        """G as a DeviceCSR without leaving HBM (GNN forward + device assembly)."""
+        boo_entry = self(sample.x, sample.edge_index, sample.edge_attr)
+        n = sample.x.shape[0] * self.block_size
+        return to_csr_device(sample.edge_index, boo_entry, n, sample.mask)
+
+    @torch.no_grad()
+    def solve(self, sample, rhs: Optional[torch.Tensor] = None, rtol: float = 1e-6, max_iter: int = 0,
+              preconditioner: str = "ext_spai", history: bool = False):
+        """GNN -> G -> PCG on the device.  ``rhs`` defaults to the reference's rhs="mask" convention
+        (b = A @ mask, infer.py:297-299).  Returns (x, PcgResult, history, A, G)."""
+        n = sample.x.shape[0] * self.block_size
+        A = to_csr_device(sample.edge_index, sample.matrix_values, n, sample.mask)
+        G = self.inference_step_device(sample)
+        if rhs is None:
+            rhs = A.matvec(sample.mask.reshape(-1).to(torch.float64))
+        solver = DevicePCG(A)
+        solver.set_spai(G, self.epsilon)
+        x, res, hist = solver.solve(rhs.to(torch.float64).reshape(-1), preconditioner, rtol=rtol, max_iter=max_iter,
+                                    history=history)
+        return x, res, hist, A, G
+
+
+class SimpleTrainingWorkspace(_WorkspaceBase):
+    @torch.no_grad()
+    def inference_step(self, sample, time_beg: Union[float, None] = None):
+        time_beg = time()
+        boo_entry = self(sample.x, sample.edge_index, sample.edge_attr).cpu().detach().numpy()
+        dt = time() - time_beg  # the preconditioner-construction time, including the D2H copy (workspace.py:200-202)
+        n = sample.x.shape[0] * self.block_size
+        csr = to_csr_cpu(sample.edge_index, boo_entry, n, sample.mask, dtype=np.float64)
+        return csr, dt
+
+    def precondition(self, sample, Adense) -> np.ndarray:
+        L, _ = self.inference_step(sample)
+        M = L @ L.T
+        return M.todense() + self.epsilon * np.eye(M.shape[0], dtype=np.float64)
+
+    def validation_step(self, batch, batch_idx: int):
+        boo_entry = self(batch.x, batch.edge_index, batch.edge_attr)
+        self._log_norms(boo_entry, int(batch.ptr.shape[0]) - 1, "Val")
+        if batch_idx == 0:
+            self.log_converge_batch(boo_entry, batch, "Val", 1)
+        return boo_entry
+
+    def test_step(self, batch, batch_idx: int):
+        boo_entry = self(batch.x, batch.edge_index, batch.edge_attr)
+        self.log_converge_batch(boo_entry, batch, "Test", 3)
+        _, dt = self.inference_step(batch)
+        self.log("Test/time_neural_prec", dt, batch_size=1)
+        return boo_entry
