@@ -1,0 +1,443 @@
+#!/usr/bin/env python
+"""bench.py -- the learned-SPAI solve path on B200: GNN -> G -> CSR assembly -> PCG to rtol 1e-6.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--grid 216] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+
+Workload (BASELINE.json north_star target / config C5 sized for ONE GPU): a 3-D Poisson system on a jittered
+Kuhn-tet grid of grid^3 nodes (216^3 = 10.08 M DOF, ~15 stored entries per row), Dirichlet patch, random-init
+GNN weights (seed 42), rhs b = A * mask, x0 = 0, rtol 1e-6, fp64 solve.  One STEP = one system through the whole
+path: topology preprocessing, GNN forward (G values), assembly of A and G into masked fp64 CSR, G^T, PCG.
+With N GPUs every rank solves its own independent system of the same shape (weak scaling, no data-path
+collective -- the reference treats batch members as independent systems, workspace.py:137-143).
+
+One JSON line on stdout (rank 0):  value = solves/s with the inputs resident in HBM; e2e = the same through
+``workspace.solve`` with the sample in pinned HOST memory (H2D of every input, D2H of x inside the timed region);
+roofline = the PCG SpMV kernel family against MEASURED_PEAKS.json; cpu_baseline = the CPU oracle (scipy PCG +
+torch GNN restatement of the reference) timed on a bounded sample on this box.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+METRIC = "learned-SPAI PCG solves/s to rtol 1e-6 (GNN->G, assembly, PCG; time-to-1e-6 in extra keys)"
+UNIT = "solves/s"
+# PCG iterations of the default workload at rtol 1e-6, measured by the CUDA path (iteration parity with the oracle
+# is +-1 on every size the oracle can solve, tests/test_pcg_gpu.py).  Used ONLY by --impl reference to scale its
+# per-iteration CPU time to a whole solve without running ~10^3 s of scipy; override with B200SPAI_REF_ITERS.
+DEFAULT_ITERS = {216: 560}
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# helpers
+# ---------------------------------------------------------------------------------------------------------
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                f = [t.strip() for t in line.split(",")]
+                if len(f) < 7:
+                    continue
+                try:
+                    sm.append(float(f[0]))
+                    mx.append(float(f[1]))
+                except ValueError:
+                    continue
+                for nm, v in zip(names, f[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def tensor_bytes(*ts) -> int:
+    return int(sum(t.numel() * t.element_size() for t in ts if isinstance(t, torch.Tensor)))
+
+
+INPUT_FIELDS = ("x", "edge_index", "edge_attr", "mask", "matrix_values")
+
+
+# ---------------------------------------------------------------------------------------------------------
+# the CUDA arm
+# ---------------------------------------------------------------------------------------------------------
+def run_step(ws, sample, rtol, timers=None):
+    """One system through the whole path on the current device.  ``sample`` tensors are already on the GPU."""
+    from learningsparsepreconditioner4gpu_b200.device import DevicePCG
+    from learningsparsepreconditioner4gpu_b200.neural_cg.nn.gnns import DeviceGraph
+    from learningsparsepreconditioner4gpu_b200.neural_cg.utils.validate import to_csr_device
+
+    def mark(name):
+        if timers is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            timers.append((name, ev))
+
+    n = sample.x.shape[0] * ws.block_size
+    mark("start")
+    graph = DeviceGraph(sample.edge_index, sample.x.shape[0])           # target-sorted edges, segment offsets
+    mark("graph")
+    _, g_vals = ws.gnn(sample.x, sample.edge_index, sample.edge_attr, graph=graph)   # G values, fp32 [E, b*b]
+    g_vals = g_vals.reshape(-1, ws.block_size, ws.block_size)
+    mark("gnn")
+    A = to_csr_device(sample.edge_index, sample.matrix_values, n, sample.mask)       # masked fp64 CSR
+    G = to_csr_device(sample.edge_index, g_vals, n, sample.mask)
+    rhs = A.matvec(sample.mask.reshape(-1).to(torch.float64))                         # b = A @ mask (infer.py:297)
+    mark("assemble")
+    solver = DevicePCG(A)
+    solver.set_spai(G, ws.epsilon)                                                    # G^T on the device
+    mark("transpose")
+    x, res, _ = solver.solve(rhs, "ext_spai", rtol=rtol)
+    mark("pcg")
+    graph.close()
+    return x, res, solver, A, G, rhs
+
+
+def phases_ms(timers):
+    torch.cuda.synchronize()
+    out = {}
+    for (_, e0), (name, e1) in zip(timers[:-1], timers[1:]):
+        out[name] = out.get(name, 0.0) + e0.elapsed_time(e1)
+    return out
+
+
+def main_ours(args):
+    from learningsparsepreconditioner4gpu_b200 import _lib, systems
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    _lib.require_cuda()
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n_gpus = world
+    if args.gpus and args.gpus != world and rank == 0:
+        log(f"[bench] --gpus {args.gpus} but WORLD_SIZE={world}: running on {world} rank(s)")
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v: float) -> float:
+        if dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(v: float) -> float:
+        if dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    g = args.grid
+    t0 = time.time()
+    sample = systems.poisson_sample(g, seed=100 + rank, gen_device="cuda", device="cuda")
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    N, E = sample.num_nodes, sample.num_edges
+    ws = systems.default_workspace(sample)
+    host = sample.to("cpu").pin_memory()                      # the e2e arm starts from pinned host memory
+    log(f"[bench r{rank}] system {g}^3: N={N} E={E} generated in {time.time() - t0:.1f}s")
+    h2d = tensor_bytes(*[getattr(host, k) for k in INPUT_FIELDS])
+    d2h = N * ws.block_size * 8
+
+    # ---- warm-up (also builds the lazily created pieces: weight blob, occupancy queries, graphs) ----------
+    for _ in range(max(args.warmup, 3)):
+        x, res, solver, A, G, rhs = run_step(ws, sample, args.rtol)
+        del solver, A, G, rhs
+    iters_warm = res.iterations
+    log(f"[bench r{rank}] warm-up done: {res.iterations} iterations, converged={res.converged}, pcg {res.solve_ms:.1f} ms")
+
+    # ---- timed region 1: inputs resident in HBM -------------------------------------------------------------
+    sampler = ClockSampler(local)
+    launches0 = _lib.total_launches()
+    timers = []
+    barrier()
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    pcg_ms, iters = [], []
+    for _ in range(args.steps):
+        x, res, solver, A, G, rhs = run_step(ws, sample, args.rtol, timers)
+        pcg_ms.append(float(res.solve_ms))
+        iters.append(int(res.iterations))
+        if _ < args.steps - 1:
+            del solver, A, G, rhs
+    ev1.record()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    launches = _lib.total_launches() - launches0
+    ph = phases_ms(timers)
+    converged = int(res.converged)
+    value = n_gpus * args.steps / (dev_ms * 1e-3)
+
+    # ---- per-kernel times of the PCG iteration (roofline), on the last step's matrices ----------------------
+    kms = solver.profile_iterations(rhs, "ext_spai", iterations=20)
+    nnzA, nnzG, n = A.nnz, G.nnz, N * ws.block_size
+    bytes_k = {
+        "GT_r (t = G^T r)": 12 * nnzG + 20 * n + 4,
+        "G_t (z = G t + eps r; r.z)": 12 * nnzG + 28 * n + 4,
+        "update_p": 24 * n,
+        "A_p (q = A p; p.q)": 12 * nnzA + 20 * n + 4,
+        "update_xr (x, r; r.r)": 48 * n,
+    }
+    peak, peak_src = peaks()
+    detail = {}
+    for (name, by), ms in zip(bytes_k.items(), kms):
+        detail[name] = {"ms": round(ms, 4), "bytes": by, "GB/s": round(by / (ms * 1e-3) / 1e9, 1) if ms > 0 else None}
+    spmv_bytes = sum(by for k, by in bytes_k.items() if "update" not in k)
+    spmv_ms = kms[0] + kms[1] + kms[3]
+    achieved = spmv_bytes / 3 / (spmv_ms / 3 * 1e-3) / 1e9
+    iter_bytes = sum(bytes_k.values())
+    iter_ms = sum(kms)
+    roofline = {
+        "kernel": "spmv_stream_kernel<2048,3,*> (3 launches per PCG iteration: t=G^T r, z=G t+eps r, q=A p)",
+        "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+        "peak_source": peak_src, "traffic": None,
+        "bytes_per_launch": spmv_bytes // 3, "ms_per_launch": round(spmv_ms / 3, 4),
+        "pcg_iteration": {"ms": round(iter_ms, 4), "bytes": iter_bytes, "GB/s": round(iter_bytes / (iter_ms * 1e-3) / 1e9, 1),
+                          "frac": round(iter_bytes / (iter_ms * 1e-3) / 1e9 / peak, 4)},
+        "per_kernel": detail,
+    }
+    del solver, A, G, rhs
+    torch.cuda.empty_cache()
+
+    # ---- timed region 2: end to end from pinned host memory -------------------------------------------------
+    x_host = torch.empty(N * ws.block_size, dtype=torch.float64).pin_memory()
+
+    def e2e_step():
+        dev = host.to("cuda", non_blocking=True)              # H2D of x, edge_index, edge_attr, mask, matrix_values
+        xs, r, sv, A_, G_, b_ = run_step(ws, dev, args.rtol)
+        x_host.copy_(xs, non_blocking=True)                    # D2H of the solution
+        torch.cuda.current_stream().synchronize()
+        return r
+
+    e2e_step()
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        r2 = e2e_step()
+    ev1.record()
+    barrier()
+    e2e_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    e2e_value = n_gpus * args.steps / (e2e_ms * 1e-3)
+
+    # ---- CPU oracle beside it (rank 0, N = 1 only) -----------------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            cpu = cpu_reference_sample(sample, ws, int(np.mean(iters)), args)
+        except Exception as exc:  # the baseline must never take the bench line down with it
+            cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "port", "sample": f"failed: {exc!r}"}
+
+    total_iters = sum_over_ranks(float(np.mean(iters))) / n_gpus
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": round(dev_ms / args.steps, 3), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64 (PCG) / f32 (GNN)", "data": "synthetic",
+            "config": {"workload": f"poisson3d jittered Kuhn-tet grid {g}^3 = {N} DOF per GPU, E = {E} stored entries, "
+                                   f"Dirichlet patch, random-init GNN (seed 42), eps 3e-3, rhs = A*mask, rtol {args.rtol:g}",
+                       "systems_per_step": n_gpus, "parallelism": f"{n_gpus} independent system(s), one per GPU",
+                       "l2": "inputs larger than L2 (A + G + G^T = %.1f GB)" % ((nnzA + 2 * nnzG) * 12 / 1e9)},
+            "time_to_tol_ms": round(float(np.mean(pcg_ms)), 3), "iterations": round(total_iters, 1), "converged": converged,
+            "ms_per_iteration": round(float(np.mean(pcg_ms)) / max(float(np.mean(iters)), 1.0), 4),
+            "phases_ms_per_step": {k: round(v / args.steps, 3) for k, v in ph.items()},
+            "e2e": {"value": round(e2e_value, 4), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": round(e2e_ms / args.steps, 3), "api": "SimpleTrainingWorkspace.solve path on a pinned-host sample"},
+            "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------------------
+# the CPU arm: the oracle (restated reference) on this box's host cores
+# ---------------------------------------------------------------------------------------------------------
+class CpuArm:
+    """Bounded CPU sample of one step of the same workload (the oracle = restated reference), scaled to the
+    metric's unit.
+
+    * GNN: the oracle forward (torch CPU, all threads) on a gnn_grid^3 system of the same family; the per-edge time
+      is scaled to the workload's E (the forward is O(E)).
+    * PCG: ``pcg_iters`` iterations of the oracle's scipy solve (validate.py:163-201: scipy cg, M = G G^T + eps I,
+      G^T materialised as CSR before the clock starts) on the FULL system; per-iteration time scaled to
+      ``iterations``.  scipy's csr_matvec is single-threaded.  G's values are a value-independent timing stand-in
+      on A's pattern (|G| ~ 0.1 like the random-init GNN's output; csr_matvec cost does not depend on values), so
+      nothing computed by the CUDA library enters this arm.
+    """
+
+    def __init__(self, sample_cpu, ws, rtol, gnn_grid):
+        from learningsparsepreconditioner4gpu_b200 import systems
+        from oracle import assemble as oasm
+        from oracle import pcg as opcg
+
+        self.threads = torch.get_num_threads()
+        self.rtol = rtol
+        self.small = systems.poisson_sample(gnn_grid, seed=7)
+        self.gnn_grid = gnn_grid
+        self.sd = {k: v.detach().cpu() for k, v in ws.state_dict().items()}
+        self.E = sample_cpu.num_edges
+        n = sample_cpu.num_nodes
+        A = oasm.to_csr_cpu_sorted(sample_cpu.edge_index, sample_cpu.matrix_values, n, sample_cpu.mask)
+        rng = np.random.default_rng(0)
+        g_vals = (0.1 + 0.002 * rng.standard_normal(self.E)).astype(np.float32)
+        G = oasm.to_csr_cpu_sorted(sample_cpu.edge_index, g_vals, n, sample_cpu.mask)
+        self.gt = sample_cpu.mask.numpy().reshape(-1).astype(np.float64)
+        self.timer = opcg.ScipyPcgTimer(A, G, ws.epsilon)
+
+    def step(self, iterations: int, pcg_iters: int):
+        from oracle import gnn as ognn
+
+        s = self.small
+        t0 = time.perf_counter()
+        ognn.workspace_forward(self.sd, s.x, s.edge_index, s.edge_attr, 1)
+        t_gnn_small = time.perf_counter() - t0
+        t_gnn = t_gnn_small * self.E / s.num_edges
+        done, t_pcg = self.timer.run(self.gt, self.rtol, pcg_iters)
+        t_iter = t_pcg / max(done, 1)
+        t_solve = t_iter * iterations
+        return {
+            "value": 1.0 / (t_gnn + t_solve), "unit": UNIT, "cores": self.threads, "kind": "port",
+            "sample": (f"oracle GNN forward on a {self.gnn_grid}^3 system ({s.num_edges} edges, {t_gnn_small:.2f} s, "
+                       f"{self.threads} torch threads) scaled by E to {t_gnn:.1f} s; oracle scipy PCG (1 thread) {done} iterations "
+                       f"on the full system = {t_iter:.3f} s/iteration x {iterations} iterations = {t_solve:.1f} s; extrapolated"),
+            "gnn_s": t_gnn, "pcg_s": t_solve, "s_per_iteration": t_iter, "iterations": iterations,
+        }
+
+
+def cpu_reference_sample(sample, ws, iterations: int, args):
+    arm = CpuArm(sample.to("cpu"), ws, args.rtol, gnn_grid=56)
+    arm.step(iterations, 1)  # warm-up (page in, torch thread pool)
+    return arm.step(iterations, 6)
+
+
+def main_reference(args):
+    """--impl reference: the reference's CPU path (oracle port; the reference itself needs torch_geometric,
+    lightning and pymathprim, none installable here) on this box's host cores, same workload and metric."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from learningsparsepreconditioner4gpu_b200 import systems
+
+    g = args.grid
+    iterations = int(os.environ.get("B200SPAI_REF_ITERS", DEFAULT_ITERS.get(g, 0)) or 0)
+    if iterations <= 0:
+        iterations = int(2.6 * g)  # CG on a 3-D Laplacian: iterations grow linearly with the grid edge
+    gen_device = "cuda" if torch.cuda.is_available() else "cpu"   # input generation only
+    sample = systems.poisson_sample(g, seed=100, gen_device=gen_device, device="cpu")
+    ws = systems.default_workspace(sample)
+    N, E = sample.num_nodes, sample.num_edges
+    arm = CpuArm(sample, ws, args.rtol, gnn_grid=40)
+    steps = max(args.steps, 1)
+    vals, last = [], None
+    t_begin = time.perf_counter()
+    for i in range(max(args.warmup, 0) + steps):
+        # every step is a bounded sample: a few PCG iterations on the full system + a small-grid GNN forward
+        last = arm.step(iterations, pcg_iters=3)
+        if i >= args.warmup:
+            vals.append(last["value"])
+        if time.perf_counter() - t_begin > 200 and vals:
+            break
+    value = float(np.mean(vals))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
+        "steps": len(vals), "warmup": args.warmup, "ms_per_step": 1e3 / value, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64 (PCG) / f32 (GNN)", "data": "synthetic",
+        "config": {"workload": f"poisson3d jittered Kuhn-tet grid {g}^3 = {N} DOF, E = {E} stored entries, Dirichlet patch, "
+                               f"random-init GNN (seed 42), eps 3e-3, rhs = A*mask, rtol {args.rtol:g}",
+                   "systems_per_step": 1, "parallelism": "CPU: torch threads for the GNN, 1 thread for scipy PCG"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": last["cores"], "kind": "port", "sample": last["sample"]},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--grid", type=int, default=216)
+    ap.add_argument("--rtol", type=float, default=1e-6)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        main_reference(args)
+    else:
+        main_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -46,6 +46,9 @@ const char* b200spai_last_error(void);
 int b200spai_version(void);
 /* Device query: name (<= 127 chars), SM count, compute capability major*10+minor. */
 int b200spai_device_info(char* name128, int* sm_count, int* cc);
+/* Process-wide count of this library's own kernel launches so far (bench.py's gpu_launches; cub sort/scan
+ * passes used in one-off setup steps are library kernels and are not counted). */
+int b200spai_total_launches(int64_t* launches);
 
 /* ------------------------------------------------------------------------------------------------
  * CSR matrices.  Stand in for the scipy.sparse.csr_matrix objects the reference hands to its solver

@@ -25,6 +25,7 @@ class PcgResult(C.Structure):
 SIGNATURES = {
     "b200spai_version": [],
     "b200spai_device_info": [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int)],
+    "b200spai_total_launches": [C.POINTER(c_i64)],
     "b200spai_csr_create_host": [c_i32, c_i32, c_i64, c_vp, c_vp, c_vp, c_vp, C.POINTER(c_vp)],
     "b200spai_csr_create_dev": [c_i32, c_i32, c_i64, c_vp, c_vp, c_vp, c_vp, C.POINTER(c_vp)],
     "b200spai_csr_transpose": [c_vp, c_vp, C.POINTER(c_vp)],
@@ -89,6 +90,13 @@ def check(rc: int, what: str = "") -> None:
     if rc != 0:
         msg = load().b200spai_last_error().decode("utf-8", "replace")
         raise B200SpaiError(f"{what} failed with status {rc}: {msg}")
+
+
+def total_launches() -> int:
+    """Kernel launches made by libb200spai in this process so far."""
+    v = c_i64()
+    check(load().b200spai_total_launches(C.byref(v)), "total_launches")
+    return v.value
 
 
 def require_cuda():

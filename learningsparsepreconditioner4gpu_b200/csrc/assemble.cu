@@ -148,6 +148,7 @@ extern "C" int b200spai_edges_to_csr(int64_t num_nodes, int64_t num_edges, int32
       rc = B200SPAI_ERR_CUDA;
     }
   }
+  count_launches(4);
   cudaFree(tmp);
   cudaFree(bad);
   cudaFree(brp);

@@ -12,6 +12,7 @@ namespace b200spai {
 
 void set_error(const std::string& msg);
 int sm_count();  // cached SM count of the current device
+void count_launches(long long n);  // process-wide tally of this library's kernel launches
 
 #define B2_CUDA(call)                                                                           \
   do {                                                                                          \

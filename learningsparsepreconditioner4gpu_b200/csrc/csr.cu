@@ -1,8 +1,8 @@
 // CSR container, row-block partition, transpose and SpMV dispatch.
 #include <cub/cub.cuh>
 
+#include <atomic>
 #include <cstdlib>
-#include <mutex>
 
 #include "csr.h"
 
@@ -11,6 +11,10 @@ namespace b200spai {
 static thread_local std::string g_last_error;
 void set_error(const std::string& msg) { g_last_error = msg; }
 const std::string& last_error() { return g_last_error; }
+
+static std::atomic<long long> g_launches{0};
+void count_launches(long long n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+long long total_launches() { return g_launches.load(std::memory_order_relaxed); }
 
 int sm_count() {
   static int cached[64] = {0};
@@ -53,8 +57,10 @@ void csr_free(b200spai_csr_s* a) {
   cudaFree(a->rowptr);
   cudaFree(a->col);
   cudaFree(a->val);
+  cudaFree(a->val32);
   cudaFree(a->blk[0]);
   cudaFree(a->blk[1]);
+  cudaFree(a->blk[2]);
   delete a;
 }
 
@@ -95,16 +101,71 @@ int build_row_blocks(const int* rowptr, int n_rows, long long nnz, long long tar
   partition_bounds_kernel<<<(nblk + 1 + 255) / 256, 256, 0, stream>>>(rowptr, n_rows, target, weight, nblk, bounds);
   partition_pack_kernel<<<(nblk + 255) / 256, 256, 0, stream>>>(rowptr, bounds, nblk, *blk_out);
   B2_LAUNCH_CHECK();
+  count_launches(2);
   B2_CUDA(cudaStreamSynchronize(stream));
   cudaFree(bounds);
   return 0;
 }
 
-static long long partition_target(int which) { return which == 0 ? StreamCfg<2048>::TARGET : StreamCfg<1024>::TARGET; }
+static long long partition_target(int which) {
+  return which == 0 ? StreamCfg<1024, double>::TARGET : which == 1 ? StreamCfg<2048, double>::TARGET : StreamCfg<4096, double>::TARGET;
+}
 
 int csr_ensure_partition(b200spai_csr_s* A, int which, cudaStream_t stream) {
   if (A->blk[which]) return 0;
   return build_row_blocks(A->rowptr, A->n_rows, A->nnz, partition_target(which), 2, &A->blk[which], &A->nblk[which], stream);
+}
+
+// ---- lossless fp32 value copy ---------------------------------------------------------------------
+__global__ void narrow_values_kernel(const double* __restrict__ v, long long n, float* __restrict__ out, int* __restrict__ lossy) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  int bad = 0;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double d = v[i];
+    const float f = (float)d;
+    out[i] = f;
+    bad |= !((double)f == d);  // also true for NaN: keep the fp64 stream then
+  }
+  if (__syncthreads_or(bad) && threadIdx.x == 0) atomicOr(lossy, 1);
+}
+
+static bool f32_disabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200SPAI_NO_FP32");
+    v = (e && atoi(e) != 0) ? 1 : 0;
+  }
+  return v == 1;
+}
+
+int csr_ensure_f32(b200spai_csr_s* A, cudaStream_t stream) {
+  if (A->f32_state != 0) return 0;
+  if (f32_disabled() || A->nnz == 0) {
+    A->f32_state = -1;
+    return 0;
+  }
+  int* lossy = nullptr;
+  B2_TRY(dev_alloc(&lossy, 1));
+  B2_CUDA(cudaMemsetAsync(lossy, 0, sizeof(int), stream));
+  B2_TRY(dev_alloc(&A->val32, (size_t)A->nnz + PAD));
+  B2_CUDA(cudaMemsetAsync(A->val32 + A->nnz, 0, PAD * sizeof(float), stream));
+  long long ctas = (A->nnz + 1023) / 1024;
+  if (ctas > (long long)sm_count() * 8) ctas = (long long)sm_count() * 8;
+  narrow_values_kernel<<<(int)ctas, 256, 0, stream>>>(A->val, A->nnz, A->val32, lossy);
+  B2_LAUNCH_CHECK();
+  count_launches(1);
+  int h = 0;
+  B2_CUDA(cudaMemcpyAsync(&h, lossy, sizeof(int), cudaMemcpyDeviceToHost, stream));
+  B2_CUDA(cudaStreamSynchronize(stream));
+  cudaFree(lossy);
+  if (h) {
+    cudaFree(A->val32);
+    A->val32 = nullptr;
+    A->f32_state = -1;
+  } else {
+    A->f32_state = 1;
+  }
+  return 0;
 }
 
 // ---- SpMV dispatch -------------------------------------------------------------------------------
@@ -113,7 +174,7 @@ static int stream_cfg_from_env() {
   if (cfg < 0) {
     const char* e = getenv("B200SPAI_STREAM_CFG");
     cfg = e ? atoi(e) : 0;
-    if (cfg < 0 || cfg > 3) cfg = 0;
+    if (cfg < 0 || cfg > 11) cfg = 0;
   }
   return cfg;
 }
@@ -152,34 +213,49 @@ static int launch_vector_mode(b200spai_csr_s* A, const SpmvArgs& args, cudaStrea
   return launch_vector<32, MODE>(A, args, stream);
 }
 
-template <int CAP, int STAGES, int MODE>
-static int launch_stream(b200spai_csr_s* A, const SpmvArgs& args, cudaStream_t stream) {
-  constexpr int which = (CAP == 2048) ? 0 : 1;
-  B2_TRY(csr_ensure_partition(A, which, stream));
-  const int smem = StreamCfg<CAP>::smem_bytes(STAGES);
-  auto kern = spmv_stream_kernel<CAP, STAGES, MODE>;
+template <int CAP, int STAGES, int NCW, typename VT, int MODE>
+static int launch_stream_t(b200spai_csr_s* A, const VT* vals, const SpmvArgs& args, cudaStream_t stream) {
+  constexpr int which = (CAP == 1024) ? 0 : (CAP == 2048) ? 1 : 2;
+  constexpr int threads = (NCW + 1) * 32;
+  const int smem = StreamCfg<CAP, VT>::smem_bytes(STAGES);
+  auto kern = spmv_stream_kernel<CAP, STAGES, NCW, VT, MODE>;
   static int ctas_per_sm = 0;  // per instantiation
   if (ctas_per_sm == 0) {
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     int occ = 0;
-    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 256, smem));
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, smem));
     ctas_per_sm = occ > 0 ? occ : 1;
   }
   int grid = sm_count() * ctas_per_sm;
   if (grid > A->nblk[which]) grid = A->nblk[which];
   if (grid < 1) grid = 1;
-  kern<<<grid, 256, smem, stream>>>(A->view(), A->blk[which], A->nblk[which], args);
+  kern<<<grid, threads, smem, stream>>>(A->view(), vals, A->blk[which], A->nblk[which], args);
   B2_LAUNCH_CHECK();
   return 0;
+}
+
+template <int CAP, int STAGES, int NCW, int MODE>
+static int launch_stream(b200spai_csr_s* A, const SpmvArgs& args, cudaStream_t stream) {
+  constexpr int which = (CAP == 1024) ? 0 : (CAP == 2048) ? 1 : 2;
+  B2_TRY(csr_ensure_partition(A, which, stream));
+  B2_TRY(csr_ensure_f32(A, stream));
+  if (A->f32_state == 1) return launch_stream_t<CAP, STAGES, NCW, float, MODE>(A, A->val32, args, stream);
+  return launch_stream_t<CAP, STAGES, NCW, double, MODE>(A, A->val, args, stream);
 }
 
 template <int MODE>
 static int launch_stream_mode(b200spai_csr_s* A, const SpmvArgs& args, cudaStream_t stream) {
   switch (stream_cfg_from_env()) {
-    case 1: return launch_stream<2048, 2, MODE>(A, args, stream);
-    case 2: return launch_stream<1024, 4, MODE>(A, args, stream);
-    case 3: return launch_stream<1024, 2, MODE>(A, args, stream);
-    default: return launch_stream<2048, 3, MODE>(A, args, stream);
+    // development sweep (B200SPAI_STREAM_CFG); the default is the measured best on the 216^3 Poisson system
+    case 1: return launch_stream<2048, 3, 4, MODE>(A, args, stream);
+    case 2: return launch_stream<4096, 2, 8, MODE>(A, args, stream);
+    case 3: return launch_stream<1024, 2, 2, MODE>(A, args, stream);
+    case 4: return launch_stream<1024, 2, 4, MODE>(A, args, stream);
+    case 5: return launch_stream<2048, 2, 2, MODE>(A, args, stream);
+    case 6: return launch_stream<2048, 2, 8, MODE>(A, args, stream);
+    case 7: return launch_stream<4096, 2, 4, MODE>(A, args, stream);
+    case 8: return launch_stream<1024, 3, 2, MODE>(A, args, stream);
+    default: return launch_stream<2048, 2, 4, MODE>(A, args, stream);
   }
 }
 
@@ -261,6 +337,7 @@ static int csr_transpose_impl(b200spai_csr_s* A, cudaStream_t stream, b200spai_c
     B2_CUDA(cub::DeviceScan::InclusiveSum(tmp, scan_bytes, T->rowptr, T->rowptr, A->n_cols + 1, stream));
     gather_transposed_kernel<<<(unsigned)((nnz + tb - 1) / tb), tb, 0, stream>>>(perm, rowidx, A->val, nnz, T->col, T->val);
     B2_LAUNCH_CHECK();
+    count_launches(4);  // + the cub sort / scan passes, which are library kernels and not counted
     B2_CUDA(cudaStreamSynchronize(stream));
     cudaFree(tmp);
     cudaFree(rowidx);
@@ -291,7 +368,13 @@ using namespace b200spai;
 extern "C" {
 
 const char* b200spai_last_error(void) { return last_error().c_str(); }
-int b200spai_version(void) { return 100; }
+int b200spai_version(void) { return 101; }
+
+int b200spai_total_launches(int64_t* launches) {
+  B2_ARG(launches, "total_launches: NULL argument");
+  *launches = total_launches();
+  return 0;
+}
 
 int b200spai_device_info(char* name128, int* sm, int* cc) {
   int dev = 0;
@@ -374,6 +457,7 @@ int b200spai_spmv(b200spai_csr_t a, const double* x, double* y, int kernel, void
   SpmvArgs args{};
   args.x = x;
   args.y = y;
+  count_launches(1);
   return spmv_launch(a, args, SPMV_PLAIN, kernel, as_stream(stream));
 }
 
@@ -382,6 +466,7 @@ int b200spai_csr_diagonal(b200spai_csr_t a, double* diag, void* stream) {
   if (a->n_rows == 0) return 0;
   diagonal_kernel<<<(a->n_rows + 255) / 256, 256, 0, as_stream(stream)>>>(a->view(), diag);
   B2_LAUNCH_CHECK();
+  count_launches(1);
   return 0;
 }
 

@@ -9,9 +9,13 @@ struct b200spai_csr_s {
   int* rowptr = nullptr;
   int* col = nullptr;
   double* val = nullptr;
-  // streaming partition (built lazily per CAP): {r0, lo, r1, hi} per row block
-  int4* blk[2] = {nullptr, nullptr};
-  int nblk[2] = {0, 0};
+  // fp32 copy of the values, present when every value is exactly representable in fp32 (built lazily with
+  // the partition).  f32_state: 0 = not examined yet, 1 = val32 valid, -1 = not lossless / disabled.
+  float* val32 = nullptr;
+  int f32_state = 0;
+  // streaming partition (built lazily per CAP: 1024, 2048, 4096): {r0, lo, r1, hi} per row block
+  int4* blk[3] = {nullptr, nullptr, nullptr};
+  int nblk[3] = {0, 0, 0};
   int max_row_len = -1;
   double mean_row_len = 0.0;
 
@@ -26,8 +30,10 @@ void csr_free(b200spai_csr_s* a);
 
 // kernel: 0 auto, 1 vector, 2 stream.  `mode` selects the epilogue.
 int spmv_launch(b200spai_csr_s* A, const SpmvArgs& args, int mode, int kernel, cudaStream_t stream);
-// number of kernel launches spmv_launch performs (always 1; partition build is one-off)
+// Lazily built per-matrix pieces of the streaming kernel (row-block partition for CAP index `which`, fp32 value
+// copy).  One-off; synchronises the stream.
 int csr_ensure_partition(b200spai_csr_s* A, int which, cudaStream_t stream);
+int csr_ensure_f32(b200spai_csr_s* A, cudaStream_t stream);
 // Contiguous row blocks {r0, rowptr[r0], r1, rowptr[r1]} balanced on rowptr[r] + weight*r (one-off, synchronises).
 int build_row_blocks(const int* rowptr, int n_rows, long long nnz, long long target, int weight, int4** blk_out,
                      int* nblk_out, cudaStream_t stream);

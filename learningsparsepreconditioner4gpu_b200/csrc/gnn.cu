@@ -187,6 +187,7 @@ static int graph_create_impl(long long N, long long E, const long long* edge_ind
     graph_free(g);
     return B200SPAI_ERR_ARG;
   }
+  count_launches(E > 0 ? 8 : 1);
   rc = build_row_blocks(g->segptr, (int)N, E, NB_TARGET, 4, &g->nb, &g->nnb, st);
   if (rc) {
     graph_free(g);
@@ -308,7 +309,7 @@ int b200spai_gnn_forward(b200spai_gnn_t m, b200spai_graph_t g, const float* x_de
   }
   B2_LAUNCH_CHECK();
   if (node_out_dev) B2_CUDA(cudaMemcpyAsync(node_out_dev, xin, (size_t)N * F * sizeof(float), cudaMemcpyDeviceToDevice, st));
-  m->launches += 2 + m->L;
+  { const long long _nl = (2 + m->L); m->launches += _nl; count_launches(_nl); }
   return 0;
 }
 
@@ -327,6 +328,7 @@ int b200spai_graph_spmv_f32(b200spai_graph_t g, int32_t block_size, const float*
     graph_spmv_f32_kernel<false><<<grid, tb, 0, as_stream(stream)>>>(g->rsegptr, g->rperm, g->rcol, g->N, block_size,
                                                                      values_dev, x_dev, mask_dev, y_dev);
   B2_LAUNCH_CHECK();
+  count_launches(1);
   return 0;
 }
 

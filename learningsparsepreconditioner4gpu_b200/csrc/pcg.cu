@@ -88,6 +88,9 @@ __global__ void __launch_bounds__(VTHREADS) pcg_init_kernel(const double* __rest
     sc->converged = (bn == 0.0);
     if (!(bn == bn)) sc->breakdown = 1;
     hist[0] = bn;
+    // graph driver: the WHILE node that follows must not be entered for b == 0 (every body kernel would return
+    // at its `done` test and nobody would ever clear the loop condition)
+    if (sc->use_cond) cudaGraphSetConditional((cudaGraphConditionalHandle)sc->cond_handle, zero_rhs ? 0u : 1u);
   }
 }
 
@@ -110,16 +113,30 @@ __global__ void __launch_bounds__(VTHREADS) pcg_jacobi_kernel(const double* __re
   if (grid_sum_last(cta, partials, ticket, red, total) && threadIdx.x == 0) pcg_final_scalar(sc, FINAL_RHO, total);
 }
 
+// The two vector kernels move 16 bytes per thread and access (double2) with two independent pairs in flight.
 __global__ void __launch_bounds__(VTHREADS) pcg_update_p_kernel(const double* __restrict__ z, double* __restrict__ p,
                                                                 int n, const PcgScalars* sc) {
   if (sc->done) return;
   const bool first = (sc->iter == 0);
   const double beta = sc->beta;
   const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const double zv = z[i];
+  const long long n2 = n >> 1;
+  const double2* z2 = reinterpret_cast<const double2*>(z);
+  double2* p2 = reinterpret_cast<double2*>(p);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
+    const double2 zv = z2[i];
     // scipy: p *= beta; p += z  (two roundings, reproduced: no fma contraction)
-    p[i] = first ? zv : __dadd_rn(__dmul_rn(p[i], beta), zv);
+    double2 pv = zv;
+    if (!first) {
+      pv = p2[i];
+      pv.x = __dadd_rn(__dmul_rn(pv.x, beta), zv.x);
+      pv.y = __dadd_rn(__dmul_rn(pv.y, beta), zv.y);
+    }
+    p2[i] = pv;
+  }
+  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+    const double zv = z[n - 1];
+    p[n - 1] = first ? zv : __dadd_rn(__dmul_rn(p[n - 1], beta), zv);
   }
 }
 
@@ -128,12 +145,34 @@ __global__ void __launch_bounds__(VTHREADS) pcg_update_xr_kernel(double* __restr
                                                                  int n, PcgScalars* sc, double* partials, unsigned* ticket,
                                                                  double* hist) {
   __shared__ double red[34];
-  if (sc->done) return;
+  if (sc->done) {  // never inside the loop of a healthy solve; keeps a WHILE body from spinning if it happens
+    if (sc->use_cond && blockIdx.x == 0 && threadIdx.x == 0)
+      cudaGraphSetConditional((cudaGraphConditionalHandle)sc->cond_handle, 0u);
+    return;
+  }
   const double alpha = sc->alpha;
   double acc = 0.0;
   const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+  const long long n2 = n >> 1;
+  double2* x2 = reinterpret_cast<double2*>(x);
+  double2* r2 = reinterpret_cast<double2*>(r);
+  const double2* p2 = reinterpret_cast<const double2*>(p);
+  const double2* q2 = reinterpret_cast<const double2*>(q);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
     // scipy: x += alpha*p ; r -= alpha*q  (product rounded, then add)
+    double2 xv = x2[i], rv = r2[i];
+    const double2 pv = p2[i], qv = q2[i];
+    xv.x = __dadd_rn(xv.x, __dmul_rn(alpha, pv.x));
+    xv.y = __dadd_rn(xv.y, __dmul_rn(alpha, pv.y));
+    rv.x = __dsub_rn(rv.x, __dmul_rn(alpha, qv.x));
+    rv.y = __dsub_rn(rv.y, __dmul_rn(alpha, qv.y));
+    x2[i] = xv;
+    r2[i] = rv;
+    acc += rv.x * rv.x;
+    acc += rv.y * rv.y;
+  }
+  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+    const int i = n - 1;
     x[i] = __dadd_rn(x[i], __dmul_rn(alpha, p[i]));
     const double rv = __dsub_rn(r[i], __dmul_rn(alpha, q[i]));
     r[i] = rv;
@@ -320,9 +359,10 @@ static int solve_impl(b200spai_pcg_s* s, int precond, const double* b, double* x
     B2_CUDA(cudaGraphLaunch(s->exec[precond], st));
     B2_CUDA(cudaMemcpyAsync(x, s->xw, (size_t)s->n * sizeof(double), cudaMemcpyDeviceToDevice, st));
   } else {
-    pcg_init_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(b, x, s->r, s->n, s->sc, s->partials, s->ticket, s->hist);
+    double* xs = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) ? x : s->xw;  // the vector kernels use 16-byte accesses
+    pcg_init_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(b, xs, s->r, s->n, s->sc, s->partials, s->ticket, s->hist);
     B2_LAUNCH_CHECK();
-    s->launches += 1;
+    { const long long _nl = (1); s->launches += _nl; count_launches(_nl); }
     const int CH = 8;
     int slot = 0;
     long long enq = 0;
@@ -330,8 +370,8 @@ static int solve_impl(b200spai_pcg_s* s, int precond, const double* b, double* x
     s->h_done[0] = s->h_done[1] = 0;
     while (true) {
       int nl = 0;
-      for (int c = 0; c < CH; ++c) B2_TRY(enqueue_iteration(s, precond, x, st, &nl));
-      s->launches += nl;
+      for (int c = 0; c < CH; ++c) B2_TRY(enqueue_iteration(s, precond, xs, st, &nl));
+      { const long long _nl = (nl); s->launches += _nl; count_launches(_nl); }
       enq += CH;
       B2_CUDA(cudaMemcpyAsync(s->h_done + slot, &s->sc->done, sizeof(int), cudaMemcpyDeviceToHost, st));
       B2_CUDA(cudaEventRecord(s->ev_chunk[slot], st));
@@ -344,12 +384,13 @@ static int solve_impl(b200spai_pcg_s* s, int precond, const double* b, double* x
       if (s->h_done[slot]) break;
       if (enq >= (long long)max_iter + 2 * CH) break;
     }
+    if (xs != x) B2_CUDA(cudaMemcpyAsync(x, xs, (size_t)s->n * sizeof(double), cudaMemcpyDeviceToDevice, st));
   }
   B2_CUDA(cudaEventRecord(s->ev1, st));
   B2_CUDA(cudaMemcpyAsync(s->h_out, s->sc, sizeof(PcgScalars), cudaMemcpyDeviceToHost, st));
   B2_CUDA(cudaStreamSynchronize(st));
   const PcgScalars& o = *s->h_out;
-  if (mode == 2) s->launches += 1 + (long long)s->launches_per_iter[precond] * (o.iter > 0 ? o.iter : 1);
+  if (mode == 2) { const long long _nl = (1 + (long long)s->launches_per_iter[precond] * (o.iter > 0 ? o.iter : 1)); s->launches += _nl; count_launches(_nl); }
   res->iterations = o.iter;
   res->converged = o.converged;
   res->breakdown = o.breakdown;
@@ -468,7 +509,7 @@ int b200spai_pcg_apply_precond(b200spai_pcg_t s, int precond, const double* r, d
   if (precond == B200SPAI_PRECOND_EXT_SPAI_SCALED) B2_TRY(ensure_diag(s, st));
   int nl = 0;
   B2_TRY(enqueue_precond(s, precond, r, z, nullptr, st, &nl));
-  s->launches += nl;
+  { const long long _nl = (nl); s->launches += _nl; count_launches(_nl); }
   return 0;
 }
 
@@ -481,6 +522,7 @@ int b200spai_pcg_profile_iterations(b200spai_pcg_t s, int precond, const double*
   if (precond == B200SPAI_PRECOND_DIAGONAL || precond == B200SPAI_PRECOND_EXT_SPAI_SCALED) B2_TRY(ensure_diag(s, st));
   B2_TRY(ensure_hist(s, (long long)iterations + 1));
   const bool spai = precond >= B200SPAI_PRECOND_EXT_SPAI;
+  if (reinterpret_cast<uintptr_t>(x) & 15) x = s->xw;  // the vector kernels use 16-byte accesses
   PcgScalars init{};
   init.rtol = 0.0;  // never converges: exactly `iterations` updates are timed
   init.max_iter = iterations;
@@ -538,7 +580,7 @@ int b200spai_pcg_profile_iterations(b200spai_pcg_t s, int precond, const double*
       kernel_ms5[k] += ms / iterations;
     }
   for (auto& e : ev) cudaEventDestroy(e);
-  s->launches += (long long)iterations * (spai ? 5 : 4);
+  { const long long _nl = ((long long)iterations * (spai ? 5 : 4)); s->launches += _nl; count_launches(_nl); }
   return 0;
 }
 

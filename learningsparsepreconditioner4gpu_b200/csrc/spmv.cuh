@@ -7,12 +7,12 @@
 //  * spmv_stream_kernel  -- the B200 path.  Rows are pre-partitioned (once per matrix) into row
 //    blocks of <= CAP non-zeros.  CSR values / column indices / row pointers of a block are
 //    *contiguous* in HBM, so each block is staged into shared memory with three 1-D TMA bulk copies
-//    (cp.async.bulk + mbarrier complete_tx), STAGES blocks deep, with an L2 evict-first policy so the
-//    streamed matrix does not displace the vectors that are gathered out of L2.  A staged block is
-//    consumed in two passes: (A) nnz-parallel  prod[k] = val[k] * x[col[k]]  (coalesced smem reads,
-//    all gathers independent), (B) row-parallel  y[row] = sum(prod[rowptr..])  + fused epilogue.
-//    Blocks are dealt to CTAs round-robin, so all CTAs sweep the matrix as one wavefront and the
-//    gathered window of x stays L2/L1 resident.
+//    (cp.async.bulk + mbarrier complete_tx) by a producer warp, STAGES blocks deep, with an L2
+//    evict-first policy so the streamed matrix does not displace the vectors that are gathered out
+//    of L2.  Consumer warps process a staged block row-parallel (thread = row) straight out of
+//    shared memory and hand the slot back through an "empty" mbarrier.  Blocks are dealt to CTAs
+//    round-robin, so all CTAs sweep the matrix as one wavefront and the gathered window of x
+//    stays L2/L1 resident.  Values are streamed as fp32 when that is lossless (see below).
 //
 // Epilogues (MODE):   PLAIN      y = Ax
 //                     SCALE      y = (Ax) / d                          t = (G^T r)/d   (scaled SPAI)
@@ -153,115 +153,147 @@ __global__ void __launch_bounds__(256) spmv_vector_kernel(CsrView A, SpmvArgs a)
 }
 
 // ------------------------------------------------------------------------------------------------
-// Kernel 2: TMA-staged streaming kernel
+// Kernel 2: TMA-staged, warp-specialised, row-parallel streaming kernel
 // ------------------------------------------------------------------------------------------------
-template <int CAP>
+// One producer warp (one elected lane) keeps STAGES row blocks in flight with 1-D bulk copies
+// (values, column indices, row pointers -> shared memory, mbarrier complete_tx, L2 evict-first);
+// NCW consumer warps take a staged block ROW-PARALLEL: thread = row, walking its entries out of
+// shared memory.  Adjacent rows of a mesh matrix have adjacent column indices, so the gather
+// x[col] of one k-step of a warp touches 2-3 128-byte lines instead of the ~16 an nnz-parallel
+// sweep touches (the L1 pipeline takes about one cycle per line, which bounded the previous
+// version at ~1/3 of HBM peak).  Slots are recycled through per-slot "empty" mbarriers, so no
+// CTA-wide barrier sits in the loop and the consumer warps drift freely over the stages.
+// VT = float when every value of the matrix is exactly representable in fp32 (true for A and G of
+// this path: both are widened fp32 tensors) -- values are widened on load, arithmetic stays fp64,
+// results are bit-identical, and the stream is 8 instead of 12 bytes per entry.
+template <int CAP, typename VT>
 struct StreamCfg {
   static constexpr int SLACK = CAP / 8;          // rows up to SLACK long never overflow a block
   static constexpr int TARGET = CAP - SLACK;     // partition target on key(r) = rowptr[r] + 2 r
   static constexpr int RCAP = CAP / 2 + 1;       // max rows per block + 1
-  static constexpr int VALS = CAP + 8;           // staged doubles (alignment slack both ends)
+  static constexpr int VALS = CAP + 8;           // staged values (alignment slack both ends)
   static constexpr int COLS = CAP + 8;
   static constexpr int RPTR = ((RCAP + 8 + 3) / 4) * 4;
-  static constexpr int STAGE_BYTES = VALS * 8 + COLS * 4 + RPTR * 4;
-  static constexpr int smem_bytes(int stages) { return stages * STAGE_BYTES + stages * 16 /*hdr*/ + stages * 8 + 34 * 8; }
+  static constexpr int STAGE_BYTES = VALS * (int)sizeof(VT) + COLS * 4 + RPTR * 4;
+  static constexpr int smem_bytes(int stages) { return stages * STAGE_BYTES + stages * 16 /*hdr*/ + stages * 16 /*bars*/ + 34 * 8; }
 };
 
-template <int CAP, int STAGES, int MODE>
-__global__ void __launch_bounds__(256) spmv_stream_kernel(CsrView A, const int4* __restrict__ blk, int nblk, SpmvArgs a) {
-  using C = StreamCfg<CAP>;
+template <int CAP, int STAGES, int NCW, typename VT, int MODE>
+__global__ void __launch_bounds__((NCW + 1) * 32)
+    spmv_stream_kernel(CsrView A, const VT* __restrict__ Aval, const int4* __restrict__ blk, int nblk, SpmvArgs a) {
+  using C = StreamCfg<CAP, VT>;
+  constexpr int NCT = NCW * 32;  // consumer threads
   extern __shared__ __align__(128) unsigned char smem_raw[];
   if (a.sc && a.sc->done) return;
-  double* s_vals = reinterpret_cast<double*>(smem_raw);                              // [STAGES][VALS]
-  int* s_cols = reinterpret_cast<int*>(smem_raw + STAGES * C::VALS * 8);             // [STAGES][COLS]
-  int* s_rptr = s_cols + STAGES * C::COLS;                                           // [STAGES][RPTR]
-  int4* s_hdr = reinterpret_cast<int4*>(s_rptr + STAGES * C::RPTR);                  // [STAGES]
-  uint64_t* s_full = reinterpret_cast<uint64_t*>(s_hdr + STAGES);                    // [STAGES]
-  double* red = reinterpret_cast<double*>(s_full + STAGES);                          // [34]
+  VT* s_vals = reinterpret_cast<VT*>(smem_raw);                                                  // [STAGES][VALS]
+  int* s_cols = reinterpret_cast<int*>(smem_raw + STAGES * C::VALS * sizeof(VT));                // [STAGES][COLS]
+  int* s_rptr = s_cols + STAGES * C::COLS;                                                       // [STAGES][RPTR]
+  int4* s_hdr = reinterpret_cast<int4*>(s_rptr + STAGES * C::RPTR);                              // [STAGES]
+  uint64_t* s_full = reinterpret_cast<uint64_t*>(s_hdr + STAGES);                                // [STAGES]
+  uint64_t* s_empty = s_full + STAGES;                                                           // [STAGES]
+  double* red = reinterpret_cast<double*>(s_empty + STAGES);                                     // [34]
 
   const int tid = threadIdx.x;
   const int G = gridDim.x;
   const int first = blockIdx.x;
   const int n_items = (first < nblk) ? (nblk - first + G - 1) / G : 0;
-  uint64_t policy = 0;
   if (tid == 0) {
-    for (int s = 0; s < STAGES; ++s) mbar_init(s_full + s, 1);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(s_full + s, 1);
+      mbar_init(s_empty + s, NCW);
+    }
     mbar_fence_init();
-    policy = policy_evict_first();
   }
   __syncthreads();
 
-  // producer state (thread 0 only): block descriptor of the next item to issue, prefetched
-  int issue_j = 0;
-  int4 next_info = make_int4(0, 0, 0, 0);
-  if (tid == 0 && n_items > 0) next_info = __ldg(blk + first);
-
-  auto issue = [&](int j) {  // thread 0: stage item j into slot j % STAGES
-    const int slot = j % STAGES;
-    const int4 info = next_info;
-    if (j + 1 < n_items) next_info = __ldg(blk + first + (long long)(j + 1) * G);
-    s_hdr[slot] = info;
-    const int lo = info.y, hi = info.w, r0 = info.x, r1 = info.z;
-    const int cnt = hi - lo;
-    if (cnt > CAP || cnt <= 0) {  // long block or all-empty rows: processed from global memory
-      mbar_arrive(s_full + slot);
-      return;
-    }
-    const int a_lo = lo & ~3;
-    const int n4 = (hi - a_lo + 3) & ~3;
-    const int ra = r0 & ~3;
-    const int nr4 = (r1 + 1 - ra + 3) & ~3;
-    mbar_arrive_expect_tx(s_full + slot, (uint32_t)(n4 * 12 + nr4 * 4));
-    bulk_g2s(s_vals + slot * C::VALS, A.val + a_lo, (uint32_t)n4 * 8, s_full + slot, policy);
-    bulk_g2s(s_cols + slot * C::COLS, A.col + a_lo, (uint32_t)n4 * 4, s_full + slot, policy);
-    bulk_g2s(s_rptr + slot * C::RPTR, A.rowptr + ra, (uint32_t)nr4 * 4, s_full + slot, policy);
-  };
-
-  if (tid == 0) {
-    for (; issue_j < STAGES - 1 && issue_j < n_items; ++issue_j) issue(issue_j);
-  }
-
   double dot = 0.0;
-  for (int i = 0; i < n_items; ++i) {
-    const int slot = i % STAGES;
-    if (tid == 0 && issue_j < n_items) {
-      issue(issue_j);
-      ++issue_j;
-    }
-    mbar_wait(s_full + slot, (uint32_t)((i / STAGES) & 1));
-    const int4 info = s_hdr[slot];
-    const int r0 = info.x, lo = info.y, r1 = info.z, hi = info.w;
-    const int cnt = hi - lo;
-    if (cnt > 0 && cnt <= CAP) {
-      double* vals = s_vals + slot * C::VALS + (lo & 3);
-      const int* cols = s_cols + slot * C::COLS + (lo & 3);
-      const int* rptr = s_rptr + slot * C::RPTR + (r0 & 3);
-      // pass A: products, nnz-parallel
-      for (int k = tid; k < cnt; k += 256) vals[k] = vals[k] * __ldg(a.x + cols[k]);
-      __syncthreads();
-      // pass B: row sums, row-parallel
-      for (int rr = tid; rr < r1 - r0; rr += 256) {
-        const int row = r0 + rr;
-        const double auxv = spmv_prefetch_aux<MODE>(a, row);
-        const int s = rptr[rr] - lo, e = rptr[rr + 1] - lo;
-        double sum = 0.0;
-        for (int k = s; k < e; ++k) sum += vals[k];
-        spmv_row_epilogue<MODE>(a, row, sum, auxv, dot);
-      }
-    } else {
-      // long block (a row longer than the stage capacity) or a block of empty rows: warp per row
-      // straight from global memory
-      const int lane = tid & 31, warp = tid >> 5;
-      for (int row = r0 + warp; row < r1; row += 8) {
-        const int s = __ldg(A.rowptr + row), e = __ldg(A.rowptr + row + 1);
-        double sum = 0.0;
-        for (int k = s + lane; k < e; k += 32) sum += __ldg(A.val + k) * __ldg(a.x + __ldg(A.col + k));
-        sum = warp_sum(sum);
-        if (lane == 0) spmv_row_epilogue<MODE>(a, row, sum, spmv_prefetch_aux<MODE>(a, row), dot);
+  if (tid >= NCT) {
+    // ---------------- producer warp ----------------
+    if (tid == NCT) {
+      const uint64_t policy = policy_evict_first();
+      int4 info = make_int4(0, 0, 0, 0);
+      if (n_items > 0) info = __ldg(blk + first);
+      for (int j = 0; j < n_items; ++j) {
+        const int slot = j % STAGES;
+        if (j >= STAGES) mbar_wait(s_empty + slot, (uint32_t)(((j / STAGES) - 1) & 1));
+        const int4 cur = info;
+        if (j + 1 < n_items) info = __ldg(blk + first + (long long)(j + 1) * G);
+        s_hdr[slot] = cur;
+        const int r0 = cur.x, lo = cur.y, r1 = cur.z, hi = cur.w;
+        const int cnt = hi - lo;
+        if (cnt > CAP || cnt <= 0) {  // over-long row or all-empty rows: consumers read global memory
+          mbar_arrive(s_full + slot);
+          continue;
+        }
+        const int a_lo = lo & ~3;
+        const int n4 = (hi - a_lo + 3) & ~3;
+        const int ra = r0 & ~3;
+        const int nr4 = (r1 + 1 - ra + 3) & ~3;
+        mbar_arrive_expect_tx(s_full + slot, (uint32_t)(n4 * (4 + (int)sizeof(VT)) + nr4 * 4));
+        bulk_g2s(s_vals + slot * C::VALS, Aval + a_lo, (uint32_t)(n4 * sizeof(VT)), s_full + slot, policy);
+        bulk_g2s(s_cols + slot * C::COLS, A.col + a_lo, (uint32_t)n4 * 4, s_full + slot, policy);
+        bulk_g2s(s_rptr + slot * C::RPTR, A.rowptr + ra, (uint32_t)nr4 * 4, s_full + slot, policy);
       }
     }
-    fence_proxy_async();  // order this thread's generic smem accesses before the slot's next TMA fill
-    __syncthreads();
+  } else {
+    // ---------------- consumer warps ----------------
+    const int lane = tid & 31, warp = tid >> 5;
+    const double* __restrict__ x = a.x;
+    for (int i = 0; i < n_items; ++i) {
+      const int slot = i % STAGES;
+      mbar_wait(s_full + slot, (uint32_t)((i / STAGES) & 1));
+      const int4 info = s_hdr[slot];
+      const int r0 = info.x, lo = info.y, r1 = info.z, hi = info.w;
+      const int cnt = hi - lo;
+      if (cnt > 0 && cnt <= CAP) {
+        const VT* vals = s_vals + slot * C::VALS + (lo & 3);
+        const int* cols = s_cols + slot * C::COLS + (lo & 3);
+        const int* rptr = s_rptr + slot * C::RPTR + (r0 & 3);
+        for (int rr = tid; rr < r1 - r0; rr += NCT) {
+          const int row = r0 + rr;
+          const double auxv = spmv_prefetch_aux<MODE>(a, row);
+          int k = rptr[rr] - lo;
+          const int e = rptr[rr + 1] - lo;
+          // Row sum in scipy's csr_matvec order and arithmetic (sequential, product rounded, then added -- no
+          // fma contraction), so y is bit-identical to `A @ x` of the reference's CPU path.  UNROLL independent
+          // gathers are in flight per thread; only the adds form a dependent chain.
+          double sum = 0.0;
+#pragma unroll 1
+          for (; k + 8 <= e; k += 8) {
+            int c[8];
+            double xv[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) c[u] = cols[k + u];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) xv[u] = __ldg(x + c[u]);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) sum = __dadd_rn(sum, __dmul_rn((double)vals[k + u], xv[u]));
+          }
+          if (k + 4 <= e) {
+            const int c0 = cols[k], c1 = cols[k + 1], c2 = cols[k + 2], c3 = cols[k + 3];
+            const double x0 = __ldg(x + c0), x1 = __ldg(x + c1), x2 = __ldg(x + c2), x3 = __ldg(x + c3);
+            sum = __dadd_rn(sum, __dmul_rn((double)vals[k], x0));
+            sum = __dadd_rn(sum, __dmul_rn((double)vals[k + 1], x1));
+            sum = __dadd_rn(sum, __dmul_rn((double)vals[k + 2], x2));
+            sum = __dadd_rn(sum, __dmul_rn((double)vals[k + 3], x3));
+            k += 4;
+          }
+          for (; k < e; ++k) sum = __dadd_rn(sum, __dmul_rn((double)vals[k], __ldg(x + cols[k])));
+          spmv_row_epilogue<MODE>(a, row, sum, auxv, dot);
+        }
+      } else {
+        // a row longer than the stage capacity, or a block of empty rows: warp per row from global memory
+        for (int row = r0 + warp; row < r1; row += NCW) {
+          const int s = __ldg(A.rowptr + row), e = __ldg(A.rowptr + row + 1);
+          double sum = 0.0;
+          for (int k = s + lane; k < e; k += 32) sum = fma((double)__ldg(Aval + k), __ldg(x + __ldg(A.col + k)), sum);
+          sum = warp_sum(sum);
+          if (lane == 0) spmv_row_epilogue<MODE>(a, row, sum, spmv_prefetch_aux<MODE>(a, row), dot);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(s_empty + slot);  // this warp is done reading the slot
+    }
   }
   spmv_finish_dot<MODE>(a, dot, red);
 }

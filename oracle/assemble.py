@@ -70,3 +70,35 @@ def to_csr_cpu(edge_index, edge_attr, n: int, mask, dtype=np.float64) -> csr_mat
     mat = csr_matrix(mat)
     mat.sort_indices()
     return mat
+
+
+def to_csr_cpu_sorted(edge_index, edge_attr, n: int, mask, dtype=np.float64) -> csr_matrix:
+    """Same matrix as ``to_csr_cpu`` for the scalar case (b = 1) when the edge list is what the reference's
+    datasets produce (row-major, ascending columns, duplicate-free, neural_cg/data.py:442-450), built directly
+    from the sorted triplets in O(E) numpy passes -- for the >= 10 M-row CPU baseline in bench.py, where the
+    COO round trips of the general function cost minutes.  Falls back to ``to_csr_cpu`` when a masked row has no
+    stored diagonal.  Equality with ``to_csr_cpu`` is tested on the fixtures (tests/test_oracle_golden.py)."""
+    row = to_numpy(edge_index[0]).astype(np.int64)
+    col = to_numpy(edge_index[1]).astype(np.int64)
+    vals = to_numpy(edge_attr)
+    assert vals.size == row.size, "scalar systems only"
+    data = vals.reshape(-1).astype(dtype)
+    key = row * n + col
+    if row.size and not (np.diff(key) > 0).all():
+        return to_csr_cpu(edge_index, edge_attr, n, mask, dtype)
+    indptr = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(np.bincount(row, minlength=n), out=indptr[1:])
+    if mask is not None:
+        m = to_numpy(mask).reshape(-1).astype(dtype)
+        on_diag = row == col
+        has_diag = np.zeros(n, dtype=bool)
+        has_diag[row[on_diag]] = True
+        if not has_diag[m != 1].all():
+            return to_csr_cpu(edge_index, edge_attr, n, mask, dtype)
+        data = np.where((m[row] != 0) & (m[col] != 0), data, 0.0)
+        data[on_diag] += (1.0 - m)[row[on_diag]]
+    mat = csr_matrix((data, col.astype(np.int32), indptr.astype(np.int32)), shape=(n, n))
+    if mask is not None:
+        mat.eliminate_zeros()
+    mat.has_sorted_indices = True
+    return mat

@@ -114,3 +114,27 @@ def pcg_scipy(A, gt, G, epsilon, rtol=1e-6, max_iter=0, kind="ext_spai", with_ti
         out.append(true_res)
         out.append(x)
     return out[0] if len(out) == 1 else tuple(out)
+
+
+class ScipyPcgTimer:
+    """The reference's scipy solve with the operator built ONCE (as validate.py:173-190 does before its clock starts),
+    so that bench.py can time a bounded number of iterations per step without re-materialising G^T."""
+
+    def __init__(self, A, G, epsilon, kind="ext_spai"):
+        self.A = A.astype(np.float64)
+        n = A.shape[0]
+        self.M = LinearOperator((n, n), matvec=make_preconditioner(kind, self.A, None if G is None else G.astype(np.float64),
+                                                                   epsilon), dtype=np.float64)
+
+    def run(self, gt, rtol=1e-6, max_iter=0):
+        """-> (callbacks, seconds): ``cg`` bracketed by the clock exactly like validate.py:195-197."""
+        b = self.A @ gt
+        count = 0
+
+        def cb(xk):
+            nonlocal count
+            count += 1
+
+        t0 = time.time()
+        cg(self.A, b, M=self.M, callback=cb, rtol=rtol, maxiter=max_iter if max_iter > 0 else self.A.shape[0])
+        return count, time.time() - t0

@@ -1,6 +1,7 @@
 """Pin the CPU oracle against the golden fixtures minted from the reference's own code
 (tests/golden/make_golden.py).  CPU only."""
 import numpy as np
+import pytest
 import torch
 
 from conftest import golden_csr, golden_state_dict
@@ -70,6 +71,20 @@ def test_to_csr_matches_reference_bit_exact(golden):
     G = assemble.to_csr_cpu(ei, torch.from_numpy(g["G"]), n, torch.from_numpy(g["mask"]))
     assert _csr_equal(G, golden_csr(g, "G")), name
     assert A.indices.dtype == np.int32 and A.data.dtype == np.float64
+
+
+def test_sorted_fast_assembly_equals_general(golden):
+    """to_csr_cpu_sorted (bench.py's CPU baseline at 10 M rows) is the same matrix as to_csr_cpu, bit for bit."""
+    name, g = golden
+    if int(g["block_size"]) != 1:
+        pytest.skip("scalar systems only")
+    ei = torch.from_numpy(g["raw_edge_index"])
+    n = g["mask"].size
+    for vals, key in ((g["matrix_values"], "A"), (g["G"], "G")):
+        M = assemble.to_csr_cpu_sorted(ei, torch.from_numpy(vals), n, torch.from_numpy(g["mask"]))
+        assert _csr_equal(M, golden_csr(g, key)), (name, key)
+    M0 = assemble.to_csr_cpu_sorted(ei, torch.from_numpy(g["matrix_values"]), n, None)
+    assert _csr_equal(M0, golden_csr(g, "A_nomask")), name
 
 
 def test_csr_invariants(golden):
