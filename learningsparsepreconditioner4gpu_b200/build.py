@@ -27,6 +27,11 @@ NVCC_FLAGS = [
     "--expt-relaxed-constexpr",
     "-I", INCLUDE,
 ]
+if os.environ.get("B200SPAI_PROBE"):  # development: cycle counters inside the streaming SpMV
+    NVCC_FLAGS.append("-DB200SPAI_PROBE")
+if os.environ.get("B200SPAI_PART_W"):  # development: row-block partition weight
+    NVCC_FLAGS.append("-DB200SPAI_PART_W=" + os.environ["B200SPAI_PART_W"])
+LIB = os.environ.get("B200SPAI_LIB_OUT", LIB)
 
 
 def _nvcc() -> str:

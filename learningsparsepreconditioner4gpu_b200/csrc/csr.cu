@@ -58,9 +58,12 @@ void csr_free(b200spai_csr_s* a) {
   cudaFree(a->col);
   cudaFree(a->val);
   cudaFree(a->val32);
+  cudaFree(a->col16);
+  cudaFree(a->rowfirst);
   cudaFree(a->blk[0]);
   cudaFree(a->blk[1]);
   cudaFree(a->blk[2]);
+  cudaFree(a->blk[3]);
   delete a;
 }
 
@@ -108,12 +111,14 @@ int build_row_blocks(const int* rowptr, int n_rows, long long nnz, long long tar
 }
 
 static long long partition_target(int which) {
-  return which == 0 ? StreamCfg<1024, double>::TARGET : which == 1 ? StreamCfg<2048, double>::TARGET : StreamCfg<4096, double>::TARGET;
+  return which == 0 ? StreamCfg<1024, double, int>::TARGET
+                    : which == 1 ? StreamCfg<2048, double, int>::TARGET
+                                 : which == 2 ? StreamCfg<4096, double, int>::TARGET : StreamCfg<8192, double, int>::TARGET;
 }
 
 int csr_ensure_partition(b200spai_csr_s* A, int which, cudaStream_t stream) {
   if (A->blk[which]) return 0;
-  return build_row_blocks(A->rowptr, A->n_rows, A->nnz, partition_target(which), 2, &A->blk[which], &A->nblk[which], stream);
+  return build_row_blocks(A->rowptr, A->n_rows, A->nnz, partition_target(which), PART_W, &A->blk[which], &A->nblk[which], stream);
 }
 
 // ---- lossless fp32 value copy ---------------------------------------------------------------------
@@ -168,13 +173,74 @@ int csr_ensure_f32(b200spai_csr_s* A, cudaStream_t stream) {
   return 0;
 }
 
+// ---- lossless 16-bit column-step stream ----------------------------------------------------------------
+__global__ void encode_col16_kernel(const int* __restrict__ rowptr, const int* __restrict__ col, int n_rows,
+                                    unsigned short* __restrict__ col16, int* __restrict__ rowfirst, int* __restrict__ bad) {
+  // one warp per row; lane k handles entries k, k+32, ... (each needs only its left neighbour)
+  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= n_rows) return;
+  const int s = rowptr[w], e = rowptr[w + 1];
+  if (lane == 0) rowfirst[w] = (s < e) ? col[s] : 0;
+  int overflow = 0;
+  for (int k = s + lane; k < e; k += 32) {
+    const int d = (k == s) ? 0 : col[k] - col[k - 1];
+    overflow |= (d < 0 || d > 65535);
+    col16[k] = (unsigned short)d;
+  }
+  if (overflow) atomicOr(bad, 1);
+}
+
+static bool col16_disabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200SPAI_NO_COL16");
+    v = (e && atoi(e) != 0) ? 1 : 0;
+  }
+  return v == 1;
+}
+
+int csr_ensure_col16(b200spai_csr_s* A, cudaStream_t stream) {
+  if (A->c16_state != 0) return 0;
+  if (col16_disabled() || A->nnz == 0) {
+    A->c16_state = -1;
+    return 0;
+  }
+  int* bad = nullptr;
+  B2_TRY(dev_alloc(&bad, 1));
+  B2_CUDA(cudaMemsetAsync(bad, 0, sizeof(int), stream));
+  B2_TRY(dev_alloc(&A->col16, (size_t)A->nnz + PAD));
+  B2_TRY(dev_alloc(&A->rowfirst, (size_t)A->n_rows + 1 + PAD));
+  B2_CUDA(cudaMemsetAsync(A->col16 + A->nnz, 0, PAD * sizeof(unsigned short), stream));
+  B2_CUDA(cudaMemsetAsync(A->rowfirst + A->n_rows, 0, (1 + PAD) * sizeof(int), stream));
+  const int tb = 256;
+  encode_col16_kernel<<<(unsigned)(((long long)A->n_rows * 32 + tb - 1) / tb), tb, 0, stream>>>(A->rowptr, A->col, A->n_rows,
+                                                                                            A->col16, A->rowfirst, bad);
+  B2_LAUNCH_CHECK();
+  count_launches(1);
+  int h = 0;
+  B2_CUDA(cudaMemcpyAsync(&h, bad, sizeof(int), cudaMemcpyDeviceToHost, stream));
+  B2_CUDA(cudaStreamSynchronize(stream));
+  cudaFree(bad);
+  if (h) {
+    cudaFree(A->col16);
+    cudaFree(A->rowfirst);
+    A->col16 = nullptr;
+    A->rowfirst = nullptr;
+    A->c16_state = -1;
+  } else {
+    A->c16_state = 1;
+  }
+  return 0;
+}
+
 // ---- SpMV dispatch -------------------------------------------------------------------------------
 static int stream_cfg_from_env() {
   static int cfg = -1;
   if (cfg < 0) {
     const char* e = getenv("B200SPAI_STREAM_CFG");
     cfg = e ? atoi(e) : 0;
-    if (cfg < 0 || cfg > 11) cfg = 0;
+    if (cfg < 0 || cfg > 4) cfg = 0;
   }
   return cfg;
 }
@@ -213,12 +279,12 @@ static int launch_vector_mode(b200spai_csr_s* A, const SpmvArgs& args, cudaStrea
   return launch_vector<32, MODE>(A, args, stream);
 }
 
-template <int CAP, int STAGES, int NCW, typename VT, int MODE>
-static int launch_stream_t(b200spai_csr_s* A, const VT* vals, const SpmvArgs& args, cudaStream_t stream) {
-  constexpr int which = (CAP == 1024) ? 0 : (CAP == 2048) ? 1 : 2;
+template <int CAP, int STAGES, int NCW, typename VT, typename CT, int MODE>
+static int launch_stream_t(b200spai_csr_s* A, const VT* vals, const CT* cols, const SpmvArgs& args, cudaStream_t stream) {
+  constexpr int which = (CAP == 1024) ? 0 : (CAP == 2048) ? 1 : (CAP == 4096) ? 2 : 3;
   constexpr int threads = (NCW + 1) * 32;
-  const int smem = StreamCfg<CAP, VT>::smem_bytes(STAGES);
-  auto kern = spmv_stream_kernel<CAP, STAGES, NCW, VT, MODE>;
+  const int smem = StreamCfg<CAP, VT, CT>::smem_bytes(STAGES);
+  auto kern = spmv_stream_kernel<CAP, STAGES, NCW, VT, CT, MODE>;
   static int ctas_per_sm = 0;  // per instantiation
   if (ctas_per_sm == 0) {
     B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -229,34 +295,38 @@ static int launch_stream_t(b200spai_csr_s* A, const VT* vals, const SpmvArgs& ar
   int grid = sm_count() * ctas_per_sm;
   if (grid > A->nblk[which]) grid = A->nblk[which];
   if (grid < 1) grid = 1;
-  kern<<<grid, threads, smem, stream>>>(A->view(), vals, A->blk[which], A->nblk[which], args);
+  kern<<<grid, threads, smem, stream>>>(A->view(), vals, cols, A->rowfirst, A->blk[which], A->nblk[which], args);
   B2_LAUNCH_CHECK();
   return 0;
 }
 
 template <int CAP, int STAGES, int NCW, int MODE>
 static int launch_stream(b200spai_csr_s* A, const SpmvArgs& args, cudaStream_t stream) {
-  constexpr int which = (CAP == 1024) ? 0 : (CAP == 2048) ? 1 : 2;
+  constexpr int which = (CAP == 1024) ? 0 : (CAP == 2048) ? 1 : (CAP == 4096) ? 2 : 3;
   B2_TRY(csr_ensure_partition(A, which, stream));
   B2_TRY(csr_ensure_f32(A, stream));
-  if (A->f32_state == 1) return launch_stream_t<CAP, STAGES, NCW, float, MODE>(A, A->val32, args, stream);
-  return launch_stream_t<CAP, STAGES, NCW, double, MODE>(A, A->val, args, stream);
+  B2_TRY(csr_ensure_col16(A, stream));
+  const bool f32 = A->f32_state == 1, c16 = A->c16_state == 1;
+  if (f32 && c16) return launch_stream_t<CAP, STAGES, NCW, float, unsigned short, MODE>(A, A->val32, A->col16, args, stream);
+  if (f32) return launch_stream_t<CAP, STAGES, NCW, float, int, MODE>(A, A->val32, A->col, args, stream);
+  if (c16) return launch_stream_t<CAP, STAGES, NCW, double, unsigned short, MODE>(A, A->val, A->col16, args, stream);
+  return launch_stream_t<CAP, STAGES, NCW, double, int, MODE>(A, A->val, A->col, args, stream);
 }
 
 template <int MODE>
 static int launch_stream_mode(b200spai_csr_s* A, const SpmvArgs& args, cudaStream_t stream) {
   switch (stream_cfg_from_env()) {
-    // development sweep (B200SPAI_STREAM_CFG); the default is the measured best on the 216^3 Poisson system
-    case 1: return launch_stream<2048, 3, 4, MODE>(A, args, stream);
-    case 2: return launch_stream<4096, 2, 8, MODE>(A, args, stream);
-    case 3: return launch_stream<1024, 2, 2, MODE>(A, args, stream);
-    case 4: return launch_stream<1024, 2, 4, MODE>(A, args, stream);
-    case 5: return launch_stream<2048, 2, 2, MODE>(A, args, stream);
-    case 6: return launch_stream<2048, 2, 8, MODE>(A, args, stream);
-    case 7: return launch_stream<4096, 2, 4, MODE>(A, args, stream);
-    case 8: return launch_stream<1024, 3, 2, MODE>(A, args, stream);
-    default: return launch_stream<2048, 2, 4, MODE>(A, args, stream);
+    // development sweep (B200SPAI_STREAM_CFG = 1..4)
+    case 1: return launch_stream<2048, 2, 4, MODE>(A, args, stream);
+    case 2: return launch_stream<4096, 2, 6, MODE>(A, args, stream);
+    case 3: return launch_stream<8192, 2, 8, MODE>(A, args, stream);
+    case 4: return launch_stream<4096, 2, 8, MODE>(A, args, stream);
+    default: break;
   }
+  // measured on the 216^3 Poisson system (profiles/r01_spmv_sweep.txt): 4096-entry stages with 8 consumer warps
+  // are the fastest once there are enough row blocks for every SM; mid-size systems keep the 2048-entry stages
+  if (A->nnz >= (1LL << 22)) return launch_stream<4096, 2, 8, MODE>(A, args, stream);
+  return launch_stream<2048, 2, 4, MODE>(A, args, stream);
 }
 
 template <int MODE>
@@ -369,6 +439,23 @@ extern "C" {
 
 const char* b200spai_last_error(void) { return last_error().c_str(); }
 int b200spai_version(void) { return 101; }
+
+/* development hook (not in the public header): cycle counters of the streaming SpMV when built with -DB200SPAI_PROBE */
+int b200spai_debug_probe(unsigned long long* out8, int reset) {
+#ifdef B200SPAI_PROBE
+  if (out8) B2_CUDA(cudaMemcpyFromSymbol(out8, g_probe, 8 * sizeof(unsigned long long)));
+  if (reset) {
+    unsigned long long z[8] = {0};
+    B2_CUDA(cudaMemcpyToSymbol(g_probe, z, sizeof(z)));
+  }
+  return 0;
+#else
+  (void)out8;
+  (void)reset;
+  set_error("built without B200SPAI_PROBE");
+  return B200SPAI_ERR_ARG;
+#endif
+}
 
 int b200spai_total_launches(int64_t* launches) {
   B2_ARG(launches, "total_launches: NULL argument");

@@ -13,9 +13,14 @@ struct b200spai_csr_s {
   // the partition).  f32_state: 0 = not examined yet, 1 = val32 valid, -1 = not lossless / disabled.
   float* val32 = nullptr;
   int f32_state = 0;
-  // streaming partition (built lazily per CAP: 1024, 2048, 4096): {r0, lo, r1, hi} per row block
-  int4* blk[3] = {nullptr, nullptr, nullptr};
-  int nblk[3] = {0, 0, 0};
+  // 16-bit within-row column steps + first column of every row, present when every step fits 16 bits.
+  // c16_state: 0 = not examined yet, 1 = col16/rowfirst valid, -1 = does not fit / disabled.
+  unsigned short* col16 = nullptr;
+  int* rowfirst = nullptr;
+  int c16_state = 0;
+  // streaming partition (built lazily per CAP: 1024, 2048, 4096, 8192): {r0, lo, r1, hi} per row block
+  int4* blk[4] = {nullptr, nullptr, nullptr, nullptr};
+  int nblk[4] = {0, 0, 0, 0};
   int max_row_len = -1;
   double mean_row_len = 0.0;
 
@@ -34,6 +39,7 @@ int spmv_launch(b200spai_csr_s* A, const SpmvArgs& args, int mode, int kernel, c
 // copy).  One-off; synchronises the stream.
 int csr_ensure_partition(b200spai_csr_s* A, int which, cudaStream_t stream);
 int csr_ensure_f32(b200spai_csr_s* A, cudaStream_t stream);
+int csr_ensure_col16(b200spai_csr_s* A, cudaStream_t stream);
 // Contiguous row blocks {r0, rowptr[r0], r1, rowptr[r1]} balanced on rowptr[r] + weight*r (one-off, synchronises).
 int build_row_blocks(const int* rowptr, int n_rows, long long nnz, long long target, int weight, int4** blk_out,
                      int* nblk_out, cudaStream_t stream);

@@ -6,30 +6,43 @@ namespace b200spai {
 // nn.GELU() default = exact erf form (neural_cg/nn/basic_layers.py:21-22)
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 
+// Packed fp32 FMA (Blackwell FFMA2): two independent fma.rn.f32 per instruction, same bits as two FFMA.
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  float2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;"
+      : "=l"(reinterpret_cast<unsigned long long&>(d))
+      : "l"(reinterpret_cast<const unsigned long long&>(a)), "l"(reinterpret_cast<const unsigned long long&>(b)),
+        "l"(reinterpret_cast<const unsigned long long&>(c)));
+  return d;
+}
+
 // y[j] = bias[j] + sum_k x[k] * W[k][j];  W [K][16] and bias [16] in shared memory (16-byte aligned).
-// Every lane reads the same addresses (broadcast LDS.128), 4 weights per load, 16 FFMA per k.
+// Every lane reads the same addresses (broadcast LDS.128), 4 weights per load, 8 FFMA2 (= 16 FMA) per k.
 template <int K>
 __device__ __forceinline__ void dense16(const float* W, const float* bias, const float (&x)[K], float (&y)[F]) {
   const float4* b4 = reinterpret_cast<const float4*>(bias);
+  float2 acc[8];
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
     const float4 v = b4[q];
-    y[4 * q + 0] = v.x;
-    y[4 * q + 1] = v.y;
-    y[4 * q + 2] = v.z;
-    y[4 * q + 3] = v.w;
+    acc[2 * q] = make_float2(v.x, v.y);
+    acc[2 * q + 1] = make_float2(v.z, v.w);
   }
 #pragma unroll
   for (int k = 0; k < K; ++k) {
     const float4* w4 = reinterpret_cast<const float4*>(W + k * F);
+    const float2 xx = make_float2(x[k], x[k]);
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const float4 w = w4[q];
-      y[4 * q + 0] = fmaf(x[k], w.x, y[4 * q + 0]);
-      y[4 * q + 1] = fmaf(x[k], w.y, y[4 * q + 1]);
-      y[4 * q + 2] = fmaf(x[k], w.z, y[4 * q + 2]);
-      y[4 * q + 3] = fmaf(x[k], w.w, y[4 * q + 3]);
+      acc[2 * q] = ffma2(xx, make_float2(w.x, w.y), acc[2 * q]);
+      acc[2 * q + 1] = ffma2(xx, make_float2(w.z, w.w), acc[2 * q + 1]);
     }
+  }
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    y[2 * q] = acc[q].x;
+    y[2 * q + 1] = acc[q].y;
   }
 }
 

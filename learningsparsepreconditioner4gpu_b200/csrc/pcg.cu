@@ -15,9 +15,11 @@
 //   mode 2 (graph):  one CUDA graph = init kernel + a WHILE conditional node whose body is the 5
 //           kernels; K5's last CTA sets the loop condition (cudaGraphSetConditional).  One launch
 //           per solve, no host involvement until the result is read.
+#include <cstdlib>
 #include <vector>
 
 #include "csr.h"
+#include "pcg_kernels.cuh"
 
 using namespace b200spai;
 
@@ -50,156 +52,15 @@ struct b200spai_pcg_s {
 
 namespace b200spai {
 
-static constexpr int VTHREADS = 256;
-static constexpr int MAX_PARTIALS = 8192;
-
-static int vec_grid(int n) {
-  long long g = ((long long)n + VTHREADS * 4 - 1) / (VTHREADS * 4);
-  const long long cap = (long long)sm_count() * 8;
-  if (g > cap) g = cap;
-  if (g < 1) g = 1;
-  return (int)g;
-}
-
-__global__ void __launch_bounds__(VTHREADS) pcg_init_kernel(const double* __restrict__ b, double* __restrict__ x,
-                                                            double* __restrict__ r, int n, PcgScalars* sc,
-                                                            double* partials, unsigned* ticket, double* hist) {
-  __shared__ double red[34];
-  double acc = 0.0;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const double v = b[i];
-    r[i] = v;
-    x[i] = 0.0;
-    acc += v * v;
+// auto mode: the graph driver, unless B200SPAI_PCG_MODE=1 asks for stream-enqueued kernels (ncu cannot see the
+// kernel nodes of a graph that holds a conditional node, so the profiling passes run in mode 1)
+static int default_mode() {
+  static int v = 0;
+  if (v == 0) {
+    const char* e = getenv("B200SPAI_PCG_MODE");
+    v = (e && atoi(e) == 1) ? 1 : 2;
   }
-  double cta = block_sum(acc, red);
-  double total;
-  if (grid_sum_last(cta, partials, ticket, red, total) && threadIdx.x == 0) {
-    const double bn = sqrt(total);
-    sc->bnorm = bn;
-    sc->atol = fmax(0.0, sc->rtol * bn);
-    sc->rr = total;
-    sc->rho = sc->rho_prev = sc->pq = sc->alpha = sc->beta = 0.0;
-    sc->iter = 0;
-    sc->breakdown = 0;
-    const int zero_rhs = (bn == 0.0) || !(bn == bn);
-    sc->done = zero_rhs;
-    sc->converged = (bn == 0.0);
-    if (!(bn == bn)) sc->breakdown = 1;
-    hist[0] = bn;
-    // graph driver: the WHILE node that follows must not be entered for b == 0 (every body kernel would return
-    // at its `done` test and nobody would ever clear the loop condition)
-    if (sc->use_cond) cudaGraphSetConditional((cudaGraphConditionalHandle)sc->cond_handle, zero_rhs ? 0u : 1u);
-  }
-}
-
-// z = r (d == nullptr) or z = r / d ; rho = r.z
-__global__ void __launch_bounds__(VTHREADS) pcg_jacobi_kernel(const double* __restrict__ r, const double* __restrict__ d,
-                                                              double* __restrict__ z, int n, PcgScalars* sc,
-                                                              double* partials, unsigned* ticket) {
-  __shared__ double red[34];
-  if (sc->done) return;
-  double acc = 0.0;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const double rv = r[i];
-    const double zv = d ? rv / d[i] : rv;
-    z[i] = zv;
-    acc += rv * zv;
-  }
-  double cta = block_sum(acc, red);
-  double total;
-  if (grid_sum_last(cta, partials, ticket, red, total) && threadIdx.x == 0) pcg_final_scalar(sc, FINAL_RHO, total);
-}
-
-// The two vector kernels move 16 bytes per thread and access (double2) with two independent pairs in flight.
-__global__ void __launch_bounds__(VTHREADS) pcg_update_p_kernel(const double* __restrict__ z, double* __restrict__ p,
-                                                                int n, const PcgScalars* sc) {
-  if (sc->done) return;
-  const bool first = (sc->iter == 0);
-  const double beta = sc->beta;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  const long long n2 = n >> 1;
-  const double2* z2 = reinterpret_cast<const double2*>(z);
-  double2* p2 = reinterpret_cast<double2*>(p);
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
-    const double2 zv = z2[i];
-    // scipy: p *= beta; p += z  (two roundings, reproduced: no fma contraction)
-    double2 pv = zv;
-    if (!first) {
-      pv = p2[i];
-      pv.x = __dadd_rn(__dmul_rn(pv.x, beta), zv.x);
-      pv.y = __dadd_rn(__dmul_rn(pv.y, beta), zv.y);
-    }
-    p2[i] = pv;
-  }
-  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-    const double zv = z[n - 1];
-    p[n - 1] = first ? zv : __dadd_rn(__dmul_rn(p[n - 1], beta), zv);
-  }
-}
-
-__global__ void __launch_bounds__(VTHREADS) pcg_update_xr_kernel(double* __restrict__ x, double* __restrict__ r,
-                                                                 const double* __restrict__ p, const double* __restrict__ q,
-                                                                 int n, PcgScalars* sc, double* partials, unsigned* ticket,
-                                                                 double* hist) {
-  __shared__ double red[34];
-  if (sc->done) {  // never inside the loop of a healthy solve; keeps a WHILE body from spinning if it happens
-    if (sc->use_cond && blockIdx.x == 0 && threadIdx.x == 0)
-      cudaGraphSetConditional((cudaGraphConditionalHandle)sc->cond_handle, 0u);
-    return;
-  }
-  const double alpha = sc->alpha;
-  double acc = 0.0;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  const long long n2 = n >> 1;
-  double2* x2 = reinterpret_cast<double2*>(x);
-  double2* r2 = reinterpret_cast<double2*>(r);
-  const double2* p2 = reinterpret_cast<const double2*>(p);
-  const double2* q2 = reinterpret_cast<const double2*>(q);
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
-    // scipy: x += alpha*p ; r -= alpha*q  (product rounded, then add)
-    double2 xv = x2[i], rv = r2[i];
-    const double2 pv = p2[i], qv = q2[i];
-    xv.x = __dadd_rn(xv.x, __dmul_rn(alpha, pv.x));
-    xv.y = __dadd_rn(xv.y, __dmul_rn(alpha, pv.y));
-    rv.x = __dsub_rn(rv.x, __dmul_rn(alpha, qv.x));
-    rv.y = __dsub_rn(rv.y, __dmul_rn(alpha, qv.y));
-    x2[i] = xv;
-    r2[i] = rv;
-    acc += rv.x * rv.x;
-    acc += rv.y * rv.y;
-  }
-  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-    const int i = n - 1;
-    x[i] = __dadd_rn(x[i], __dmul_rn(alpha, p[i]));
-    const double rv = __dsub_rn(r[i], __dmul_rn(alpha, q[i]));
-    r[i] = rv;
-    acc += rv * rv;
-  }
-  double cta = block_sum(acc, red);
-  double total;
-  if (grid_sum_last(cta, partials, ticket, red, total) && threadIdx.x == 0) {
-    if (sc->breakdown || !(total == total)) {
-      sc->breakdown = 1;
-      sc->done = 1;
-    } else {
-      sc->rr = total;
-      sc->rho_prev = sc->rho;
-      const int it = sc->iter + 1;
-      sc->iter = it;
-      const double nrm = sqrt(total);
-      hist[it] = nrm;
-      if (nrm < sc->atol) {
-        sc->done = 1;
-        sc->converged = 1;
-      } else if (it >= sc->max_iter) {
-        sc->done = 1;
-      }
-    }
-    if (sc->use_cond) cudaGraphSetConditional((cudaGraphConditionalHandle)sc->cond_handle, sc->done ? 0u : 1u);
-  }
+  return v;
 }
 
 static int ensure_hist(b200spai_pcg_s* s, long long need) {
@@ -263,6 +124,7 @@ static int enqueue_iteration(b200spai_pcg_s* s, int precond, double* x, cudaStre
   pcg_update_p_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(s->z, s->p, s->n, s->sc);
   SpmvArgs a{};
   a.x = s->p;
+  a.aux = s->p;
   a.y = s->q;
   a.partials = s->partials;
   a.ticket = s->ticket;
@@ -341,7 +203,7 @@ static int solve_impl(b200spai_pcg_s* s, int precond, const double* b, double* x
   if (max_iter <= 0) max_iter = s->n;
   B2_TRY(ensure_hist(s, (long long)max_iter + 1));
   int mode = s->mode;
-  if (mode == 0) mode = 2;
+  if (mode == 0) mode = default_mode();
 
   PcgScalars init{};
   init.rtol = rtol;
@@ -563,7 +425,7 @@ int b200spai_pcg_profile_iterations(b200spai_pcg_t s, int precond, const double*
     pcg_update_p_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(s->z, s->p, s->n, s->sc);
     B2_CUDA(cudaEventRecord(e[3], st));
     SpmvArgs a{};
-    a.x = s->p; a.y = s->q; a.partials = s->partials; a.ticket = s->ticket; a.sc = s->sc; a.final_op = FINAL_PQ;
+    a.x = s->p; a.aux = s->p; a.y = s->q; a.partials = s->partials; a.ticket = s->ticket; a.sc = s->sc; a.final_op = FINAL_PQ;
     B2_TRY(spmv_launch(s->A, a, SPMV_DOT, 0, st));
     B2_CUDA(cudaEventRecord(e[4], st));
     pcg_update_xr_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(x, s->r, s->p, s->q, s->n, s->sc, s->partials, s->ticket,
