@@ -168,6 +168,40 @@ int b200spai_gnn_launch_count(b200spai_gnn_t m, int64_t* launches);
 int b200spai_graph_spmv_f32(b200spai_graph_t g, int32_t block_size, const float* values_dev, const float* x_dev,
                             const float* mask_dev, int32_t transpose, float* y_dev, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Device memory pool.  The library caches the device blocks it releases (a solve step allocates the same
+ * multi-GB blocks every time; cudaMalloc/cudaFree of those cost ~0.1 s per step).  Cached blocks are handed out
+ * again in the order of the one stream a handle works on.  Limit: B200SPAI_POOL_MAX_GB (default 64).
+ * ---------------------------------------------------------------------------------------------- */
+int b200spai_pool_trim(void);                      /* return every cached block to the driver (synchronises) */
+int b200spai_pool_cached_bytes(int64_t* bytes);
+
+/* ------------------------------------------------------------------------------------------------
+ * Row-partitioned PCG of ONE system over the GPUs of an NVSwitch box (one process per GPU).  Not in the
+ * reference (it is single-process); the solve is the same recurrence as b200spai_pcg_solve_dev, with the rows of
+ * A, G and G^T split into contiguous blocks, halos pushed over NVLink by peer stores and the CG scalars all-reduced
+ * through peer memory in rank order (bit-identical on every rank).  See DESIGN.md section 6.
+ *   1. every rank: b200spai_dist_create (allocates the peer-visible segment) and b200spai_dist_ipc_handle;
+ *   2. the caller gathers the 64-byte handles and the per-rank layout {row_start, row_end, shift, hi} from all ranks
+ *      (torch.distributed.all_gather) and passes them to b200spai_dist_connect;
+ *   3. local matrices = rows [row_start, row_end) with columns shifted by -shift (b200spai_csr_slice_rows);
+ *   4. b200spai_dist_pcg_solve on every rank (collective: all ranks must call it with the same arguments).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct b200spai_dist_s* b200spai_dist_t;
+int b200spai_dist_create(int32_t rank, int32_t world, int64_t ext_cap, b200spai_dist_t* out);
+int b200spai_dist_ipc_handle(b200spai_dist_t d, unsigned char* handle64);
+int b200spai_dist_connect(b200spai_dist_t d, const unsigned char* handles, const int64_t* layout);
+int b200spai_dist_info(b200spai_dist_t d, int32_t* n_push, int32_t* n_recv, int64_t* push_elems, int32_t* owned_offset);
+int b200spai_csr_slice_rows(b200spai_csr_t a, int32_t r0, int32_t r1, int64_t shift, int32_t n_cols_local, void* stream,
+                            b200spai_csr_t* out);
+int b200spai_dist_pcg_setup(b200spai_dist_t d, b200spai_csr_t a_local, b200spai_csr_t g_local, b200spai_csr_t gt_local,
+                            double epsilon);
+int b200spai_dist_pcg_set_mode(b200spai_dist_t d, int mode);
+/* b / x: the owned rows only.  max_iter must be given (> 0).  resid_hist_dev: NULL or max_iter+1 doubles. */
+int b200spai_dist_pcg_solve(b200spai_dist_t d, int precond, const double* b_local_dev, double* x_local_dev, double rtol,
+                            int32_t max_iter, double* resid_hist_dev, void* stream, b200spai_pcg_result* result);
+int b200spai_dist_destroy(b200spai_dist_t d);
+
 #ifdef __cplusplus
 }
 #endif

@@ -122,7 +122,7 @@ extern "C" int b200spai_edges_to_csr(int64_t num_nodes, int64_t num_edges, int32
   size_t tmp_bytes = 0;
   B2_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, counts, counts, (int)(n + 1), st));
   void* tmp = nullptr;
-  B2_CUDA(cudaMalloc(&tmp, tmp_bytes + 16));
+  B2_CUDA(pool_malloc(&tmp, tmp_bytes + 16));
   B2_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, counts, counts, (int)(n + 1), st));
   int h_bad = 0, h_nnz = 0;
   B2_CUDA(cudaMemcpyAsync(&h_bad, bad, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -149,10 +149,10 @@ extern "C" int b200spai_edges_to_csr(int64_t num_nodes, int64_t num_edges, int32
     }
   }
   count_launches(4);
-  cudaFree(tmp);
-  cudaFree(bad);
-  cudaFree(brp);
-  cudaFree(counts);
+  dev_free(tmp);
+  dev_free(bad);
+  dev_free(brp);
+  dev_free(counts);
   if (!rc) *out = A;
   return rc;
 }

@@ -40,11 +40,19 @@ void count_launches(long long n);  // process-wide tally of this library's kerne
 
 #define B2_LAUNCH_CHECK() B2_CUDA(cudaGetLastError())
 
+// Device memory comes from a per-device caching pool (csr.cu): a solve step allocates and releases the same few
+// multi-GB blocks every time, and cudaMalloc / cudaFree of those cost ~100 ms per step (cudaFree also synchronises
+// the device).  Blocks are reused in the order of the ONE stream a handle works on (include/b200spai.h), which is what
+// makes handing a just-released block to the next allocation safe.  b200spai_pool_trim() returns cached blocks.
+cudaError_t pool_malloc(void** p, size_t bytes);
+void pool_free(void* p);
+
 template <typename T>
 inline int dev_alloc(T** p, size_t count) {
-  B2_CUDA(cudaMalloc((void**)p, (count ? count : 1) * sizeof(T)));
+  B2_CUDA(::b200spai::pool_malloc((void**)p, (count ? count : 1) * sizeof(T)));
   return 0;
 }
+inline void dev_free(void* p) { ::b200spai::pool_free(p); }
 
 static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 

@@ -3,6 +3,10 @@
 
 #include <atomic>
 #include <cstdlib>
+#include <map>
+#include <mutex>
+#include <unordered_map>
+#include <vector>
 
 #include "csr.h"
 
@@ -26,6 +30,80 @@ int sm_count() {
     cached[dev] = n;
   }
   return cached[dev];
+}
+
+// ---- caching device-memory pool ------------------------------------------------------------------------------
+namespace {
+struct Pool {
+  std::mutex mu;
+  std::unordered_map<void*, std::pair<size_t, int>> live;            // ptr -> (bytes, device)
+  std::map<std::pair<int, size_t>, std::vector<void*>> free_blocks;  // (device, bytes) -> cached blocks
+  size_t cached = 0, limit = 0;
+};
+Pool& pool() {
+  static Pool* p = new Pool();  // leaked on purpose: handles may be destroyed after static destructors ran
+  return *p;
+}
+size_t pool_limit() {
+  Pool& P = pool();
+  if (P.limit == 0) {
+    const char* e = getenv("B200SPAI_POOL_MAX_GB");
+    const double gb = e ? atof(e) : 64.0;
+    P.limit = (size_t)((gb < 0 ? 0 : gb) * (double)(1ull << 30)) + 1;
+  }
+  return P.limit;
+}
+size_t round_size(size_t bytes) { return (bytes + 511) & ~(size_t)511; }
+}  // namespace
+
+cudaError_t pool_malloc(void** p, size_t bytes) {
+  Pool& P = pool();
+  bytes = round_size(bytes ? bytes : 1);
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  {
+    std::lock_guard<std::mutex> lock(P.mu);
+    auto it = P.free_blocks.find({dev, bytes});
+    if (it != P.free_blocks.end() && !it->second.empty()) {
+      *p = it->second.back();
+      it->second.pop_back();
+      P.cached -= bytes;
+      P.live[*p] = {bytes, dev};
+      return cudaSuccess;
+    }
+  }
+  e = cudaMalloc(p, bytes);
+  if (e != cudaSuccess) {  // out of memory: give the cache back and try once more
+    cudaGetLastError();
+    b200spai_pool_trim();
+    e = cudaMalloc(p, bytes);
+    if (e != cudaSuccess) return e;
+  }
+  std::lock_guard<std::mutex> lock(P.mu);
+  P.live[*p] = {bytes, dev};
+  return cudaSuccess;
+}
+
+void pool_free(void* p) {
+  if (!p) return;
+  Pool& P = pool();
+  const size_t limit = pool_limit();
+  {
+    std::lock_guard<std::mutex> lock(P.mu);
+    auto it = P.live.find(p);
+    if (it != P.live.end()) {
+      const size_t bytes = it->second.first;
+      const int dev = it->second.second;
+      P.live.erase(it);
+      if (P.cached + bytes <= limit) {
+        P.free_blocks[{dev, bytes}].push_back(p);
+        P.cached += bytes;
+        return;
+      }
+    }
+  }
+  cudaFree(p);  // over the cache limit, or not ours
 }
 
 static constexpr int PAD = 16;  // elements of slack behind every CSR array (bulk-copy over-read)
@@ -54,16 +132,16 @@ int csr_alloc(int n_rows, int n_cols, long long nnz, b200spai_csr_s** out) {
 
 void csr_free(b200spai_csr_s* a) {
   if (!a) return;
-  cudaFree(a->rowptr);
-  cudaFree(a->col);
-  cudaFree(a->val);
-  cudaFree(a->val32);
-  cudaFree(a->col16);
-  cudaFree(a->rowfirst);
-  cudaFree(a->blk[0]);
-  cudaFree(a->blk[1]);
-  cudaFree(a->blk[2]);
-  cudaFree(a->blk[3]);
+  dev_free(a->rowptr);
+  dev_free(a->col);
+  dev_free(a->val);
+  dev_free(a->val32);
+  dev_free(a->col16);
+  dev_free(a->rowfirst);
+  dev_free(a->blk[0]);
+  dev_free(a->blk[1]);
+  dev_free(a->blk[2]);
+  dev_free(a->blk[3]);
   delete a;
 }
 
@@ -106,7 +184,7 @@ int build_row_blocks(const int* rowptr, int n_rows, long long nnz, long long tar
   B2_LAUNCH_CHECK();
   count_launches(2);
   B2_CUDA(cudaStreamSynchronize(stream));
-  cudaFree(bounds);
+  dev_free(bounds);
   return 0;
 }
 
@@ -162,9 +240,9 @@ int csr_ensure_f32(b200spai_csr_s* A, cudaStream_t stream) {
   int h = 0;
   B2_CUDA(cudaMemcpyAsync(&h, lossy, sizeof(int), cudaMemcpyDeviceToHost, stream));
   B2_CUDA(cudaStreamSynchronize(stream));
-  cudaFree(lossy);
+  dev_free(lossy);
   if (h) {
-    cudaFree(A->val32);
+    dev_free(A->val32);
     A->val32 = nullptr;
     A->f32_state = -1;
   } else {
@@ -221,10 +299,10 @@ int csr_ensure_col16(b200spai_csr_s* A, cudaStream_t stream) {
   int h = 0;
   B2_CUDA(cudaMemcpyAsync(&h, bad, sizeof(int), cudaMemcpyDeviceToHost, stream));
   B2_CUDA(cudaStreamSynchronize(stream));
-  cudaFree(bad);
+  dev_free(bad);
   if (h) {
-    cudaFree(A->col16);
-    cudaFree(A->rowfirst);
+    dev_free(A->col16);
+    dev_free(A->rowfirst);
     A->col16 = nullptr;
     A->rowfirst = nullptr;
     A->c16_state = -1;
@@ -402,18 +480,18 @@ static int csr_transpose_impl(b200spai_csr_s* A, cudaStream_t stream, b200spai_c
     size_t scan_bytes = 0;
     B2_CUDA(cub::DeviceScan::InclusiveSum(nullptr, scan_bytes, T->rowptr, T->rowptr, A->n_cols + 1, stream));
     void* tmp = nullptr;
-    B2_CUDA(cudaMalloc(&tmp, (tmp_bytes > scan_bytes ? tmp_bytes : scan_bytes) + 16));
+    B2_CUDA(pool_malloc(&tmp, (tmp_bytes > scan_bytes ? tmp_bytes : scan_bytes) + 16));
     B2_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, A->col, keys_out, iota, perm, (int)nnz, 0, end_bit, stream));
     B2_CUDA(cub::DeviceScan::InclusiveSum(tmp, scan_bytes, T->rowptr, T->rowptr, A->n_cols + 1, stream));
     gather_transposed_kernel<<<(unsigned)((nnz + tb - 1) / tb), tb, 0, stream>>>(perm, rowidx, A->val, nnz, T->col, T->val);
     B2_LAUNCH_CHECK();
     count_launches(4);  // + the cub sort / scan passes, which are library kernels and not counted
     B2_CUDA(cudaStreamSynchronize(stream));
-    cudaFree(tmp);
-    cudaFree(rowidx);
-    cudaFree(iota);
-    cudaFree(keys_out);
-    cudaFree(perm);
+    dev_free(tmp);
+    dev_free(rowidx);
+    dev_free(iota);
+    dev_free(keys_out);
+    dev_free(perm);
   }
   *out = T;
   return 0;
@@ -439,6 +517,30 @@ extern "C" {
 
 const char* b200spai_last_error(void) { return last_error().c_str(); }
 int b200spai_version(void) { return 101; }
+
+int b200spai_pool_trim(void) {
+  std::vector<void*> blocks;
+  {
+    Pool& P = pool();
+    std::lock_guard<std::mutex> lock(P.mu);
+    for (auto& kv : P.free_blocks) {
+      blocks.insert(blocks.end(), kv.second.begin(), kv.second.end());
+      kv.second.clear();
+    }
+    P.cached = 0;
+  }
+  cudaDeviceSynchronize();  // a cached block may still be read by work enqueued before its release
+  for (void* b : blocks) cudaFree(b);
+  return 0;
+}
+
+int b200spai_pool_cached_bytes(int64_t* bytes) {
+  B2_ARG(bytes, "pool_cached_bytes: NULL argument");
+  Pool& P = pool();
+  std::lock_guard<std::mutex> lock(P.mu);
+  *bytes = (int64_t)P.cached;
+  return 0;
+}
 
 /* development hook (not in the public header): cycle counters of the streaming SpMV when built with -DB200SPAI_PROBE */
 int b200spai_debug_probe(unsigned long long* out8, int reset) {

@@ -332,49 +332,374 @@ static int dist_warm(b200spai_dist_s* s, int precond, cudaStream_t st) {
   return 0;
 }
 
-static int dist_build_graph(b200spai_dist_s* s, int precond, cudaStream_t st) {
-  if (s->exec[precond]) return 0;
-  cudaGraph_t graph = nullptr;
-  cudaStream_t cs = s->cap_stream;
-  B2_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeRelaxed));
-  int nl0 = 0;
-  int rc = dist_enqueue_init(s, s->bw, s->xw, cs, &nl0);
-  if (rc) {
-    cudaGraph_t junk = nullptr;
-    cudaStreamEndCapture(cs, &junk);
-    if (junk) cudaGraphDestroy(junk);
-    return rc;
+}  // namespace b200spai
+
+// =================================================================================================================
+// C ABI
+// =================================================================================================================
+extern "C" {
+
+int b200spai_dist_create(int32_t rank, int32_t world, int64_t ext_cap, b200spai_dist_t* out) {
+  B2_ARG(out && world >= 1 && world <= MAXR && rank >= 0 && rank < world && ext_cap > 0, "dist_create: bad argument");
+  auto* s = new b200spai_dist_s();
+  s->rank = rank;
+  s->world = world;
+  s->ext_cap = (ext_cap + 31) & ~31LL;
+  s->seg_bytes = SEG_VEC_OFFSET + (size_t)NVEC * (size_t)s->ext_cap * sizeof(double);
+  // plain cudaMalloc (not the pool): the segment is exported to the peer processes through CUDA IPC
+  cudaError_t e = cudaMalloc((void**)&s->seg, s->seg_bytes);
+  if (e == cudaSuccess) e = cudaMemset(s->seg, 0, s->seg_bytes);
+  if (e != cudaSuccess) {
+    set_error(std::string("dist_create: ") + cudaGetErrorString(e));
+    delete s;
+    return B200SPAI_ERR_CUDA;
   }
-  cudaStreamCaptureStatus status;
-  const cudaGraphNode_t* deps = nullptr;
-  size_t ndeps = 0;
-  B2_CUDA(cudaStreamGetCaptureInfo(cs, &status, nullptr, &graph, &deps, &ndeps));
-  cudaGraphConditionalHandle handle = (cudaGraphConditionalHandle)s->cond[precond];
-  cudaGraphNodeParams cp = {};
-  cp.type = cudaGraphNodeTypeConditional;
-  cp.conditional.handle = handle;
-  cp.conditional.type = cudaGraphCondTypeWhile;
-  cp.conditional.size = 1;
-  cudaGraphNode_t cnode;
-  B2_CUDA(cudaGraphAddNode(&cnode, graph, deps, ndeps, &cp));
-  cudaGraph_t body = cp.conditional.phGraph_out[0];
-  B2_CUDA(cudaStreamUpdateCaptureDependencies(cs, &cnode, 1, cudaStreamSetCaptureDependencies));
-  int nl = 0;
-  B2_CUDA(cudaStreamBeginCaptureToGraph(s->body_stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
-  rc = dist_enqueue_iteration(s, precond, s->xw, s->body_stream, &nl);
-  cudaGraph_t body_out = nullptr;
-  cudaError_t e1 = cudaStreamEndCapture(s->body_stream, &body_out);
-  cudaGraph_t full = nullptr;
-  cudaError_t e2 = cudaStreamEndCapture(cs, &full);
-  if (rc) return rc;
-  B2_CUDA(e1);
-  B2_CUDA(e2);
-  cudaGraphExec_t exec = nullptr;
-  B2_CUDA(cudaGraphInstantiate(&exec, full, 0));
-  s->graph[precond] = full;
-  s->exec[precond] = exec;
-  s->launches_per_iter[precond] = nl;
+  s->peer_seg[rank] = s->seg;
+  *out = s;
   return 0;
 }
 
-}  // namespace b200spai
+int b200spai_dist_ipc_handle(b200spai_dist_t s, unsigned char* handle64) {
+  B2_ARG(s && handle64, "dist_ipc_handle: NULL argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handles are 64 bytes");
+  cudaIpcMemHandle_t h;
+  B2_CUDA(cudaIpcGetMemHandle(&h, s->seg));
+  memcpy(handle64, &h, 64);
+  return 0;
+}
+
+// handles: [world][64] as gathered from every rank; layout: [world][4] = {row_start, row_end, shift, hi} per rank
+// (extended range [shift, hi); shift may be row-aligned down by one so that the owned slice starts 16-byte aligned).
+int b200spai_dist_connect(b200spai_dist_t s, const unsigned char* handles, const int64_t* layout) {
+  B2_ARG(s && layout && (handles || s->world == 1), "dist_connect: NULL argument");
+  B2_ARG(!s->connected, "dist_connect: already connected");
+  const int R = s->world, me = s->rank;
+  for (int q = 0; q < R; ++q) {
+    if (q == me) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handles + (size_t)q * 64, 64);
+    B2_CUDA(cudaIpcOpenMemHandle(&s->peer_seg[q], h, cudaIpcMemLazyEnablePeerAccess));
+  }
+  const int64_t* L = layout;
+  s->rs = L[me * 4 + 0];
+  s->re = L[me * 4 + 1];
+  s->shift = L[me * 4 + 2];
+  s->hi = L[me * 4 + 3];
+  B2_ARG(s->rs <= s->re && s->shift <= s->rs && s->hi >= s->re, "dist_connect: inconsistent layout");
+  B2_ARG(s->hi - s->shift <= s->ext_cap, "dist_connect: extended range exceeds the segment capacity");
+  B2_ARG(((s->rs - s->shift) & 1) == 0, "dist_connect: the owned slice must start at an even extended index");
+  s->n = (int)(s->re - s->rs);
+  s->off = (int)(s->rs - s->shift);
+  DistCtx& c = s->ctx;
+  c = DistCtx{};
+  c.rank = me;
+  c.world = R;
+  for (int q = 0; q < R; ++q) {
+    auto* base = reinterpret_cast<unsigned char*>(s->peer_seg[q]);
+    c.hdr[q] = reinterpret_cast<SegHeader*>(base);
+    for (int v = 0; v < NVEC; ++v)
+      c.vec[v][q] = reinterpret_cast<double*>(base + SEG_VEC_OFFSET) + (size_t)v * (size_t)s->ext_cap;
+  }
+  for (int q = 0; q < R; ++q) {
+    if (q == me) continue;
+    const int64_t rs_q = L[q * 4 + 0], re_q = L[q * 4 + 1], lo_q = L[q * 4 + 2], hi_q = L[q * 4 + 3];
+    // what q needs from my owned rows
+    const int64_t a = std::max<int64_t>(s->rs, lo_q), b = std::min<int64_t>(s->re, hi_q);
+    if (a < b) {
+      const int k = c.n_push++;
+      c.push_peer[k] = q;
+      c.push_dst_off[k] = a - lo_q;
+      c.push_src_off[k] = a - s->shift;
+      c.push_len[k] = (int)(b - a);
+    }
+    // what I need from q's owned rows
+    const int64_t a2 = std::max<int64_t>(rs_q, s->shift), b2 = std::min<int64_t>(re_q, s->hi);
+    if (a2 < b2) c.recv_peer[c.n_recv++] = q;
+  }
+  // local solver state
+  const size_t n = (size_t)(s->n > 0 ? s->n : 1);
+  int rc = 0;
+  for (double** v : {&s->z, &s->q, &s->xw, &s->bw})
+    if (!rc) rc = dev_alloc(v, n + 2);
+  if (!rc) rc = dev_alloc(&s->sc, 1);
+  if (!rc) rc = dev_alloc(&s->partials, 8192);
+  if (!rc) rc = dev_alloc(&s->ticket, 1);
+  if (!rc) rc = dev_alloc(&s->ticket_halo, 1);
+  if (!rc) rc = dev_alloc(&s->epoch, NVEC + NRED);
+  if (rc) return rc;
+  B2_CUDA(cudaMemset(s->ticket, 0, sizeof(unsigned)));
+  B2_CUDA(cudaMemset(s->ticket_halo, 0, sizeof(unsigned)));
+  B2_CUDA(cudaMemset(s->epoch, 0, (NVEC + NRED) * sizeof(unsigned long long)));
+  B2_CUDA(cudaMemset(s->sc, 0, sizeof(PcgScalars)));
+  B2_CUDA(cudaMallocHost((void**)&s->h_in, sizeof(PcgScalars)));
+  B2_CUDA(cudaMallocHost((void**)&s->h_out, sizeof(PcgScalars)));
+  B2_CUDA(cudaMallocHost((void**)&s->h_done, 2 * sizeof(int)));
+  B2_CUDA(cudaEventCreate(&s->ev0));
+  B2_CUDA(cudaEventCreate(&s->ev1));
+  B2_CUDA(cudaEventCreateWithFlags(&s->ev_chunk[0], cudaEventDisableTiming));
+  B2_CUDA(cudaEventCreateWithFlags(&s->ev_chunk[1], cudaEventDisableTiming));
+  B2_CUDA(cudaStreamCreateWithFlags(&s->body_stream, cudaStreamNonBlocking));
+  B2_CUDA(cudaStreamCreateWithFlags(&s->cap_stream, cudaStreamNonBlocking));
+  c.epoch = s->epoch;
+  c.ticket = s->ticket_halo;
+  c.sc = s->sc;
+  c.hist = nullptr;
+  int khz = 1965000;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
+  const char* e = getenv("B200SPAI_DIST_TIMEOUT_S");
+  const double secs = e ? atof(e) : 10.0;
+  c.spin_limit = (long long)(secs * 1e3 * (double)khz);
+  s->connected = true;
+  return 0;
+}
+
+int b200spai_dist_info(b200spai_dist_t s, int32_t* n_push, int32_t* n_recv, int64_t* push_elems, int32_t* owned_offset) {
+  B2_ARG(s && s->connected, "dist_info: not connected");
+  if (n_push) *n_push = s->ctx.n_push;
+  if (n_recv) *n_recv = s->ctx.n_recv;
+  if (push_elems) {
+    int64_t t = 0;
+    for (int i = 0; i < s->ctx.n_push; ++i) t += s->ctx.push_len[i];
+    *push_elems = t;
+  }
+  if (owned_offset) *owned_offset = s->off;
+  return 0;
+}
+
+/* Rows [r0, r1) of `a` as a new matrix with n_cols_local columns, every column index shifted by -shift. */
+int b200spai_csr_slice_rows(b200spai_csr_t a, int32_t r0, int32_t r1, int64_t shift, int32_t n_cols_local, void* stream,
+                            b200spai_csr_t* out) {
+  B2_ARG(a && out && r0 >= 0 && r0 <= r1 && r1 <= a->n_rows && n_cols_local >= 0, "csr_slice_rows: bad argument");
+  cudaStream_t st = as_stream(stream);
+  int h[2] = {0, 0};
+  B2_CUDA(cudaMemcpyAsync(&h[0], a->rowptr + r0, sizeof(int), cudaMemcpyDeviceToHost, st));
+  B2_CUDA(cudaMemcpyAsync(&h[1], a->rowptr + r1, sizeof(int), cudaMemcpyDeviceToHost, st));
+  B2_CUDA(cudaStreamSynchronize(st));
+  const long long cnt = (long long)h[1] - h[0];
+  b200spai_csr_s* L = nullptr;
+  B2_TRY(csr_alloc(r1 - r0, n_cols_local, cnt, &L));
+  int* bad = nullptr;
+  B2_TRY(dev_alloc(&bad, 1));
+  B2_CUDA(cudaMemsetAsync(bad, 0, sizeof(int), st));
+  const int nl = r1 - r0;
+  slice_rowptr_kernel<<<(nl + 1 + 255) / 256, 256, 0, st>>>(a->rowptr, r0, nl, L->rowptr);
+  if (cnt > 0) {
+    long long g = (cnt + 1023) / 1024;
+    if (g > (long long)sm_count() * 8) g = (long long)sm_count() * 8;
+    slice_entries_kernel<<<(int)g, 256, 0, st>>>(a->col, a->val, h[0], cnt, (int)shift, n_cols_local, L->col, L->val, bad);
+  }
+  B2_LAUNCH_CHECK();
+  count_launches(cnt > 0 ? 2 : 1);
+  int hb = 0;
+  B2_CUDA(cudaMemcpyAsync(&hb, bad, sizeof(int), cudaMemcpyDeviceToHost, st));
+  B2_CUDA(cudaStreamSynchronize(st));
+  dev_free(bad);
+  if (hb) {
+    csr_free(L);
+    set_error("csr_slice_rows: a column falls outside [shift, shift + n_cols_local)");
+    return B200SPAI_ERR_ARG;
+  }
+  *out = L;
+  return 0;
+}
+
+int b200spai_dist_pcg_setup(b200spai_dist_t s, b200spai_csr_t a_local, b200spai_csr_t g_local, b200spai_csr_t gt_local,
+                            double epsilon) {
+  B2_ARG(s && s->connected && a_local, "dist_pcg_setup: not connected or NULL matrix");
+  const int ext = (int)(s->hi - s->shift);
+  B2_ARG(a_local->n_rows == s->n && a_local->n_cols == ext, "dist_pcg_setup: A_local must be [owned rows x extended range]");
+  if (g_local || gt_local) {
+    B2_ARG(g_local && gt_local, "dist_pcg_setup: G and G^T come together");
+    B2_ARG(g_local->n_rows == s->n && g_local->n_cols == ext && gt_local->n_rows == s->n && gt_local->n_cols == ext,
+           "dist_pcg_setup: G_local / GT_local must be [owned rows x extended range]");
+  }
+  s->A = a_local;
+  s->G = g_local;
+  s->GT = gt_local;
+  s->eps = epsilon;
+  s->have_d = false;
+  dist_drop_graphs(s);
+  return 0;
+}
+
+int b200spai_dist_pcg_set_mode(b200spai_dist_t s, int mode) {
+  B2_ARG(s && mode >= 0 && mode <= 2, "dist_pcg_set_mode: mode must be 0, 1 or 2");
+  s->mode = mode;
+  return 0;
+}
+
+int b200spai_dist_pcg_solve(b200spai_dist_t s, int precond, const double* b_local_dev, double* x_local_dev, double rtol,
+                            int32_t max_iter, double* resid_hist_dev, void* stream, b200spai_pcg_result* res) {
+  B2_ARG(s && s->connected && s->A && b_local_dev && x_local_dev && res && max_iter > 0, "dist_pcg_solve: bad argument");
+  B2_ARG(precond >= 0 && precond <= 3, "dist_pcg_solve: unknown preconditioner");
+  if (precond >= B200SPAI_PRECOND_EXT_SPAI) B2_ARG(s->G && s->GT, "dist_pcg_solve: ext_spai needs G and G^T");
+  cudaStream_t st = as_stream(stream);
+  if ((precond == B200SPAI_PRECOND_DIAGONAL || precond == B200SPAI_PRECOND_EXT_SPAI_SCALED) && !s->have_d) {
+    if (!s->d) B2_TRY(dev_alloc(&s->d, (size_t)(s->n > 0 ? s->n : 1)));
+    if (s->n > 0) dist_diagonal_kernel<<<(s->n + 255) / 256, 256, 0, st>>>(s->A->view(), s->off, s->d);
+    B2_LAUNCH_CHECK();
+    s->have_d = true;
+  }
+  B2_TRY(dist_ensure_hist(s, (long long)max_iter + 1));
+  int mode = s->mode;
+  if (mode == 0) {
+    const char* e = getenv("B200SPAI_PCG_MODE");
+    mode = (e && atoi(e) == 1) ? 1 : 2;
+  }
+  B2_TRY(dist_warm(s, precond, st));
+  PcgScalars init{};
+  init.rtol = rtol;
+  init.max_iter = max_iter;
+  init.dist = 1;
+  if (mode == 2) init.use_cond = 1;
+  const size_t nbytes = (size_t)s->n * sizeof(double);
+  int nl_init = 0;
+  if (mode == 2) {
+    if (!s->exec[precond]) {
+      // one graph = init (+ its all-reduce and the first r halo) followed by a device-side WHILE over the iteration body
+      cudaStream_t cs = s->cap_stream;
+      cudaGraph_t graph = nullptr;
+      B2_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeRelaxed));
+      cudaStreamCaptureStatus status;
+      B2_CUDA(cudaStreamGetCaptureInfo(cs, &status, nullptr, &graph, nullptr, nullptr));
+      cudaGraphConditionalHandle handle;
+      cudaError_t eh = cudaGraphConditionalHandleCreate(&handle, graph, 1, cudaGraphCondAssignDefault);
+      if (eh != cudaSuccess) {
+        cudaGraph_t junk = nullptr;
+        cudaStreamEndCapture(cs, &junk);
+        if (junk) cudaGraphDestroy(junk);
+        B2_CUDA(eh);
+      }
+      s->cond[precond] = (unsigned long long)handle;
+      // continue the same capture: init + WHILE(body)
+      int nl0 = 0;
+      int rc = dist_enqueue_init(s, s->bw, s->xw, cs, &nl0);
+      const cudaGraphNode_t* deps = nullptr;
+      size_t ndeps = 0;
+      cudaError_t e0 = cudaStreamGetCaptureInfo(cs, &status, nullptr, &graph, &deps, &ndeps);
+      cudaGraphNodeParams cp = {};
+      cp.type = cudaGraphNodeTypeConditional;
+      cp.conditional.handle = handle;
+      cp.conditional.type = cudaGraphCondTypeWhile;
+      cp.conditional.size = 1;
+      cudaGraphNode_t cnode;
+      cudaError_t e1 = (rc == 0 && e0 == cudaSuccess) ? cudaGraphAddNode(&cnode, graph, deps, ndeps, &cp) : cudaErrorUnknown;
+      int nl = 0;
+      cudaError_t e2 = cudaErrorUnknown, e3 = cudaErrorUnknown;
+      if (e1 == cudaSuccess) {
+        cudaGraph_t body = cp.conditional.phGraph_out[0];
+        e2 = cudaStreamUpdateCaptureDependencies(cs, &cnode, 1, cudaStreamSetCaptureDependencies);
+        if (e2 == cudaSuccess) e2 = cudaStreamBeginCaptureToGraph(s->body_stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed);
+        if (e2 == cudaSuccess) {
+          rc = dist_enqueue_iteration(s, precond, s->xw, s->body_stream, &nl);
+          cudaGraph_t body_out = nullptr;
+          e3 = cudaStreamEndCapture(s->body_stream, &body_out);
+        }
+      }
+      cudaGraph_t full = nullptr;
+      cudaError_t e4 = cudaStreamEndCapture(cs, &full);
+      if (rc) return rc;
+      B2_CUDA(e0);
+      B2_CUDA(e1);
+      B2_CUDA(e2);
+      B2_CUDA(e3);
+      B2_CUDA(e4);
+      cudaGraphExec_t exec = nullptr;
+      B2_CUDA(cudaGraphInstantiate(&exec, full, 0));
+      s->graph[precond] = full;
+      s->exec[precond] = exec;
+      s->launches_per_iter[precond] = nl;
+      nl_init = nl0;
+    }
+    init.cond_handle = s->cond[precond];
+  }
+  *s->h_in = init;
+  B2_CUDA(cudaEventRecord(s->ev0, st));
+  B2_CUDA(cudaMemcpyAsync(s->sc, s->h_in, sizeof(PcgScalars), cudaMemcpyHostToDevice, st));
+  if (mode == 2) {
+    if (s->n > 0) B2_CUDA(cudaMemcpyAsync(s->bw, b_local_dev, nbytes, cudaMemcpyDeviceToDevice, st));
+    B2_CUDA(cudaGraphLaunch(s->exec[precond], st));
+    if (s->n > 0) B2_CUDA(cudaMemcpyAsync(x_local_dev, s->xw, nbytes, cudaMemcpyDeviceToDevice, st));
+  } else {
+    double* xs = ((reinterpret_cast<uintptr_t>(x_local_dev) & 15) == 0) ? x_local_dev : s->xw;
+    int nl = 0;
+    B2_TRY(dist_enqueue_init(s, b_local_dev, xs, st, &nl));
+    const int CH = 8;
+    int slot = 0;
+    long long enq = 0;
+    bool first = true;
+    s->h_done[0] = s->h_done[1] = 0;
+    while (true) {
+      for (int k = 0; k < CH; ++k) B2_TRY(dist_enqueue_iteration(s, precond, xs, st, &nl));
+      enq += CH;
+      B2_CUDA(cudaMemcpyAsync(s->h_done + slot, &s->sc->done, sizeof(int), cudaMemcpyDeviceToHost, st));
+      B2_CUDA(cudaEventRecord(s->ev_chunk[slot], st));
+      slot ^= 1;
+      if (first) {
+        first = false;
+        if (enq < (long long)max_iter + CH) continue;
+      }
+      // every rank reads the SAME flag values (the scalars are bit-identical), so all ranks stop after the same chunk
+      B2_CUDA(cudaEventSynchronize(s->ev_chunk[slot]));
+      if (s->h_done[slot]) break;
+      if (enq >= (long long)max_iter + 2 * CH) break;
+    }
+    if (xs != x_local_dev && s->n > 0) B2_CUDA(cudaMemcpyAsync(x_local_dev, xs, nbytes, cudaMemcpyDeviceToDevice, st));
+    s->launches += nl;
+    count_launches(nl);
+  }
+  B2_CUDA(cudaEventRecord(s->ev1, st));
+  B2_CUDA(cudaMemcpyAsync(s->h_out, s->sc, sizeof(PcgScalars), cudaMemcpyDeviceToHost, st));
+  B2_CUDA(cudaStreamSynchronize(st));
+  const PcgScalars& o = *s->h_out;
+  if (mode == 2) {
+    const long long nl = 3 + (long long)s->launches_per_iter[precond] * (o.iter > 0 ? o.iter : 1);
+    (void)nl_init;
+    s->launches += nl;
+    count_launches(nl);
+  }
+  res->iterations = o.iter;
+  res->converged = o.converged;
+  res->breakdown = o.breakdown;
+  res->reserved = mode;
+  res->b_norm = o.bnorm;
+  res->final_residual = sqrt(o.rr);
+  res->setup_ms = 0.f;
+  B2_CUDA(cudaEventElapsedTime(&res->solve_ms, s->ev0, s->ev1));
+  if (resid_hist_dev)
+    B2_CUDA(cudaMemcpyAsync(resid_hist_dev, s->hist, ((size_t)o.iter + 1) * sizeof(double), cudaMemcpyDefault, st));
+  B2_CUDA(cudaStreamSynchronize(st));
+  if (o.breakdown == 3) {
+    set_error("dist_pcg_solve: a wait on a peer rank timed out (peer process gone?)");
+    return B200SPAI_ERR_CUDA;
+  }
+  return 0;
+}
+
+int b200spai_dist_destroy(b200spai_dist_t s) {
+  if (!s) return 0;
+  dist_drop_graphs(s);
+  for (int q = 0; q < s->world; ++q)
+    if (q != s->rank && s->peer_seg[q]) cudaIpcCloseMemHandle(s->peer_seg[q]);
+  cudaFree(s->seg);
+  for (double* v : {s->z, s->q, s->xw, s->bw, s->d, s->partials, s->hist}) dev_free(v);
+  dev_free(s->sc);
+  dev_free(s->ticket);
+  dev_free(s->ticket_halo);
+  dev_free(s->epoch);
+  if (s->h_in) cudaFreeHost(s->h_in);
+  if (s->h_out) cudaFreeHost(s->h_out);
+  if (s->h_done) cudaFreeHost(s->h_done);
+  if (s->ev0) cudaEventDestroy(s->ev0);
+  if (s->ev1) cudaEventDestroy(s->ev1);
+  if (s->ev_chunk[0]) cudaEventDestroy(s->ev_chunk[0]);
+  if (s->ev_chunk[1]) cudaEventDestroy(s->ev_chunk[1]);
+  if (s->body_stream) cudaStreamDestroy(s->body_stream);
+  if (s->cap_stream) cudaStreamDestroy(s->cap_stream);
+  delete s;
+  return 0;
+}
+
+}  // extern "C"

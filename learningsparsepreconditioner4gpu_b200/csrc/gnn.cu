@@ -94,17 +94,17 @@ __global__ void graph_segptr_kernel(const int* __restrict__ dst, long long E, lo
 
 static void graph_free(b200spai_graph_s* g) {
   if (!g) return;
-  cudaFree(g->perm);
-  cudaFree(g->src);
-  cudaFree(g->dst);
-  cudaFree(g->segptr);
-  cudaFree(g->rperm);
-  cudaFree(g->rcol);
-  cudaFree(g->rsegptr);
-  cudaFree(g->nb);
-  cudaFree(g->ef);
-  cudaFree(g->x0);
-  cudaFree(g->x1);
+  dev_free(g->perm);
+  dev_free(g->src);
+  dev_free(g->dst);
+  dev_free(g->segptr);
+  dev_free(g->rperm);
+  dev_free(g->rcol);
+  dev_free(g->rsegptr);
+  dev_free(g->nb);
+  dev_free(g->ef);
+  dev_free(g->x0);
+  dev_free(g->x1);
   delete g;
 }
 
@@ -130,10 +130,10 @@ static int graph_create_impl(long long N, long long E, const long long* edge_ind
   if (!rc) rc = dev_alloc(&iota, (size_t)E);
   if (!rc) rc = dev_alloc(&bad, 1);
   auto cleanup = [&]() {
-    cudaFree(keys);
-    cudaFree(iota);
-    cudaFree(bad);
-    cudaFree(tmp);
+    dev_free(keys);
+    dev_free(iota);
+    dev_free(bad);
+    dev_free(tmp);
   };
   if (rc) {
     cleanup();
@@ -152,7 +152,7 @@ static int graph_create_impl(long long N, long long E, const long long* edge_ind
     while (end_bit < 31 && (1LL << end_bit) < N) ++end_bit;
     size_t tmp_bytes = 0;
     e = cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, g->dst, iota, g->perm, (int)E, 0, end_bit, st);
-    if (e == cudaSuccess) e = cudaMalloc(&tmp, tmp_bytes + 16);
+    if (e == cudaSuccess) e = pool_malloc(&tmp, tmp_bytes + 16);
     if (e == cudaSuccess) e = cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, g->dst, iota, g->perm, (int)E, 0, end_bit, st);
     if (e == cudaSuccess) graph_src_kernel<<<(unsigned)((E + tb - 1) / tb), tb, 0, st>>>(row, g->perm, E, g->src);
     // the same, keyed on the row (identity permutation for the reference's row-major edge lists)
@@ -238,7 +238,7 @@ int b200spai_gnn_create(int32_t node_in, int32_t edge_in, int32_t block_size, in
   cudaError_t e = cudaMemcpy(m->blob, blob_host, (size_t)blob_len * sizeof(float), cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
     set_error(std::string("gnn_create: ") + cudaGetErrorString(e));
-    cudaFree(m->blob);
+    dev_free(m->blob);
     delete m;
     return B200SPAI_ERR_CUDA;
   }
@@ -248,7 +248,7 @@ int b200spai_gnn_create(int32_t node_in, int32_t edge_in, int32_t block_size, in
 
 int b200spai_gnn_destroy(b200spai_gnn_t m) {
   if (!m) return 0;
-  cudaFree(m->blob);
+  dev_free(m->blob);
   delete m;
   return 0;
 }

@@ -65,7 +65,7 @@ static int default_mode() {
 
 static int ensure_hist(b200spai_pcg_s* s, long long need) {
   if (need <= s->hist_cap) return 0;
-  cudaFree(s->hist);
+  dev_free(s->hist);
   s->hist = nullptr;
   B2_TRY(dev_alloc(&s->hist, (size_t)need));
   s->hist_cap = need;
@@ -359,8 +359,8 @@ int b200spai_pcg_solve_host(b200spai_pcg_t s, int precond, const double* b_host,
       rc = B200SPAI_ERR_CUDA;
     }
   }
-  cudaFree(bd);
-  cudaFree(xd);
+  dev_free(bd);
+  dev_free(xd);
   return rc;
 }
 
@@ -459,9 +459,9 @@ int b200spai_pcg_destroy(b200spai_pcg_t s) {
     if (s->graph[i]) cudaGraphDestroy(s->graph[i]);
   }
   if (s->GT) csr_free(s->GT);
-  for (double* v : {s->r, s->z, s->p, s->q, s->t, s->d, s->bw, s->xw, s->partials, s->hist}) cudaFree(v);
-  cudaFree(s->sc);
-  cudaFree(s->ticket);
+  for (double* v : {s->r, s->z, s->p, s->q, s->t, s->d, s->bw, s->xw, s->partials, s->hist}) dev_free(v);
+  dev_free(s->sc);
+  dev_free(s->ticket);
   if (s->h_in) cudaFreeHost(s->h_in);
   if (s->h_out) cudaFreeHost(s->h_out);
   if (s->h_done) cudaFreeHost(s->h_done);

@@ -1,0 +1,101 @@
+"""GPU tests of the row-partitioned solver (csrc/dist.cu) through the C ABI.
+
+world = 1 exercises the whole device path (extended layout, all-reduce and halo kernels with no peers, graph and stream
+drivers) on one GPU and must reproduce the single-GPU solver bit for bit; the multi-rank test runs
+tests/dist_worker.py under torchrun when the box has >= 2 GPUs (peer stores over NVLink, epoch flags)."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _system(grid=14):
+    from learningsparsepreconditioner4gpu_b200 import systems
+    from learningsparsepreconditioner4gpu_b200.neural_cg.utils.validate import to_csr_device
+
+    s = systems.poisson_sample(grid, seed=2, device="cuda")
+    ws = systems.default_workspace(s)
+    n = s.num_nodes
+    A = to_csr_device(s.edge_index, s.matrix_values, n, s.mask)
+    G = ws.inference_step_device(s)
+    rhs = A.matvec(s.mask.reshape(-1).double())
+    return s, ws, A, G, rhs
+
+
+@pytest.mark.parametrize("mode", [1, 2])
+@pytest.mark.parametrize("precond", ["ext_spai", "ext_spai_scaled", "none", "diagonal"])
+def test_world1_reproduces_single_gpu_solver(precond, mode):
+    from learningsparsepreconditioner4gpu_b200 import parallel as par
+    from learningsparsepreconditioner4gpu_b200.device import DevicePCG
+
+    s, ws, A, G, rhs = _system()
+    n = s.num_nodes
+    starts = par.partition_rows(par.row_weights_from_edges(s.edge_index, n), 1)
+    assert starts == [0, n]
+    spai = precond.startswith("ext_spai")
+    d = par.DistPCG(A, G if spai else None, ws.epsilon, starts, par.extended_range(s.edge_index, 0, n), rank=0, world=1, mode=mode)
+    x, res, hist = d.solve(rhs, precond, rtol=1e-8, history=True)
+    ref = DevicePCG(A, mode=mode)
+    if spai:
+        ref.set_spai(G, ws.epsilon)
+    x1, res1, hist1 = ref.solve(rhs, precond, rtol=1e-8, history=True)
+    assert res.converged == 1 and res.iterations == res1.iterations
+    assert torch.equal(hist, hist1)
+    assert torch.equal(x, x1)
+    assert d.info() == {"n_push": 0, "n_recv": 0, "push_elems": 0, "owned_offset": 0}
+    d.close()
+
+
+def test_slice_rows_matches_scipy():
+    import ctypes as C
+
+    from learningsparsepreconditioner4gpu_b200 import _lib
+    from learningsparsepreconditioner4gpu_b200.device import DeviceCSR, _stream
+
+    s, ws, A, G, rhs = _system(10)
+    As = A.to_scipy()
+    lib = _lib.load()
+    h = C.c_void_p()
+    r0, r1, shift, ncl = 200, 611, 57, 900
+    _lib.check(lib.b200spai_csr_slice_rows(A._h, r0, r1, shift, ncl, _stream(), C.byref(h)), "slice")
+    L = DeviceCSR(h).to_scipy()
+    ref = As[r0:r1, shift:shift + ncl]
+    assert L.shape == ref.shape and (abs(L - ref)).nnz == 0 and L.nnz == As[r0:r1].nnz
+    # a window that does not contain every column is rejected
+    rc = lib.b200spai_csr_slice_rows(A._h, r0, r1, 300, 100, _stream(), C.byref(h))
+    assert rc != 0
+
+
+def test_zero_rhs_and_repeat_solves():
+    from learningsparsepreconditioner4gpu_b200 import parallel as par
+
+    s, ws, A, G, rhs = _system(10)
+    n = s.num_nodes
+    d = par.DistPCG(A, G, ws.epsilon, [0, n], par.extended_range(s.edge_index, 0, n), rank=0, world=1)
+    x, res, _ = d.solve(torch.zeros_like(rhs), "ext_spai")
+    assert res.iterations == 0 and res.converged == 1 and float(x.abs().max()) == 0.0
+    x1, r1, _ = d.solve(rhs, "ext_spai")
+    x2, r2, _ = d.solve(rhs, "ext_spai")
+    assert r1.iterations == r2.iterations and torch.equal(x1, x2)
+    d.close()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("mode", [1, 2])
+def test_multi_rank_matches_single_gpu(mode):
+    world = min(torch.cuda.device_count(), 4)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(29611 + mode), os.path.join(ROOT, "tests", "dist_worker.py"), "20", str(mode)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
+    out = json.loads(line)
+    assert out["world"] == world and out["ext_spai"]["n_push"] >= 1

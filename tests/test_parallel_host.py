@@ -1,0 +1,171 @@
+"""Host-side logic of the row-partitioned solve (no GPU): the partitioner against a numpy mirror, the halo plan's
+consistency between ranks, and -- over a real 2-process gloo group -- a distributed SpMV / PCG built from the same
+layouts and plans, with scipy as the local operator, against the global scipy result.  The device path itself
+(peer stores, flags) is covered by tests/test_dist_gpu.py on GPUs."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from learningsparsepreconditioner4gpu_b200 import parallel as par  # noqa: E402
+
+
+def _grid_laplacian(n):
+    I = sp.identity(n)
+    T = sp.diags([-1.0, 2.0, -1.0], [-1, 0, 1], shape=(n, n))
+    A = sp.kron(sp.kron(T, I), I) + sp.kron(sp.kron(I, T), I) + sp.kron(sp.kron(I, I), T)
+    A = sp.csr_matrix(A + 0.01 * sp.identity(n ** 3))
+    A.sort_indices()
+    return A
+
+
+def _edges(A):
+    coo = A.tocoo()
+    order = np.lexsort((coo.col, coo.row))
+    return torch.from_numpy(np.stack([coo.row[order], coo.col[order]]).astype(np.int64))
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_partition_matches_numpy_mirror(world):
+    rng = np.random.default_rng(world)
+    w = rng.integers(0, 40, size=5000)
+    starts = par.partition_rows(torch.from_numpy(w), world)
+    c = np.cumsum(w)
+    ref = [0] + [int(np.searchsorted(c, (k * int(c[-1])) // world, side="right")) for k in range(1, world)] + [len(w)]
+    assert starts == ref
+    assert starts == sorted(starts) and starts[0] == 0 and starts[-1] == len(w)
+    loads = [int(w[a:b].sum()) for a, b in zip(starts[:-1], starts[1:])]
+    assert max(loads) - min(loads) <= 2 * int(w.max())  # balanced up to one row either side
+
+
+def test_partition_degenerate():
+    z = par.partition_rows(torch.zeros(7, dtype=torch.int64), 3)  # zero weights: any monotone cut that covers the rows
+    assert z[0] == 0 and z[-1] == 7 and z == sorted(z)
+    s = par.partition_rows(torch.ones(2, dtype=torch.int64), 4)
+    assert s[0] == 0 and s[-1] == 2 and s == sorted(s)
+
+
+@pytest.mark.parametrize("world", [2, 4, 7])
+def test_halo_plan_is_consistent_between_ranks(world):
+    A = _grid_laplacian(9)
+    ei = _edges(A)
+    n = A.shape[0]
+    starts = par.partition_rows(par.row_weights_from_edges(ei, n), world)
+    layouts = [par.rank_layout(starts[r], starts[r + 1], *par.extended_range(ei, starts[r], starts[r + 1])) for r in range(world)]
+    for r, (rs, re, shift, hi) in enumerate(layouts):
+        assert (rs - shift) % 2 == 0 and shift <= rs and hi >= re
+        # every column a rank's rows touch lies in its extended range
+        cols = A[rs:re].indices
+        assert cols.size == 0 or (cols.min() >= shift and cols.max() < hi)
+    plans = [par.halo_plan(layouts, r) for r in range(world)]
+    for r in range(world):
+        pushes, recvs = plans[r]
+        for (q, src_off, dst_off, length) in pushes:
+            assert r in plans[q][1]                      # q expects data from r
+            g0 = src_off + layouts[r][2]                 # global index of the first pushed entry
+            assert layouts[r][0] <= g0 and g0 + length <= layouts[r][1]          # r owns it
+            assert dst_off == g0 - layouts[q][2] and dst_off + length <= layouts[q][3] - layouts[q][2]
+        for q in recvs:
+            assert any(p[0] == r for p in plans[q][0])   # ... and q pushes to r
+    # the pushes cover every non-owned column some rank reads
+    for r, (rs, re, shift, hi) in enumerate(layouts):
+        have = np.zeros(hi - shift, dtype=bool)
+        have[rs - shift: re - shift] = True
+        for q in range(world):
+            for (dst, src_off, dst_off, length) in plans[q][0]:
+                if dst == r:
+                    have[dst_off: dst_off + length] = True
+        cols = np.unique(A[rs:re].indices) - shift
+        assert have[cols].all()
+
+
+def _worker(rank, world, port, q):
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        A = _grid_laplacian(8)
+        ei = _edges(A)
+        n = A.shape[0]
+        starts = par.partition_rows(par.row_weights_from_edges(ei, n), world)
+        mine = par.rank_layout(starts[rank], starts[rank + 1], *par.extended_range(ei, starts[rank], starts[rank + 1]))
+        layouts = par._all_gather_object(mine, None)
+        rs, re, shift, hi = mine
+        pushes, recvs = par.halo_plan(layouts, rank)
+        A_loc = sp.csr_matrix(A[rs:re, shift if shift >= 0 else 0: hi])
+        pad = 0 if shift >= 0 else -shift                 # shift may be -1: one unused slot in front
+        ext = np.zeros(hi - shift)
+
+        def exchange(owned):
+            """emulates dist_halo_kernel with gloo point-to-point: push my slices, receive the neighbours'."""
+            ext[rs - shift: re - shift] = owned
+            reqs = []
+            for (qr, src_off, dst_off, length) in pushes:
+                reqs.append(dist.isend(torch.from_numpy(ext[src_off: src_off + length].copy()), qr))
+            for qr in recvs:
+                (_, s_off, d_off, length) = next(p for p in par.halo_plan(layouts, qr)[0] if p[0] == rank)
+                buf = torch.empty(length, dtype=torch.float64)
+                dist.recv(buf, qr)
+                ext[d_off: d_off + length] = buf.numpy()
+            for r_ in reqs:
+                r_.wait()
+            return ext[pad:]
+
+        def allreduce(v):
+            """emulates dist_reduce_kernel: every rank sums the per-rank values in rank order."""
+            vals = par._all_gather_object(float(v), None)
+            t = 0.0
+            for x in vals:
+                t += x
+            return t
+
+        rng = np.random.default_rng(0)
+        xg = rng.standard_normal(n)
+        y_loc = A_loc @ exchange(xg[rs:re])
+        ok_spmv = np.allclose(y_loc, (A @ xg)[rs:re], rtol=0, atol=1e-12)
+        # unpreconditioned CG with the scipy recurrence, distributed
+        b = (A @ np.ones(n))[rs:re]
+        x = np.zeros(re - rs)
+        r = b.copy()
+        bn = np.sqrt(allreduce(r @ r))
+        it, rho_prev, p = 0, 0.0, None
+        while np.sqrt(allreduce(r @ r)) >= 1e-8 * bn and it < 500:
+            rho = allreduce(r @ r)
+            p = r.copy() if it == 0 else r + (rho / rho_prev) * p
+            qv = A_loc @ exchange(p)
+            alpha = rho / allreduce(p @ qv)
+            x += alpha * p
+            r -= alpha * qv
+            rho_prev = rho
+            it += 1
+        err = np.abs(x - 1.0).max()
+        q.put((rank, bool(ok_spmv), it, float(err)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_world2_distributed_spmv_and_cg():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok, _, _ in res)
+    assert res[0][2] == res[1][2] and res[0][2] < 500          # same iteration count on both ranks
+    assert max(e for *_, e in res) < 1e-6
