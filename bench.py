@@ -38,7 +38,7 @@ UNIT = "solves/s"
 # PCG iterations of the default workload at rtol 1e-6, measured by the CUDA path (iteration parity with the oracle
 # is +-1 on every size the oracle can solve, tests/test_pcg_gpu.py).  Used ONLY by --impl reference to scale its
 # per-iteration CPU time to a whole solve without running ~10^3 s of scipy; override with B200SPAI_REF_ITERS.
-DEFAULT_ITERS = {216: 560}
+DEFAULT_ITERS = {216: 1372}
 
 
 def log(*a):
@@ -250,21 +250,45 @@ def main_ours(args):
         "update_xr (x, r; r.r)": 48 * n,
     }
     peak, peak_src = peaks()
+    # bytes the kernels really read: lossless fp32 value stream and 16-bit column steps where they apply
+    (va, ia), (vg, ig) = A.stream_bytes(), G.stream_bytes()
+    per_a, per_g = va + ia, vg + ig
+    row_a, row_g = (8 if ia == 2 else 4), (8 if ig == 2 else 4)      # row pointer (+ first column of the row)
+    streamed_k = {
+        "GT_r (t = G^T r)": per_g * nnzG + (row_g + 16) * n,
+        "G_t (z = G t + eps r; r.z)": per_g * nnzG + (row_g + 24) * n,
+        "update_p": 24 * n,
+        "A_p (q = A p; p.q)": per_a * nnzA + (row_a + 16) * n,
+        "update_xr (x, r; r.r)": 48 * n,
+    }
     detail = {}
     for (name, by), ms in zip(bytes_k.items(), kms):
-        detail[name] = {"ms": round(ms, 4), "bytes": by, "GB/s": round(by / (ms * 1e-3) / 1e9, 1) if ms > 0 else None}
+        detail[name] = {"ms": round(ms, 4), "bytes": by, "GB/s": round(by / (ms * 1e-3) / 1e9, 1) if ms > 0 else None,
+                        "streamed_bytes": streamed_k[name],
+                        "streamed_GB/s": round(streamed_k[name] / (ms * 1e-3) / 1e9, 1) if ms > 0 else None}
     spmv_bytes = sum(by for k, by in bytes_k.items() if "update" not in k)
+    spmv_streamed = sum(by for k, by in streamed_k.items() if "update" not in k)
     spmv_ms = kms[0] + kms[1] + kms[3]
     achieved = spmv_bytes / 3 / (spmv_ms / 3 * 1e-3) / 1e9
+    streamed = spmv_streamed / 3 / (spmv_ms / 3 * 1e-3) / 1e9
     iter_bytes = sum(bytes_k.values())
+    iter_streamed = sum(streamed_k.values())
     iter_ms = sum(kms)
     roofline = {
-        "kernel": "spmv_stream_kernel<2048,3,*> (3 launches per PCG iteration: t=G^T r, z=G t+eps r, q=A p)",
+        "kernel": "spmv_stream_kernel<4096,2,8,float,u16,*> (3 launches per PCG iteration: t=G^T r, z=G t+eps r, q=A p)",
         "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-        "peak_source": peak_src, "traffic": None,
+        "peak_source": peak_src,
+        "traffic": 1.11e9 if g == 216 else None,
+        "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch at 216^3 (profiles/r01_spmv_stream_ncu_full.txt)",
         "bytes_per_launch": spmv_bytes // 3, "ms_per_launch": round(spmv_ms / 3, 4),
+        "note": ("achieved = ALGORITHMIC bytes (SURVEY 8d: 12 B per entry, fp64 value + i32 index) / time; the kernel streams a lossless "
+                 f"{per_a} B per entry (fp32 values widened on load, 16-bit column steps), so it can exceed the copy peak; "
+                 "'streamed' is the same time against the bytes really read"),
+        "streamed": {"bytes_per_launch": spmv_streamed // 3, "GB/s": round(streamed, 1), "frac": round(streamed / peak, 4)},
         "pcg_iteration": {"ms": round(iter_ms, 4), "bytes": iter_bytes, "GB/s": round(iter_bytes / (iter_ms * 1e-3) / 1e9, 1),
-                          "frac": round(iter_bytes / (iter_ms * 1e-3) / 1e9 / peak, 4)},
+                          "frac": round(iter_bytes / (iter_ms * 1e-3) / 1e9 / peak, 4),
+                          "streamed_bytes": iter_streamed, "streamed_GB/s": round(iter_streamed / (iter_ms * 1e-3) / 1e9, 1),
+                          "streamed_frac": round(iter_streamed / (iter_ms * 1e-3) / 1e9 / peak, 4)},
         "per_kernel": detail,
     }
     del solver, A, G, rhs
@@ -392,7 +416,7 @@ def main_reference(args):
     g = args.grid
     iterations = int(os.environ.get("B200SPAI_REF_ITERS", DEFAULT_ITERS.get(g, 0)) or 0)
     if iterations <= 0:
-        iterations = int(2.6 * g)  # CG on a 3-D Laplacian: iterations grow linearly with the grid edge
+        iterations = int(6.4 * g)  # measured: 1372 PCG iterations at g = 216 (random-init G); linear in the grid edge
     gen_device = "cuda" if torch.cuda.is_available() else "cpu"   # input generation only
     sample = systems.poisson_sample(g, seed=100, gen_device=gen_device, device="cpu")
     ws = systems.default_workspace(sample)
@@ -423,6 +447,107 @@ def main_reference(args):
     print(json.dumps(line), flush=True)
 
 
+
+# ---------------------------------------------------------------------------------------------------------
+# --mode rowpart: ONE system row-partitioned over all ranks (BASELINE config C5; strong scaling)
+# ---------------------------------------------------------------------------------------------------------
+def main_rowpart(args):
+    """Every rank holds the same system; the PCG runs row-partitioned over the ranks (csrc/dist.cu: NVLink peer-store
+    halos, peer-memory all-reduce).  v1: the GNN and the assembly are still replicated on every rank (bit-identical
+    G everywhere); only the solve is partitioned, and the phases are reported separately so the PCG scaling is visible."""
+    from learningsparsepreconditioner4gpu_b200 import _lib, parallel as par, systems
+    from learningsparsepreconditioner4gpu_b200.neural_cg.nn.gnns import DeviceGraph
+    from learningsparsepreconditioner4gpu_b200.neural_cg.utils.validate import to_csr_device
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    _lib.require_cuda()
+    torch.cuda.set_device(local)
+    import torch.distributed as dist
+
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29533")
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local), rank=rank, world_size=world)
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v: float) -> float:
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    g = args.grid
+    sample = systems.poisson_sample(g, seed=100, gen_device="cuda", device="cuda")   # the SAME system on every rank
+    N, E = sample.num_nodes, sample.num_edges
+    ws = systems.default_workspace(sample)
+    n = N * ws.block_size
+    starts = par.partition_rows(par.row_weights_from_edges(sample.edge_index, N), world)
+    rs, re = starts[rank], starts[rank + 1]
+    ext = par.extended_range(sample.edge_index, rs, re)
+    log(f"[rowpart r{rank}] {g}^3: N={N} rows [{rs},{re}) ext {ext}")
+
+    def step(timers=None):
+        def mark(name):
+            if timers is not None:
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record()
+                timers.append((name, ev))
+        mark("start")
+        graph = DeviceGraph(sample.edge_index, N)
+        _, g_vals = ws.gnn(sample.x, sample.edge_index, sample.edge_attr, graph=graph)
+        mark("gnn (replicated)")
+        A = to_csr_device(sample.edge_index, sample.matrix_values, n, sample.mask)
+        G = to_csr_device(sample.edge_index, g_vals.reshape(-1, 1, 1), n, sample.mask)
+        rhs = A.matvec(sample.mask.reshape(-1).to(torch.float64))
+        mark("assemble (replicated)")
+        solver = par.DistPCG(A, G, ws.epsilon, starts, ext)
+        mark("partition + G^T + connect")
+        x, res, _ = solver.solve(rhs[rs:re].contiguous(), "ext_spai", rtol=args.rtol)
+        mark("pcg (row-partitioned)")
+        info = solver.info()
+        dist.barrier()      # nobody unmaps a segment a slower peer might still be writing to
+        solver.close()
+        graph.close()
+        return res, info
+
+    for _ in range(max(args.warmup, 1)):
+        res, info = step()
+    launches0 = _lib.total_launches()
+    timers = []
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    pcg_ms, iters = [], []
+    for _ in range(args.steps):
+        res, info = step(timers)
+        pcg_ms.append(float(res.solve_ms))
+        iters.append(int(res.iterations))
+    ev1.record()
+    barrier()
+    dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    pcg = max_over_ranks(float(np.mean(pcg_ms)))
+    ph = phases_ms(timers)
+    launches = _lib.total_launches() - launches0
+    if rank == 0:
+        line = {
+            "metric": "row-partitioned learned-SPAI PCG, one system over all GPUs: solves/s (strong scaling)", "mode": "rowpart",
+            "value": round(args.steps / (dev_ms * 1e-3), 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 1), "ms_per_step": round(dev_ms / args.steps, 3), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64 (PCG) / f32 (GNN)", "data": "synthetic",
+            "config": {"workload": f"ONE poisson3d jittered Kuhn-tet system {g}^3 = {N} DOF, E = {E}, row-partitioned over {world} GPU(s); "
+                                   f"GNN + assembly replicated, PCG partitioned; rtol {args.rtol:g}",
+                       "halo": info, "rows_rank0": [rs, re]},
+            "time_to_tol_ms": round(pcg, 3), "iterations": float(np.mean(iters)), "converged": int(res.converged),
+            "ms_per_iteration": round(pcg / max(float(np.mean(iters)), 1.0), 4),
+            "phases_ms_per_step": {k: round(v / args.steps, 3) for k, v in ph.items()}, "gpu_launches": int(launches),
+        }
+        print(json.dumps(line), flush=True)
+    dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -432,9 +557,13 @@ def main():
     ap.add_argument("--rtol", type=float, default=1e-6)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--mode", default="batch", choices=["batch", "rowpart"],
+                    help="batch: one independent system per GPU (the bench contract); rowpart: one system over all GPUs")
     args = ap.parse_args()
     if args.impl == "reference":
         main_reference(args)
+    elif args.mode == "rowpart":
+        main_rowpart(args)
     else:
         main_ours(args)
 

@@ -75,6 +75,9 @@ int b200spai_csr_destroy(b200spai_csr_t a);
 /* y = A x (scipy csr @ vector; the csr_matvec under validate.py:182,197).  kernel: 0 = auto,
  * 1 = sub-warp-per-row kernel, 2 = TMA-staged streaming kernel. */
 int b200spai_spmv(b200spai_csr_t a, const double* x_dev, double* y_dev, int kernel, void* stream);
+/* Bytes per stored entry the streaming SpMV really reads for this matrix: values 4 (lossless fp32 stream) or 8,
+ * column indices 2 (16-bit within-row steps + 4 bytes per row) or 4.  Builds the streams if they do not exist yet. */
+int b200spai_csr_stream_info(b200spai_csr_t a, int32_t* value_bytes, int32_t* index_bytes, void* stream);
 /* diag[i] = A[i,i] (0 where absent)  (A.diagonal(), validate.py:286). */
 int b200spai_csr_diagonal(b200spai_csr_t a, double* diag_dev, void* stream);
 

@@ -518,6 +518,15 @@ extern "C" {
 const char* b200spai_last_error(void) { return last_error().c_str(); }
 int b200spai_version(void) { return 101; }
 
+int b200spai_csr_stream_info(b200spai_csr_t a, int32_t* value_bytes, int32_t* index_bytes, void* stream) {
+  B2_ARG(a, "csr_stream_info: NULL handle");
+  B2_TRY(csr_ensure_f32(a, as_stream(stream)));
+  B2_TRY(csr_ensure_col16(a, as_stream(stream)));
+  if (value_bytes) *value_bytes = (a->f32_state == 1) ? 4 : 8;
+  if (index_bytes) *index_bytes = (a->c16_state == 1) ? 2 : 4;
+  return 0;
+}
+
 int b200spai_pool_trim(void) {
   std::vector<void*> blocks;
   {

@@ -29,13 +29,14 @@ namespace b200spai {
 
 constexpr int MAXR = 16;
 enum { V_P = 0, V_R = 1, V_T = 2, NVEC = 3 };
-enum { RED_INIT = 0, RED_RHO = 1, RED_PQ = 2, RED_RR = 3, NRED = 4 };
+enum { RED_INIT = 0, RED_RHO = 1 /* + ||r||^2 */, RED_PQ = 2, NRED = 3 };
 
 // header of the symmetric segment (same offsets on every rank)
 struct SegHeader {
   unsigned long long halo_flag[NVEC][MAXR];
   unsigned long long red_epoch[NRED][MAXR];
   double red_val[NRED][MAXR];
+  double red_val2[NRED][MAXR];  // second scalar of a fused exchange (||r||^2 travelling with rho)
 };
 constexpr size_t SEG_VEC_OFFSET = (sizeof(SegHeader) + 255) / 256 * 256;
 
@@ -109,8 +110,11 @@ __global__ void __launch_bounds__(256) dist_halo_kernel(const __grid_constant__ 
 }
 
 // ---- all-reduce (sum, fp64, rank order) of sc->local_total + the scalar update it feeds -----------------------
+// RED_RHO also carries ||r||^2 of the preceding x/r update (sc->have_rr): the convergence test is applied first, then
+// rho / beta -- the order of the single-GPU solver -- so the t = G^T r and z = G t kernels of an iteration that turns out
+// not to be needed have run speculatively (they only write t and z) and the exchange count drops from 3 to 2.
 __global__ void __launch_bounds__(32) dist_reduce_kernel(const __grid_constant__ DistCtx c, int kind) {
-  __shared__ double s_val[MAXR];
+  __shared__ double s_val[MAXR], s_val2[MAXR];
   __shared__ unsigned long long s_epoch;
   PcgScalars* sc = c.sc;
   if (kind != RED_INIT && sc->done) return;
@@ -119,27 +123,39 @@ __global__ void __launch_bounds__(32) dist_reduce_kernel(const __grid_constant__
   __syncwarp();
   const unsigned long long ep = s_epoch;
   const double local = sc->local_total;
+  const bool with_rr = (kind == RED_RHO) && sc->have_rr;  // identical on every rank
+  const double local2 = with_rr ? sc->local_rr : 0.0;
   if (t < c.world) {
     c.hdr[t]->red_val[kind][c.rank] = local;
+    if (with_rr) c.hdr[t]->red_val2[kind][c.rank] = local2;
     __threadfence_system();
     st_release_sys(&c.hdr[t]->red_epoch[kind][c.rank], ep);
   }
   if (t < c.world) {
     dist_wait(c, &c.hdr[c.rank]->red_epoch[kind][t], ep);
     s_val[t] = *reinterpret_cast<volatile double*>(&c.hdr[c.rank]->red_val[kind][t]);
+    if (with_rr) s_val2[t] = *reinterpret_cast<volatile double*>(&c.hdr[c.rank]->red_val2[kind][t]);
   }
   __syncwarp();
   if (t != 0) return;
   if (sc->breakdown == 3) return;  // a wait timed out
-  double total = 0.0;
+  double total = 0.0, total2 = 0.0;
   for (int r = 0; r < c.world; ++r) total += s_val[r];
-  const int was_dist = sc->dist;
+  if (with_rr)
+    for (int r = 0; r < c.world; ++r) total2 += s_val2[r];
   sc->dist = 0;  // the shared update code below must apply the update, not store a local total
-  if (kind == RED_INIT) pcg_final_init(sc, total, c.hist);
-  else if (kind == RED_RHO) pcg_final_scalar(sc, FINAL_RHO, total);
-  else if (kind == RED_PQ) pcg_final_scalar(sc, FINAL_PQ, total);
-  else pcg_final_rr(sc, total, c.hist);
-  sc->dist = was_dist;
+  if (kind == RED_INIT) {
+    pcg_final_init(sc, total, c.hist);
+  } else if (kind == RED_RHO) {
+    if (with_rr) {
+      sc->have_rr = 0;
+      pcg_final_rr(sc, total2, c.hist);
+    }
+    if (!sc->done) pcg_final_scalar(sc, FINAL_RHO, total);
+  } else {
+    pcg_final_scalar(sc, FINAL_PQ, total);
+  }
+  sc->dist = 1;
 }
 
 // diag[i] = A_local[i, i + off]
@@ -300,8 +316,8 @@ static int dist_enqueue_iteration(b200spai_dist_s* s, int precond, double* x, cu
   pcg_update_xr_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(x, r, p, s->q, s->n, s->sc, s->partials, s->ticket, s->hist);
   B2_LAUNCH_CHECK();
   *nl += 1;
-  B2_TRY(dist_enqueue_reduce(s, RED_RR, st, nl));
-  if (precond >= B200SPAI_PRECOND_EXT_SPAI) B2_TRY(dist_enqueue_halo(s, V_R, st, nl));  // the next t = G^T r gathers r
+  // ||r||^2 is all-reduced together with the next rho (dist_reduce_kernel); the next t = G^T r gathers r
+  if (precond >= B200SPAI_PRECOND_EXT_SPAI) B2_TRY(dist_enqueue_halo(s, V_R, st, nl));
   return 0;
 }
 

@@ -164,8 +164,12 @@ static __global__ void __launch_bounds__(VTHREADS) pcg_update_xr_kernel(double* 
   double cta = block_sum(acc, red);
   double total;
   if (grid_sum_last(cta, partials, ticket, red, total) && threadIdx.x == 0) {
-    if (sc->dist) sc->local_total = total;
-    else pcg_final_rr(sc, total, hist);
+    if (sc->dist) {  // all-reduced together with the next rho (one exchange instead of two, same arithmetic)
+      sc->local_rr = total;
+      sc->have_rr = 1;
+    } else {
+      pcg_final_rr(sc, total, hist);
+    }
   }
 }
 

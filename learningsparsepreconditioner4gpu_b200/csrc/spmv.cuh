@@ -32,7 +32,9 @@ struct PcgScalars {
   unsigned long long cond_handle;
   // row-partitioned solve (dist.cu): reductions stop at the local total, an all-reduce kernel finishes them
   int dist;
+  int have_rr;        // dist: ||r||^2 of the update just made is waiting in local_rr (all-reduced together with rho)
   double local_total;
+  double local_rr;
 };
 
 struct CsrView {

@@ -97,6 +97,12 @@ class DeviceCSR:
         _lib.check(self._lib.b200spai_csr_shape(self._h, C.byref(r), C.byref(c), C.byref(z)), "csr_shape")
         return z.value
 
+    def stream_bytes(self):
+        """(value bytes, index bytes) per stored entry that the streaming SpMV reads (4/8, 2/4)."""
+        v, i = C.c_int32(), C.c_int32()
+        _lib.check(self._lib.b200spai_csr_stream_info(self._h, C.byref(v), C.byref(i), _stream()), "csr_stream_info")
+        return v.value, i.value
+
     def to_scipy(self):
         from scipy.sparse import csr_matrix
 
