@@ -164,6 +164,16 @@ int b200spai_gnn_destroy(b200spai_gnn_t m);
  * node_out_dev: NULL or [N,16] final node features. */
 int b200spai_gnn_forward(b200spai_gnn_t m, b200spai_graph_t g, const float* x_dev, const float* edge_attr_dev,
                          float* g_out_dev, float* node_out_dev, void* stream);
+/* The same forward one kernel at a time, for a graph whose nodes are partly owned by other ranks (row-partitioned
+ * system): stage 0 = node encoder (gnns.py:83), stages 1..num_layers = MPLayer k-1
+ * (basic_layers.py:193-225; stage 1 also runs the edge encoder, gnns.py:84), stage num_layers+1 = decoder
+ * (gnns.py:88-95).  After stages 1..num_layers the caller overwrites the rows of b200spai_gnn_node_features(g, stage)
+ * that belong to halo nodes with their owners' values before the next stage.  Arguments a stage does not use may be
+ * NULL. */
+int b200spai_gnn_forward_stage(b200spai_gnn_t m, b200spai_graph_t g, int32_t stage, const float* x_dev,
+                               const float* edge_attr_dev, float* g_out_dev, void* stream);
+/* [N,16] fp32 node features written by `stage` (valid until the graph is destroyed). */
+int b200spai_gnn_node_features(b200spai_graph_t g, int32_t stage, float** x_dev);
 int b200spai_gnn_launch_count(b200spai_gnn_t m, int64_t* launches);
 /* GraphSpmv (neural_cg/nn/basic_layers.py:112-142), the fp32 edge-list operator AATPE (:228-261) is built
  * from: y[N,b] = mask * (A x) with values [E,b,b] in the caller's edge order; transpose != 0 applies A^T

@@ -50,6 +50,8 @@ SIGNATURES = {
     "b200spai_gnn_create": [c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, C.POINTER(c_vp)],
     "b200spai_gnn_destroy": [c_vp],
     "b200spai_gnn_forward": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp],
+    "b200spai_gnn_forward_stage": [c_vp, c_vp, c_i32, c_vp, c_vp, c_vp, c_vp],
+    "b200spai_gnn_node_features": [c_vp, c_i32, C.POINTER(c_vp)],
     "b200spai_gnn_launch_count": [c_vp, C.POINTER(c_i64)],
     "b200spai_graph_spmv_f32": [c_vp, c_i32, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp],
     "b200spai_csr_stream_info": [c_vp, C.POINTER(c_i32), C.POINTER(c_i32), c_vp],

@@ -516,7 +516,7 @@ using namespace b200spai;
 extern "C" {
 
 const char* b200spai_last_error(void) { return last_error().c_str(); }
-int b200spai_version(void) { return 101; }
+int b200spai_version(void) { return 102; }
 
 int b200spai_csr_stream_info(b200spai_csr_t a, int32_t* value_bytes, int32_t* index_bytes, void* stream) {
   B2_ARG(a, "csr_stream_info: NULL handle");

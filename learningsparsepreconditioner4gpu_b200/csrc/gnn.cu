@@ -25,6 +25,10 @@
 // math (10-bit mantissa) cannot meet, and the GEMMs are K<=48, N=16.
 #include <cub/cub.cuh>
 
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
 #include "csr.h"
 
 namespace b200spai {
@@ -36,6 +40,7 @@ constexpr int NB_MAXN = 64;          // >= NB_TARGET / 4 nodes per block
 constexpr int MLP16 = 3 * (F * F + F);        // 816 floats: three 16x16 Linear (+bias)
 constexpr int MLP48 = 48 * F + F + 2 * (F * F + F);  // 1328 floats: 48->16, 16->16, 16->16
 constexpr int LAYER_FLOATS = 2 * MLP48 + MLP16;      // msg, edge, node
+constexpr int GNN_CFG_DEFAULT = 2;
 
 }  // namespace b200spai
 
@@ -90,6 +95,16 @@ __global__ void graph_segptr_kernel(const int* __restrict__ dst, long long E, lo
     if (dst[mid] >= i) hi = mid; else lo = mid + 1;
   }
   segptr[i] = (int)lo;
+}
+
+// B200SPAI_GNN_CFG (development switch): bit 1 = rational-erfc GELU (default) instead of erff.
+static int gnn_cfg() {
+  static int cfg = -1;
+  if (cfg < 0) {
+    const char* e = getenv("B200SPAI_GNN_CFG");
+    cfg = e ? (atoi(e) & 2) : GNN_CFG_DEFAULT;
+  }
+  return cfg;
 }
 
 static void graph_free(b200spai_graph_s* g) {
@@ -203,6 +218,84 @@ static int graph_create_impl(long long N, long long E, const long long* edge_ind
 
 using namespace b200spai;
 
+namespace {
+
+template <bool FIRST, int G>
+int launch_mp(const MpParams& P, int nnb, cudaStream_t st) {
+  static int occ = 0;
+  if (!occ) {
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gnn_mp_kernel<FIRST, G>, MP_THREADS, 0));
+    if (occ < 1) occ = 1;
+  }
+  int grid = sm_count() * occ;
+  if (grid > nnb) grid = nnb;
+  if (grid < 1) grid = 1;
+  gnn_mp_kernel<FIRST, G><<<grid, MP_THREADS, 0, st>>>(P);
+  return 0;
+}
+
+template <int G>
+int launch_dec(b200spai_gnn_t m, b200spai_graph_t g, const float* x, float* g_out_dev, cudaStream_t st) {
+  static int occ = 0;
+  if (!occ) {
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gnn_dec_kernel<G>, 256, 0));
+    if (occ < 1) occ = 1;
+  }
+  long long ctas = (g->E + 255) / 256;
+  if (ctas > (long long)sm_count() * occ) ctas = (long long)sm_count() * occ;
+  gnn_dec_kernel<G><<<(int)ctas, 256, 0, st>>>(g->src, g->dst, g->perm, g->ef, x, m->w_dec(), g->E, m->bb, g_out_dev);
+  return 0;
+}
+
+// stage 0 = node encoder, 1..L = message-passing layers, L+1 = decoder.  Node features ping-pong between g->x0 and
+// g->x1: stage s (<= L) writes buffer s & 1, the decoder reads buffer L & 1.
+int gnn_stage(b200spai_gnn_t m, b200spai_graph_t g, int stage, const float* x_dev, const float* edge_attr_dev,
+              float* g_out_dev, cudaStream_t st) {
+  const long long N = g->N, E = g->E;
+  if (N == 0) return 0;
+  const int cfg = gnn_cfg();
+  float* xb[2] = {g->x0, g->x1};
+  if (stage == 0) {
+    long long ctas = (N + 255) / 256;
+    if (ctas > (long long)sm_count() * 4) ctas = (long long)sm_count() * 4;
+    if (cfg & 2)
+      gnn_node_enc_kernel<1><<<(int)ctas, 256, 0, st>>>(x_dev, m->node_in, N, m->w_node_enc(), g->x0);
+    else
+      gnn_node_enc_kernel<0><<<(int)ctas, 256, 0, st>>>(x_dev, m->node_in, N, m->w_node_enc(), g->x0);
+  } else if (stage <= m->L) {
+    const int l = stage - 1;
+    MpParams P{};
+    P.src = g->src;
+    P.dst = g->dst;
+    P.segptr = g->segptr;
+    P.perm = g->perm;
+    P.nb = g->nb;
+    P.nnb = g->nnb;
+    P.ef = g->ef;
+    P.xin = xb[(stage - 1) & 1];
+    P.xout = xb[stage & 1];
+    P.w_layer = m->w_layer(l);
+    P.w_eenc = m->w_edge_enc();
+    P.edge_attr = edge_attr_dev;
+    P.edge_in = m->edge_in;
+    int rc;
+    if (l == 0)
+      rc = (cfg & 2) ? launch_mp<true, 1>(P, g->nnb, st) : launch_mp<true, 0>(P, g->nnb, st);
+    else
+      rc = (cfg & 2) ? launch_mp<false, 1>(P, g->nnb, st) : launch_mp<false, 0>(P, g->nnb, st);
+    if (rc) return rc;
+  } else if (E > 0) {
+    int rc = (cfg & 2) ? launch_dec<1>(m, g, xb[m->L & 1], g_out_dev, st) : launch_dec<0>(m, g, xb[m->L & 1], g_out_dev, st);
+    if (rc) return rc;
+  }
+  B2_LAUNCH_CHECK();
+  m->launches += 1;
+  count_launches(1);
+  return 0;
+}
+
+}  // namespace
+
 extern "C" {
 
 int b200spai_graph_create(int64_t num_nodes, int64_t num_edges, const int64_t* edge_index_dev, void* stream,
@@ -257,59 +350,30 @@ int b200spai_gnn_forward(b200spai_gnn_t m, b200spai_graph_t g, const float* x_de
                          float* g_out_dev, float* node_out_dev, void* stream) {
   B2_ARG(m && g && x_dev && (edge_attr_dev || g->E == 0) && (g_out_dev || g->E == 0), "gnn_forward: NULL argument");
   cudaStream_t st = as_stream(stream);
-  const long long N = g->N, E = g->E;
-  if (N == 0) return 0;
-  static int occ_first = 0, occ_rest = 0, occ_dec = 0;
-  if (!occ_first) {
-    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_first, gnn_mp_kernel<true>, MP_THREADS, 0));
-    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_rest, gnn_mp_kernel<false>, MP_THREADS, 0));
-    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_dec, gnn_dec_kernel, 256, 0));
-    if (occ_first < 1) occ_first = 1;
-    if (occ_rest < 1) occ_rest = 1;
-    if (occ_dec < 1) occ_dec = 1;
+  if (g->N == 0) return 0;
+  for (int stage = 0; stage <= m->L + 1; ++stage) {
+    int rc = gnn_stage(m, g, stage, x_dev, edge_attr_dev, g_out_dev, st);
+    if (rc) return rc;
   }
-  const int sms = sm_count();
-  {
-    long long ctas = (N + 255) / 256;
-    if (ctas > (long long)sms * 4) ctas = (long long)sms * 4;
-    gnn_node_enc_kernel<<<(int)ctas, 256, 0, st>>>(x_dev, m->node_in, N, m->w_node_enc(), g->x0);
-  }
-  float* xin = g->x0;
-  float* xout = g->x1;
-  for (int l = 0; l < m->L; ++l) {
-    MpParams P{};
-    P.src = g->src;
-    P.dst = g->dst;
-    P.segptr = g->segptr;
-    P.perm = g->perm;
-    P.nb = g->nb;
-    P.nnb = g->nnb;
-    P.ef = g->ef;
-    P.xin = xin;
-    P.xout = xout;
-    P.w_layer = m->w_layer(l);
-    P.w_eenc = m->w_edge_enc();
-    P.edge_attr = edge_attr_dev;
-    P.edge_in = m->edge_in;
-    int grid = sms * (l == 0 ? occ_first : occ_rest);
-    if (grid > g->nnb) grid = g->nnb;
-    if (grid < 1) grid = 1;
-    if (l == 0)
-      gnn_mp_kernel<true><<<grid, MP_THREADS, 0, st>>>(P);
-    else
-      gnn_mp_kernel<false><<<grid, MP_THREADS, 0, st>>>(P);
-    float* t = xin;
-    xin = xout;
-    xout = t;
-  }
-  if (E > 0) {
-    long long ctas = (E + 255) / 256;
-    if (ctas > (long long)sms * occ_dec) ctas = (long long)sms * occ_dec;
-    gnn_dec_kernel<<<(int)ctas, 256, 0, st>>>(g->src, g->dst, g->perm, g->ef, xin, m->w_dec(), E, m->bb, g_out_dev);
-  }
-  B2_LAUNCH_CHECK();
-  if (node_out_dev) B2_CUDA(cudaMemcpyAsync(node_out_dev, xin, (size_t)N * F * sizeof(float), cudaMemcpyDeviceToDevice, st));
-  { const long long _nl = (2 + m->L); m->launches += _nl; count_launches(_nl); }
+  if (node_out_dev)
+    B2_CUDA(cudaMemcpyAsync(node_out_dev, (m->L & 1) ? g->x1 : g->x0, (size_t)g->N * F * sizeof(float),
+                            cudaMemcpyDeviceToDevice, st));
+  return 0;
+}
+
+int b200spai_gnn_forward_stage(b200spai_gnn_t m, b200spai_graph_t g, int32_t stage, const float* x_dev,
+                               const float* edge_attr_dev, float* g_out_dev, void* stream) {
+  B2_ARG(m && g, "gnn_forward_stage: NULL argument");
+  B2_ARG(stage >= 0 && stage <= m->L + 1, "gnn_forward_stage: stage must be in [0, num_layers + 1]");
+  B2_ARG(stage != 0 || x_dev, "gnn_forward_stage: stage 0 needs the node inputs");
+  B2_ARG(stage != 1 || edge_attr_dev || g->E == 0, "gnn_forward_stage: stage 1 needs edge_attr");
+  B2_ARG(stage != m->L + 1 || g_out_dev || g->E == 0, "gnn_forward_stage: the decoder stage needs g_out");
+  return gnn_stage(m, g, stage, x_dev, edge_attr_dev, g_out_dev, as_stream(stream));
+}
+
+int b200spai_gnn_node_features(b200spai_graph_t g, int32_t stage, float** x_dev) {
+  B2_ARG(g && x_dev && stage >= 0, "gnn_node_features: bad argument");
+  *x_dev = (stage & 1) ? g->x1 : g->x0;
   return 0;
 }
 
