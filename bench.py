@@ -452,9 +452,9 @@ def main_reference(args):
 # --mode rowpart: ONE system row-partitioned over all ranks (BASELINE config C5; strong scaling)
 # ---------------------------------------------------------------------------------------------------------
 def main_rowpart(args):
-    """Every rank holds the same system; the PCG runs row-partitioned over the ranks (csrc/dist.cu: NVLink peer-store
-    halos, peer-memory all-reduce).  v1: the GNN and the assembly are still replicated on every rank (bit-identical
-    G everywhere); only the solve is partitioned, and the phases are reported separately so the PCG scaling is visible."""
+    """Every rank holds the INPUTS of the same system and computes only its share (parallel.PartitionedSystem): the GNN
+    on the edges whose target it owns (node-feature halo per layer), one boundary swap of G values, assembly of its rows
+    of A, G and G^T, and the row-partitioned PCG (csrc/dist.cu: NVLink peer-store halos, peer-memory all-reduce)."""
     from learningsparsepreconditioner4gpu_b200 import _lib, parallel as par, systems
     from learningsparsepreconditioner4gpu_b200.neural_cg.nn.gnns import DeviceGraph
     from learningsparsepreconditioner4gpu_b200.neural_cg.utils.validate import to_csr_device
@@ -480,14 +480,12 @@ def main_rowpart(args):
         return float(t.item())
 
     g = args.grid
-    sample = systems.poisson_sample(g, seed=100, gen_device="cuda", device="cuda")   # the SAME system on every rank
+    sample = systems.poisson_sample(g, seed=100, gen_device="cuda", device="cuda")   # the SAME inputs on every rank
     N, E = sample.num_nodes, sample.num_edges
     ws = systems.default_workspace(sample)
-    n = N * ws.block_size
     starts = par.partition_rows(par.row_weights_from_edges(sample.edge_index, N), world)
     rs, re = starts[rank], starts[rank + 1]
-    ext = par.extended_range(sample.edge_index, rs, re)
-    log(f"[rowpart r{rank}] {g}^3: N={N} rows [{rs},{re}) ext {ext}")
+    log(f"[rowpart r{rank}] {g}^3: N={N} rows [{rs},{re})")
 
     def step(timers=None):
         def mark(name):
@@ -496,21 +494,22 @@ def main_rowpart(args):
                 ev.record()
                 timers.append((name, ev))
         mark("start")
-        graph = DeviceGraph(sample.edge_index, N)
-        _, g_vals = ws.gnn(sample.x, sample.edge_index, sample.edge_attr, graph=graph)
-        mark("gnn (replicated)")
-        A = to_csr_device(sample.edge_index, sample.matrix_values, n, sample.mask)
-        G = to_csr_device(sample.edge_index, g_vals.reshape(-1, 1, 1), n, sample.mask)
-        rhs = A.matvec(sample.mask.reshape(-1).to(torch.float64))
-        mark("assemble (replicated)")
-        solver = par.DistPCG(A, G, ws.epsilon, starts, ext)
-        mark("partition + G^T + connect")
-        x, res, _ = solver.solve(rhs[rs:re].contiguous(), "ext_spai", rtol=args.rtol)
+        ps = par.PartitionedSystem(sample.edge_index, N, ws.block_size, starts)
+        mark("partition (edge ownership, local edge lists)")
+        g_t = ps.gnn_forward(ws.gnn, sample.x, sample.edge_attr)
+        mark("gnn (target-owned edges, halo per layer)")
+        local = ps.assemble(sample.matrix_values, g_t, sample.mask)
+        rhs_loc = local[0].matvec(ps.ext_slice(sample.mask.reshape(N, ws.block_size)).reshape(-1).to(torch.float64))
+        mark("G swap + assemble A, G, G^T rows")
+        solver = ps.make_solver(local, ws.epsilon)
+        mark("connect")
+        x, res, _ = solver.solve(rhs_loc, "ext_spai", rtol=args.rtol)
         mark("pcg (row-partitioned)")
         info = solver.info()
+        info["edges_gnn"] = int(ps.ids_t.numel())
         dist.barrier()      # nobody unmaps a segment a slower peer might still be writing to
         solver.close()
-        graph.close()
+        ps.close()
         return res, info
 
     for _ in range(max(args.warmup, 1)):
@@ -538,7 +537,7 @@ def main_rowpart(args):
             "warmup": max(args.warmup, 1), "ms_per_step": round(dev_ms / args.steps, 3), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64 (PCG) / f32 (GNN)", "data": "synthetic",
             "config": {"workload": f"ONE poisson3d jittered Kuhn-tet system {g}^3 = {N} DOF, E = {E}, row-partitioned over {world} GPU(s); "
-                                   f"GNN + assembly replicated, PCG partitioned; rtol {args.rtol:g}",
+                                   f"GNN on target-owned edges, assembly of owned rows, PCG partitioned; rtol {args.rtol:g}",
                        "halo": info, "rows_rank0": [rs, re]},
             "time_to_tol_ms": round(pcg, 3), "iterations": float(np.mean(iters)), "converged": int(res.converged),
             "ms_per_iteration": round(pcg / max(float(np.mean(iters)), 1.0), 4),

@@ -100,8 +100,13 @@ class DistPCG:
     ``A``, ``G`` are the GLOBAL matrices resident on this rank's GPU (v1: every rank assembles the whole system and
     keeps only its rows); ``row_starts`` comes from ``partition_rows`` and must be identical on every rank."""
 
-    def __init__(self, A: DeviceCSR, G: Optional[DeviceCSR], epsilon: float, row_starts: Sequence[int],
-                 ext: Tuple[int, int], group=None, rank: Optional[int] = None, world: Optional[int] = None, mode: int = 0):
+    def __init__(self, A: Optional[DeviceCSR], G: Optional[DeviceCSR], epsilon: float, row_starts: Sequence[int],
+                 ext: Tuple[int, int], group=None, rank: Optional[int] = None, world: Optional[int] = None, mode: int = 0,
+                 local: Optional[Tuple[DeviceCSR, Optional[DeviceCSR], Optional[DeviceCSR]]] = None,
+                 layout: Optional[Layout] = None):
+        """``local`` = (A_loc, G_loc, GT_loc): the owned rows already assembled in the extended column layout
+        (``PartitionedSystem.assemble``); then ``A`` / ``G`` are ignored and nothing global is needed on this rank.
+        ``layout`` overrides the layout derived from ``ext`` (block systems keep it node-aligned)."""
         self._lib = _lib.load()
         _lib.require_cuda()
         if world is None:
@@ -109,10 +114,11 @@ class DistPCG:
 
             world, rank = dist.get_world_size(group), dist.get_rank(group)
         self.rank, self.world = int(rank), int(world)
-        n = A.shape[0]
+        n = int(row_starts[-1]) if local is not None else A.shape[0]
         assert len(row_starts) == self.world + 1 and row_starts[0] == 0 and row_starts[-1] == n
         rs, re = int(row_starts[self.rank]), int(row_starts[self.rank + 1])
-        self.layout = rank_layout(rs, re, int(ext[0]), int(ext[1]))
+        self.layout = tuple(int(v) for v in layout) if layout is not None else rank_layout(rs, re, int(ext[0]), int(ext[1]))
+        assert self.layout[0] == rs and self.layout[1] == re
         self.layouts: List[Layout] = ([self.layout] if self.world == 1 else
                                       [tuple(int(v) for v in t) for t in _all_gather_object(self.layout, group)])
         ext_cap = max(l[3] - l[2] for l in self.layouts)
@@ -128,9 +134,14 @@ class DistPCG:
         # local matrices: owned rows, columns shifted into the extended layout
         _, _, shift, hi = self.layout
         self.n_local, self.ext_len = re - rs, hi - shift
-        self.A = self._slice(A, rs, re, shift)
         self.G = self.GT = None
-        if G is not None:
+        if local is not None:
+            self.A, self.G, self.GT = local
+            for m in local:
+                assert m is None or m.shape == (self.n_local, self.ext_len), (m.shape, self.n_local, self.ext_len)
+        else:
+            self.A = self._slice(A, rs, re, shift)
+        if local is None and G is not None:
             GT = G.transpose()
             self.G = self._slice(G, rs, re, shift)
             self.GT = self._slice(GT, rs, re, shift)
@@ -200,3 +211,223 @@ def row_weights_from_edges(edge_index: torch.Tensor, num_rows: int) -> torch.Ten
     row_deg = torch.bincount(edge_index[0], minlength=num_rows)
     col_deg = torch.bincount(edge_index[1], minlength=num_rows)
     return 2 * row_deg + col_deg
+
+
+# ---------------------------------------------------------------------------------------------------------
+# partitioned GNN + assembly: every rank computes only its share of G and of the matrices
+# ---------------------------------------------------------------------------------------------------------
+def owner_of(index: torch.Tensor, starts: Sequence[int]) -> torch.Tensor:
+    """Rank that owns each (node / row) index under the contiguous partition ``starts``."""
+    bounds = torch.tensor(list(starts[1:-1]), dtype=torch.int64, device=index.device)
+    return torch.bucketize(index, bounds, right=True)
+
+
+def owned_edge_sets(edge_index: torch.Tensor, rs: int, re: int):
+    """(e0, e1, ids_t): the edges whose ROW is owned are the contiguous slice [e0, e1) of the row-major edge list (they
+    give the owned rows of A and G); ``ids_t`` = ascending ids of the edges whose TARGET ``edge_index[1]`` is owned --
+    the edges this rank runs the GNN on, because messages are summed at the target (basic_layers.py:193-225)."""
+    row, col = edge_index[0], edge_index[1]
+    bnd = torch.tensor([rs, re], dtype=row.dtype, device=row.device)
+    e0, e1 = (int(v) for v in torch.searchsorted(row.contiguous(), bnd).tolist())
+    ids_t = torch.nonzero((col >= rs) & (col < re)).reshape(-1)
+    return e0, e1, ids_t
+
+
+def g_exchange_plan(edge_index: torch.Tensor, starts: Sequence[int], rank: int):
+    """Who needs which G values.  The GNN leaves rank r with G on its target-owned edges (columns of G), the solver
+    needs the owned ROWS of G: entry (i, j) with i owned by q and j owned by r != q travels r -> q.
+
+    Returns ``(e0, e1, ids_t, loc_t, loc_r, send, recv)``: ``loc_t`` / ``loc_r`` = positions (in ``ids_t`` / in the
+    row slice) of the edges that are both; ``send[q]`` = positions in ``ids_t`` to ship to q; ``recv[q]`` = positions in
+    the row slice filled by q.  Both sides enumerate a (row owner, column owner) class in ascending edge id, so the
+    k-th value sent is the k-th value expected."""
+    rs, re = int(starts[rank]), int(starts[rank + 1])
+    e0, e1, ids_t = owned_edge_sets(edge_index, rs, re)
+    row_owner_t = owner_of(edge_index[0][ids_t], starts)
+    col_owner_r = owner_of(edge_index[1][e0:e1], starts)
+    loc_t = torch.nonzero(row_owner_t == rank).reshape(-1)
+    loc_r = torch.nonzero(col_owner_r == rank).reshape(-1)
+    send, recv = {}, {}
+    for q in range(len(starts) - 1):
+        if q == rank:
+            continue
+        s = torch.nonzero(row_owner_t == q).reshape(-1)
+        if s.numel():
+            send[q] = s
+        r = torch.nonzero(col_owner_r == q).reshape(-1)
+        if r.numel():
+            recv[q] = r
+    return e0, e1, ids_t, loc_t, loc_r, send, recv
+
+
+def halo_ranges(layouts: Sequence[Layout], rank: int):
+    """(sends, recvs) as [(peer, offset, length)] in this rank's extended index space: the owned slices a peer's
+    extended range contains, and the slices of this rank's halo each peer owns (``halo_plan`` seen from both ends)."""
+    rs, re, shift, hi = layouts[rank]
+    sends, recvs = [], []
+    for q, (rs_q, re_q, lo_q, hi_q) in enumerate(layouts):
+        if q == rank:
+            continue
+        a, b = max(rs, lo_q), min(re, hi_q)
+        if a < b:
+            sends.append((q, a - shift, b - a))
+        a2, b2 = max(rs_q, shift), min(re_q, hi)
+        if a2 < b2:
+            recvs.append((q, a2 - shift, b2 - a2))
+    return sends, recvs
+
+
+def _p2p(sends, recvs, group):
+    """sends = [(peer, tensor)], recvs = [(peer, tensor)] (contiguous); one batched NCCL / gloo exchange."""
+    import torch.distributed as dist
+
+    ops = [dist.P2POp(dist.isend, t, q, group) for q, t in sends] + [dist.P2POp(dist.irecv, t, q, group) for q, t in recvs]
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+
+
+def exchange_halo_rows(buf: torch.Tensor, layouts: Sequence[Layout], rank: int, group=None) -> None:
+    """Refresh the halo rows of ``buf`` ([extended length, ...], contiguous) with their owners' rows."""
+    sends, recvs = halo_ranges(layouts, rank)
+    _p2p([(q, buf[o:o + l]) for q, o, l in sends], [(q, buf[o:o + l]) for q, o, l in recvs], group)
+
+
+def exchange_g_rows(g_t: torch.Tensor, plan, group=None) -> torch.Tensor:
+    """G values [E_t, ...] on the target-owned edges -> G values on the row-owned edges [e1 - e0, ...]."""
+    e0, e1, ids_t, loc_t, loc_r, send, recv = plan
+    out = torch.empty((e1 - e0,) + tuple(g_t.shape[1:]), dtype=g_t.dtype, device=g_t.device)
+    out[loc_r] = g_t[loc_t]
+    sb = [(q, g_t[idx].contiguous()) for q, idx in sorted(send.items())]
+    rb = [(q, torch.empty((idx.numel(),) + tuple(g_t.shape[1:]), dtype=g_t.dtype, device=g_t.device))
+          for q, idx in sorted(recv.items())]
+    _p2p(sb, rb, group)
+    for q, t in rb:
+        out[recv[q]] = t
+    return out
+
+
+class PartitionedSystem:
+    """One rank's share of a row-partitioned system: the GNN runs on the edges whose target node this
+    rank owns (node-feature halo refreshed after every MP layer), the boundary G values are swapped once, and A, G, G^T
+    are assembled for the owned rows only -- nothing of size E or N is computed twice.
+
+    ``edge_index`` is the global [2, E] list (row-major, column-ascending) on this rank's GPU; ``starts`` the NODE
+    partition from ``partition_rows``.  Collective: every rank of ``group`` builds it and calls the methods together."""
+
+    def __init__(self, edge_index: torch.Tensor, num_nodes: int, block_size: int, starts: Sequence[int],
+                 rank: Optional[int] = None, world: Optional[int] = None, group=None):
+        if world is None:
+            import torch.distributed as dist
+
+            world, rank = dist.get_world_size(group), dist.get_rank(group)
+        self.rank, self.world, self.group = int(rank), int(world), group
+        self.N, self.b, self.starts = int(num_nodes), int(block_size), [int(v) for v in starts]
+        assert len(self.starts) == self.world + 1 and self.starts[0] == 0 and self.starts[-1] == self.N
+        rs, re = self.starts[self.rank], self.starts[self.rank + 1]
+        lo, hi = extended_range(edge_index, rs, re)
+        self.layout_nodes = rank_layout(rs, re, lo, hi)
+        self.layouts_nodes: List[Layout] = ([self.layout_nodes] if self.world == 1 else
+                                            [tuple(int(v) for v in t) for t in _all_gather_object(self.layout_nodes, group)])
+        self.shift, self.hi = self.layout_nodes[2], hi
+        self.ext_nodes = hi - self.shift
+        self.plan = g_exchange_plan(edge_index, self.starts, self.rank)
+        self.e0, self.e1, self.ids_t = self.plan[0], self.plan[1], self.plan[2]
+        # local edge lists in extended node numbering (global - shift)
+        self.ei_t = (edge_index[:, self.ids_t] - self.shift).contiguous()          # target-owned, for the GNN and G^T
+        self.ei_r = (edge_index[:, self.e0:self.e1] - self.shift).contiguous()     # row-owned, for A and G
+        order = torch.argsort(self.ei_t[1], stable=True)                           # by target, rows ascending inside
+        self.order_t = order
+        self.ei_tT = torch.stack([self.ei_t[1][order], self.ei_t[0][order]]).contiguous()
+        self._graph = None
+
+    # scalar-row quantities for the solver ------------------------------------------------------------------
+    @property
+    def row_starts(self) -> List[int]:
+        return [v * self.b for v in self.starts]
+
+    @property
+    def layout(self) -> Layout:
+        return tuple(v * self.b for v in self.layout_nodes)
+
+    def ext_slice(self, t: torch.Tensor) -> torch.Tensor:
+        """Rows [shift, hi) of a per-node tensor, zero-padded where shift < 0."""
+        lo = max(self.shift, 0)
+        body = t[lo:self.hi]
+        if lo == self.shift:
+            return body.contiguous()
+        pad = torch.zeros((lo - self.shift,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        return torch.cat([pad, body]).contiguous()
+
+    # GNN ---------------------------------------------------------------------------------------------------
+    def gnn_forward(self, gnn, x: torch.Tensor, edge_attr: torch.Tensor) -> torch.Tensor:
+        """G values [E_t, b*b] of the target-owned edges (``ids_t`` order); bit-identical to the single-GPU forward on
+        those edges (per target the messages are summed in the same ascending edge order)."""
+        from .neural_cg.nn.gnns import DeviceGraph, F
+
+        lib = _lib.load()
+        if self._graph is None:
+            self._graph = DeviceGraph(self.ei_t, self.ext_nodes)
+        g = self._graph
+        x_loc = self.ext_slice(x.detach().to(torch.float32))
+        ea_loc = edge_attr.detach().to(torch.float32)[self.ids_t].contiguous()
+        out = torch.empty((self.ids_t.numel(), gnn.edge_out), dtype=torch.float32, device=x.device)
+        eng, L = gnn._get_engine(), gnn.num_mp_layers
+        for stage in range(L + 2):
+            _lib.check(lib.b200spai_gnn_forward_stage(eng, g._h, stage, _ptr(x_loc), _ptr(ea_loc), _ptr(out), _stream()),
+                       "gnn_forward_stage")
+            if 1 <= stage <= L and self.world > 1:
+                p = C.c_void_p()
+                _lib.check(lib.b200spai_gnn_node_features(g._h, stage, C.byref(p)), "gnn_node_features")
+                exchange_halo_rows(_wrap_f32(p.value, (self.ext_nodes, F), x.device), self.layouts_nodes, self.rank, self.group)
+        return out
+
+    def g_rows(self, g_t: torch.Tensor) -> torch.Tensor:  # collective
+        """G values of the row-owned edges (global edge order e0..e1) after the boundary swap."""
+        return exchange_g_rows(g_t, self.plan, self.group)
+
+    # assembly ----------------------------------------------------------------------------------------------
+    def _local_rows(self, ei: torch.Tensor, vals: torch.Tensor, mask_ext: Optional[torch.Tensor]) -> DeviceCSR:
+        """to_csr_cpu semantics on the extended node window, then the owned rows."""
+        full = DeviceCSR.from_edges(ei, vals, self.ext_nodes, mask_ext)
+        rs, re, shift, _ = self.layout
+        h = C.c_void_p()
+        _lib.check(_lib.load().b200spai_csr_slice_rows(full._h, rs - shift, re - shift, 0, self.ext_nodes * self.b, _stream(),
+                                                       C.byref(h)), "csr_slice_rows")
+        full.close()
+        return DeviceCSR(h)
+
+    def assemble(self, matrix_values: torch.Tensor, g_t: torch.Tensor, mask: Optional[torch.Tensor]):
+        """(A_loc, G_loc, GT_loc): owned rows of the masked fp64 CSR matrices, columns in the extended layout.
+        ``matrix_values`` [E, b, b] global (only rows e0..e1 are read), ``g_t`` from ``gnn_forward``."""
+        b = self.b
+        mask_ext = None if mask is None else self.ext_slice(mask.detach().to(torch.float32).reshape(self.N, b))
+        a_vals = matrix_values.detach().to(torch.float32).reshape(-1, b, b)[self.e0:self.e1].contiguous()
+        A_loc = self._local_rows(self.ei_r, a_vals, mask_ext)
+        g_t = g_t.reshape(-1, b, b)
+        G_loc = self._local_rows(self.ei_r, self.g_rows(g_t).contiguous(), mask_ext)
+        GT_loc = self._local_rows(self.ei_tT, g_t[self.order_t].transpose(1, 2).contiguous(), mask_ext)
+        return A_loc, G_loc, GT_loc
+
+    def make_solver(self, local, epsilon: float, mode: int = 0) -> "DistPCG":
+        return DistPCG(None, None, epsilon, self.row_starts, (0, 0), group=self.group, rank=self.rank, world=self.world,
+                       mode=mode, local=local, layout=self.layout)
+
+    def close(self):
+        if self._graph is not None:
+            self._graph.close()
+            self._graph = None
+
+
+def _wrap_f32(ptr: int, shape, device) -> torch.Tensor:
+    """Torch view of library-owned device memory (no copy) through the CUDA array interface."""
+    import math
+
+    class _Holder:
+        pass
+
+    h = _Holder()
+    h.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False), "version": 2,
+                                  "strides": None}
+    assert math.prod(shape) > 0
+    return torch.as_tensor(h, device=device)

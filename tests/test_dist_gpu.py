@@ -99,3 +99,53 @@ def test_multi_rank_matches_single_gpu(mode):
     line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
     out = json.loads(line)
     assert out["world"] == world and out["ext_spai"]["n_push"] >= 1
+
+
+@pytest.mark.parametrize("kind", ["poisson", "elast"])
+def test_partitioned_system_world1_matches_global(kind):
+    """PartitionedSystem with one rank: stage-wise GNN, local assembly (incl. G^T from the swapped edge list) and the
+    solver built from pre-assembled local matrices reproduce the global path bit for bit."""
+    from learningsparsepreconditioner4gpu_b200 import parallel as par, systems
+    from learningsparsepreconditioner4gpu_b200.device import DevicePCG
+    from learningsparsepreconditioner4gpu_b200.neural_cg.utils.validate import to_csr_device
+
+    if kind == "elast":
+        s, b = systems.elasticity_sample(8, 4, 4, seed=1, device="cuda"), 3
+    else:
+        s, b = systems.poisson_sample(12, seed=2, device="cuda"), 1
+    ws = systems.default_workspace(s, block_size=b)
+    N = s.num_nodes
+    n = N * b
+    ps = par.PartitionedSystem(s.edge_index, N, b, [0, N], rank=0, world=1)
+    g_t = ps.gnn_forward(ws.gnn, s.x, s.edge_attr)
+    g_ref = ws(s.x, s.edge_index, s.edge_attr)
+    assert torch.equal(g_t.reshape(-1, b, b), g_ref)
+    A_loc, G_loc, GT_loc = ps.assemble(s.matrix_values, g_t, s.mask)
+    A = to_csr_device(s.edge_index, s.matrix_values, n, s.mask)
+    G = to_csr_device(s.edge_index, g_ref, n, s.mask)
+    for loc, glob in ((A_loc, A.to_scipy()), (G_loc, G.to_scipy()), (GT_loc, G.to_scipy().T.tocsr())):
+        glob.sort_indices()
+        l = loc.to_scipy()
+        assert np.array_equal(l.indptr, glob.indptr) and np.array_equal(l.indices, glob.indices) and np.array_equal(l.data, glob.data)
+    rhs = A.matvec(s.mask.reshape(-1).double())
+    d = ps.make_solver((A_loc, G_loc, GT_loc), ws.epsilon)
+    x, res, hist = d.solve(rhs, "ext_spai", rtol=1e-8, history=True)
+    ref = DevicePCG(A)
+    ref.set_spai(G, ws.epsilon)
+    x1, res1, hist1 = ref.solve(rhs, "ext_spai", rtol=1e-8, history=True)
+    assert res.iterations == res1.iterations and torch.equal(hist, hist1) and torch.equal(x, x1)
+    d.close()
+    ps.close()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("kind", ["poisson", "elast"])
+def test_multi_rank_partitioned_gnn_and_assembly(kind):
+    world = min(torch.cuda.device_count(), 4)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(29631 + (kind == "elast")), os.path.join(ROOT, "tests", "dist_gnn_worker.py"), kind,
+           "20" if kind == "poisson" else "24"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    assert out["world"] == world and out["sent"] > 0 and out["edges_gnn"] < out["E"]

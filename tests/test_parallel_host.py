@@ -169,3 +169,95 @@ def test_gloo_world2_distributed_spmv_and_cg():
     assert all(ok for _, ok, _, _ in res)
     assert res[0][2] == res[1][2] and res[0][2] < 500          # same iteration count on both ranks
     assert max(e for *_, e in res) < 1e-6
+
+
+# ---------------------------------------------------------------------------------------------------------
+# partitioned GNN / assembly: edge ownership, G boundary swap, node-feature halo refresh
+# ---------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("world", [1, 2, 3, 5])
+def test_g_exchange_plan_covers_every_edge_once(world):
+    A = _grid_laplacian(6)
+    ei = _edges(A)
+    n, E = A.shape[0], ei.shape[1]
+    starts = par.partition_rows(par.row_weights_from_edges(ei, n), world)
+    plans = [par.g_exchange_plan(ei, starts, r) for r in range(world)]
+    G = torch.arange(E, dtype=torch.float64)                  # value = global edge id
+    seen_t = torch.zeros(E, dtype=torch.int64)
+    for r, (e0, e1, ids_t, loc_t, loc_r, send, recv) in enumerate(plans):
+        rs, re = starts[r], starts[r + 1]
+        assert bool(((ei[0][e0:e1] >= rs) & (ei[0][e0:e1] < re)).all()) and e1 - e0 == int(((ei[0] >= rs) & (ei[0] < re)).sum())
+        assert bool(((ei[1][ids_t] >= rs) & (ei[1][ids_t] < re)).all())
+        seen_t[ids_t] += 1
+        # the row slice is filled exactly once: locally or by one peer, with the right global edge
+        out = torch.full((e1 - e0,), -1.0, dtype=torch.float64)
+        out[loc_r] = G[ids_t][loc_t]
+        for q, idx in recv.items():
+            assert bool((out[idx] == -1).all())
+            out[idx] = G[plans[q][2]][plans[q][5][r]]           # what q sends to r, in q's order
+        assert torch.equal(out, G[e0:e1])
+        for q, idx in send.items():
+            assert r in plans[q][6] and plans[q][6][r].numel() == idx.numel()
+    assert bool((seen_t == 1).all())                          # every edge is computed by exactly one rank
+
+
+def test_halo_ranges_mirror_halo_plan():
+    A = _grid_laplacian(7)
+    ei = _edges(A)
+    n = A.shape[0]
+    for world in (2, 4):
+        starts = par.partition_rows(par.row_weights_from_edges(ei, n), world)
+        layouts = [par.rank_layout(starts[r], starts[r + 1], *par.extended_range(ei, starts[r], starts[r + 1])) for r in range(world)]
+        for r in range(world):
+            sends, recvs = par.halo_ranges(layouts, r)
+            pushes, precv = par.halo_plan(layouts, r)
+            assert [(q, o, l) for q, o, _, l in pushes] == sends and [q for q, _, _ in recvs] == precv
+            for q, off, length in recvs:                      # the matching send of q has the same length
+                (m,) = [s for s in par.halo_ranges(layouts, q)[0] if s[0] == r]
+                assert m[2] == length and m[1] + layouts[q][2] == off + layouts[r][2]
+
+
+def _worker_exchange(rank, world, port, q):
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        A = _grid_laplacian(7)
+        ei = _edges(A)
+        n, E = A.shape[0], ei.shape[1]
+        starts = par.partition_rows(par.row_weights_from_edges(ei, n), world)
+        gen = torch.Generator().manual_seed(5)
+        G = torch.randn(E, 3, 3, generator=gen)               # same "global G" on every rank, block size 3
+        X = torch.randn(n, 16, generator=gen)                 # same global node features
+        plan = par.g_exchange_plan(ei, starts, rank)
+        e0, e1, ids_t = plan[:3]
+        rows = par.exchange_g_rows(G[ids_t].contiguous(), plan)
+        ok_g = torch.equal(rows, G[e0:e1])
+        mine = par.rank_layout(starts[rank], starts[rank + 1], *par.extended_range(ei, starts[rank], starts[rank + 1]))
+        layouts = [tuple(t) for t in par._all_gather_object(mine, None)]
+        rs, re, shift, hi = mine
+        lo = max(shift, 0)
+        buf = torch.full((hi - shift, 16), float("nan"))
+        buf[rs - shift: re - shift] = X[rs:re]                # only the owned rows are valid
+        par.exchange_halo_rows(buf, layouts, rank)
+        ok_x = torch.equal(buf[lo - shift:], X[lo:hi])
+        q.put((rank, bool(ok_g), bool(ok_x)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_world3_g_swap_and_feature_halo():
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_worker_exchange, args=(r, 3, port, q)) for r in range(3)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(a and b for _, a, b in res), res
