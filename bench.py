@@ -38,7 +38,7 @@ UNIT = "solves/s"
 # PCG iterations of the default workload at rtol 1e-6, measured by the CUDA path (iteration parity with the oracle
 # is +-1 on every size the oracle can solve, tests/test_pcg_gpu.py).  Used ONLY by --impl reference to scale its
 # per-iteration CPU time to a whole solve without running ~10^3 s of scipy; override with B200SPAI_REF_ITERS.
-DEFAULT_ITERS = {216: 1372}
+DEFAULT_ITERS = {216: 1391}
 
 
 def log(*a):
@@ -501,19 +501,23 @@ def main_rowpart(args):
         local = ps.assemble(sample.matrix_values, g_t, sample.mask)
         rhs_loc = local[0].matvec(ps.ext_slice(sample.mask.reshape(N, ws.block_size)).reshape(-1).to(torch.float64))
         mark("G swap + assemble A, G, G^T rows")
-        solver = ps.make_solver(local, ws.epsilon)
-        mark("connect")
+        solver = ps.make_solver(local, ws.epsilon, reuse=True)   # the IPC connection is kept between steps
+        mark("connect / relayout")
         x, res, _ = solver.solve(rhs_loc, "ext_spai", rtol=args.rtol)
         mark("pcg (row-partitioned)")
         info = solver.info()
+        if timers is None and os.environ.get("B200SPAI_DIST_PROFILE"):     # warm-up steps only: per-launch times
+            info["per_launch_ms"] = solver.profile_iterations(rhs_loc, 50)
         info["edges_gnn"] = int(ps.ids_t.numel())
-        dist.barrier()      # nobody unmaps a segment a slower peer might still be writing to
-        solver.close()
+        solver.close()      # parks the connection for the next step
         ps.close()
         return res, info
 
     for _ in range(max(args.warmup, 1)):
         res, info = step()
+    prof = info.get("per_launch_ms")
+    if prof:
+        log(f"[rowpart r{rank}] per-launch ms: {prof}")
     launches0 = _lib.total_launches()
     timers = []
     barrier()
@@ -544,6 +548,8 @@ def main_rowpart(args):
             "phases_ms_per_step": {k: round(v / args.steps, 3) for k, v in ph.items()}, "gpu_launches": int(launches),
         }
         print(json.dumps(line), flush=True)
+    barrier()
+    par.DistPCG.drop_connections()
     dist.destroy_process_group()
 
 

@@ -204,6 +204,9 @@ typedef struct b200spai_dist_s* b200spai_dist_t;
 int b200spai_dist_create(int32_t rank, int32_t world, int64_t ext_cap, b200spai_dist_t* out);
 int b200spai_dist_ipc_handle(b200spai_dist_t d, unsigned char* handle64);
 int b200spai_dist_connect(b200spai_dist_t d, const unsigned char* handles, const int64_t* layout);
+/* Reuse a connected handle for the next system: new layout [world][4] of every rank (collective).  Keeps the mapped
+ * segments (ext_cap must still suffice); the matrices are attached again with b200spai_dist_pcg_setup. */
+int b200spai_dist_relayout(b200spai_dist_t d, const int64_t* layout);
 int b200spai_dist_info(b200spai_dist_t d, int32_t* n_push, int32_t* n_recv, int64_t* push_elems, int32_t* owned_offset);
 int b200spai_csr_slice_rows(b200spai_csr_t a, int32_t r0, int32_t r1, int64_t shift, int32_t n_cols_local, void* stream,
                             b200spai_csr_t* out);
@@ -213,6 +216,11 @@ int b200spai_dist_pcg_set_mode(b200spai_dist_t d, int mode);
 /* b / x: the owned rows only.  max_iter must be given (> 0).  resid_hist_dev: NULL or max_iter+1 doubles. */
 int b200spai_dist_pcg_solve(b200spai_dist_t d, int precond, const double* b_local_dev, double* x_local_dev, double rtol,
                             int32_t max_iter, double* resid_hist_dev, void* stream, b200spai_pcg_result* result);
+/* Measurement hook (collective): run exactly `iterations` (<= 256) ext_spai PCG updates with a CUDA event after every
+ * launch; kernel_ms8 = mean device time of {t = G^T r, halo t, z = G t, all-reduce rho + push z, p update, q = A p,
+ * all-reduce p.q + push q, x/r update}; a synchronisation launch includes the wait for the slowest neighbour. */
+int b200spai_dist_pcg_profile_iterations(b200spai_dist_t d, int precond, const double* b_local_dev, double* x_local_dev,
+                                         int32_t iterations, float* kernel_ms8, void* stream);
 int b200spai_dist_destroy(b200spai_dist_t d);
 
 #ifdef __cplusplus

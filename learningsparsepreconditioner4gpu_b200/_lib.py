@@ -60,11 +60,13 @@ SIGNATURES = {
     "b200spai_dist_create": [c_i32, c_i32, c_i64, C.POINTER(c_vp)],
     "b200spai_dist_ipc_handle": [c_vp, c_vp],
     "b200spai_dist_connect": [c_vp, c_vp, c_vp],
+    "b200spai_dist_relayout": [c_vp, c_vp],
     "b200spai_dist_info": [c_vp, C.POINTER(c_i32), C.POINTER(c_i32), C.POINTER(c_i64), C.POINTER(c_i32)],
     "b200spai_csr_slice_rows": [c_vp, c_i32, c_i32, c_i64, c_i32, c_vp, C.POINTER(c_vp)],
     "b200spai_dist_pcg_setup": [c_vp, c_vp, c_vp, c_vp, c_f64],
     "b200spai_dist_pcg_set_mode": [c_vp, C.c_int],
     "b200spai_dist_pcg_solve": [c_vp, C.c_int, c_vp, c_vp, c_f64, c_i32, c_vp, c_vp, C.POINTER(PcgResult)],
+    "b200spai_dist_pcg_profile_iterations": [c_vp, C.c_int, c_vp, c_vp, c_i32, C.POINTER(C.c_float), c_vp],
     "b200spai_dist_destroy": [c_vp],
 }
 

@@ -28,7 +28,7 @@
 namespace b200spai {
 
 constexpr int MAXR = 16;
-enum { V_P = 0, V_R = 1, V_T = 2, NVEC = 3 };
+enum { V_P = 0, V_R = 1, V_T = 2, V_Z = 3, V_Q = 4, NVEC = 5 };
 enum { RED_INIT = 0, RED_RHO = 1 /* + ||r||^2 */, RED_PQ = 2, NRED = 3 };
 
 // header of the symmetric segment (same offsets on every rank)
@@ -64,10 +64,19 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
   return v;
 }
 
-// Wait until *flag >= epoch.  On timeout the solve is marked broken so that every later kernel returns at once.
+__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+
+// Wait until *flag >= epoch: relaxed polls (a system-scope acquire costs microseconds, so it is not repeated per
+// poll) and ONE acquire fence once the flag is there.  On timeout the solve is marked broken so that every later
+// kernel returns at once.
 __device__ __forceinline__ void dist_wait(const DistCtx& c, const unsigned long long* flag, unsigned long long epoch) {
   const long long t0 = clock64();
-  while (ld_acquire_sys(flag) < epoch) {
+  while (ld_relaxed_sys(flag) < epoch) {
     if (clock64() - t0 > c.spin_limit) {
       c.sc->breakdown = 3;
       c.sc->done = 1;
@@ -75,6 +84,7 @@ __device__ __forceinline__ void dist_wait(const DistCtx& c, const unsigned long 
       break;
     }
   }
+  fence_acq_rel_sys();
 }
 
 // ---- halo exchange of one extended vector ---------------------------------------------------------------------
@@ -97,8 +107,8 @@ __global__ void __launch_bounds__(256) dist_halo_kernel(const __grid_constant__ 
   }
   __syncthreads();
   if (!s_last) return;
-  // every CTA's peer stores precede its ticket; this CTA drew the last one
-  __threadfence_system();
+  // every CTA's peer stores precede (fence.sys) its ticket; this CTA drew the last one, and the release stores below
+  // (fence.sys + store) are cumulative over what the ticket atomics made visible to it
   if (threadIdx.x == 0) {
     *c.ticket = 0u;
     s_epoch = ++c.epoch[v];
@@ -113,11 +123,37 @@ __global__ void __launch_bounds__(256) dist_halo_kernel(const __grid_constant__ 
 // RED_RHO also carries ||r||^2 of the preceding x/r update (sc->have_rr): the convergence test is applied first, then
 // rho / beta -- the order of the single-GPU solver -- so the t = G^T r and z = G t kernels of an iteration that turns out
 // not to be needed have run speculatively (they only write t and z) and the exchange count drops from 3 to 2.
-__global__ void __launch_bounds__(32) dist_reduce_kernel(const __grid_constant__ DistCtx c, int kind) {
+// With v >= 0 the same launch first pushes the owned boundary slices of extended vector v into the neighbours (all
+// CTAs, like dist_halo_kernel); the CTA that draws the last ticket then runs the all-reduce, whose release / acquire
+// flags order the pushed slices as well -- z travels with rho and q with p.q, so an iteration has 3 synchronisation
+// points (t, rho + z, p.q + q) instead of 5; p and r are updated on the halo by the vector kernels themselves.
+__global__ void __launch_bounds__(256) dist_reduce_kernel(const __grid_constant__ DistCtx c, int kind, int v) {
   __shared__ double s_val[MAXR], s_val2[MAXR];
   __shared__ unsigned long long s_epoch;
+  __shared__ int s_last;
   PcgScalars* sc = c.sc;
   if (kind != RED_INIT && sc->done) return;
+  if (v >= 0 && c.n_push > 0) {
+    const double* mine = c.vec[v][c.rank];
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (int s = 0; s < c.n_push; ++s) {
+      double* __restrict__ dst = c.vec[v][c.push_peer[s]] + c.push_dst_off[s];
+      const double* __restrict__ src = mine + c.push_src_off[s];
+      for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < c.push_len[s]; i += stride) dst[i] = src[i];
+    }
+    __threadfence_system();
+  }
+  if (gridDim.x > 1) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned tk = atomicAdd(c.ticket, 1u);
+      s_last = (tk == gridDim.x - 1);
+      if (s_last) *c.ticket = 0u;
+    }
+    __syncthreads();
+    if (!s_last) return;  // every CTA's peer stores precede (fence.sys) its ticket; this CTA drew the last one
+  }
+  if (threadIdx.x >= 32) return;
   const int t = threadIdx.x;
   if (t == 0) s_epoch = ++c.epoch[NVEC + kind];
   __syncwarp();
@@ -128,8 +164,7 @@ __global__ void __launch_bounds__(32) dist_reduce_kernel(const __grid_constant__
   if (t < c.world) {
     c.hdr[t]->red_val[kind][c.rank] = local;
     if (with_rr) c.hdr[t]->red_val2[kind][c.rank] = local2;
-    __threadfence_system();
-    st_release_sys(&c.hdr[t]->red_epoch[kind][c.rank], ep);
+    st_release_sys(&c.hdr[t]->red_epoch[kind][c.rank], ep);  // orders the two stores above (same thread) and the pushes
   }
   if (t < c.world) {
     dist_wait(c, &c.hdr[c.rank]->red_epoch[kind][t], ep);
@@ -204,6 +239,7 @@ struct b200spai_dist_s {
   int n = 0, off = 0;  // owned rows, offset of the owned slice inside the extended vectors
   double *z = nullptr, *q = nullptr, *xw = nullptr, *bw = nullptr, *d = nullptr, *partials = nullptr, *hist = nullptr;
   bool have_d = false;
+  size_t vec_cap = 0;  // capacity (doubles) of xw, bw
   long long hist_cap = 0;
   PcgScalars* sc = nullptr;
   unsigned *ticket = nullptr, *ticket_halo = nullptr;
@@ -249,8 +285,9 @@ static int dist_enqueue_halo(b200spai_dist_s* s, int v, cudaStream_t st, int* nl
   return 0;
 }
 
-static int dist_enqueue_reduce(b200spai_dist_s* s, int kind, cudaStream_t st, int* nl) {
-  dist_reduce_kernel<<<1, 32, 0, st>>>(s->ctx, kind);
+static int dist_enqueue_reduce(b200spai_dist_s* s, int kind, cudaStream_t st, int* nl, int v = -1) {
+  const bool push = (v >= 0 && s->world > 1 && s->ctx.n_push > 0);
+  dist_reduce_kernel<<<push ? halo_grid(s) : 1, 256, 0, st>>>(s->ctx, kind, push ? v : -1);
   B2_LAUNCH_CHECK();
   *nl += 1;
   return 0;
@@ -266,7 +303,16 @@ static int dist_enqueue_init(b200spai_dist_s* s, const double* b, double* x, cud
   return 0;
 }
 
-static int dist_enqueue_iteration(b200spai_dist_s* s, int precond, double* x, cudaStream_t st, int* nl) {
+// marks: optional array of 8 events recorded after the launches of one iteration, in the order
+// {t = G^T r, halo t, z = G t (+ r.z), all-reduce rho + push z, p update, q = A p (+ p.q), all-reduce p.q + push q, x/r update}
+// (measurement hook b200spai_dist_pcg_profile_iterations).
+static int dist_enqueue_iteration(b200spai_dist_s* s, int precond, double* x, cudaStream_t st, int* nl,
+                                  cudaEvent_t* marks = nullptr) {
+  int mk = 0;
+  auto mark = [&]() {
+    if (marks) cudaEventRecord(marks[mk], st);
+    ++mk;
+  };
   double *r_ext = s->vec(V_R), *p_ext = s->vec(V_P), *t_ext = s->vec(V_T);
   double *r = r_ext + s->off, *p = p_ext + s->off, *t = t_ext + s->off;
   if (precond == B200SPAI_PRECOND_NONE || precond == B200SPAI_PRECOND_DIAGONAL) {
@@ -283,7 +329,9 @@ static int dist_enqueue_iteration(b200spai_dist_s* s, int precond, double* x, cu
     a1.sc = s->sc;
     B2_TRY(spmv_launch(s->GT, a1, scaled ? SPMV_SCALE : SPMV_PLAIN, 0, st));
     *nl += 1;
+    mark();
     B2_TRY(dist_enqueue_halo(s, V_T, st, nl));
+    mark();
     SpmvArgs a2{};
     a2.x = t_ext;
     a2.y = s->z;
@@ -297,11 +345,15 @@ static int dist_enqueue_iteration(b200spai_dist_s* s, int precond, double* x, cu
     B2_TRY(spmv_launch(s->G, a2, SPMV_AXPY_DOT, 0, st));
     *nl += 1;
   }
-  B2_TRY(dist_enqueue_reduce(s, RED_RHO, st, nl));
-  pcg_update_p_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(s->z, p, s->n, s->sc);
+  mk = 2;
+  mark();
+  const int lo_halo = s->off, hi_halo = (int)(s->hi - s->re);
+  B2_TRY(dist_enqueue_reduce(s, RED_RHO, st, nl, V_Z));  // z's boundary travels with rho
+  mark();
+  pcg_update_p_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(s->z, p, s->n, s->sc, lo_halo, hi_halo);
   B2_LAUNCH_CHECK();
   *nl += 1;
-  B2_TRY(dist_enqueue_halo(s, V_P, st, nl));
+  mark();
   SpmvArgs a{};
   a.x = p_ext;
   a.aux = p;
@@ -312,12 +364,17 @@ static int dist_enqueue_iteration(b200spai_dist_s* s, int precond, double* x, cu
   a.final_op = FINAL_PQ;
   B2_TRY(spmv_launch(s->A, a, SPMV_DOT, 0, st));
   *nl += 1;
-  B2_TRY(dist_enqueue_reduce(s, RED_PQ, st, nl));
-  pcg_update_xr_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(x, r, p, s->q, s->n, s->sc, s->partials, s->ticket, s->hist);
+  mark();
+  // q's boundary travels with p.q (only the SPAI preconditioners gather r, through t = G^T r);
+  // ||r||^2 is all-reduced together with the next rho (dist_reduce_kernel)
+  const bool need_r = precond >= B200SPAI_PRECOND_EXT_SPAI;
+  B2_TRY(dist_enqueue_reduce(s, RED_PQ, st, nl, need_r ? V_Q : -1));
+  mark();
+  pcg_update_xr_kernel<<<vec_grid(s->n), VTHREADS, 0, st>>>(x, r, p, s->q, s->n, s->sc, s->partials, s->ticket, s->hist,
+                                                            need_r ? lo_halo : 0, need_r ? hi_halo : 0);
   B2_LAUNCH_CHECK();
   *nl += 1;
-  // ||r||^2 is all-reduced together with the next rho (dist_reduce_kernel); the next t = G^T r gathers r
-  if (precond >= B200SPAI_PRECOND_EXT_SPAI) B2_TRY(dist_enqueue_halo(s, V_R, st, nl));
+  mark();
   return 0;
 }
 
@@ -386,6 +443,64 @@ int b200spai_dist_ipc_handle(b200spai_dist_t s, unsigned char* handle64) {
 
 // handles: [world][64] as gathered from every rank; layout: [world][4] = {row_start, row_end, shift, hi} per rank
 // (extended range [shift, hi); shift may be row-aligned down by one so that the owned slice starts 16-byte aligned).
+// The layout-dependent part of the connection: owned rows, extended range, push / receive plan, local vectors.
+static int dist_apply_layout(b200spai_dist_s* s, const int64_t* L) {
+  const int R = s->world, me = s->rank;
+  const int64_t rs = L[me * 4 + 0], re = L[me * 4 + 1], shift = L[me * 4 + 2], hi = L[me * 4 + 3];
+  B2_ARG(rs <= re && shift <= rs && hi >= re, "dist layout: inconsistent layout");
+  B2_ARG(hi - shift <= s->ext_cap, "dist layout: extended range exceeds the segment capacity");
+  B2_ARG(((rs - shift) & 1) == 0, "dist layout: the owned slice must start at an even extended index");
+  s->rs = rs;
+  s->re = re;
+  s->shift = shift;
+  s->hi = hi;
+  s->n = (int)(re - rs);
+  s->off = (int)(rs - shift);
+  DistCtx& c = s->ctx;
+  c.rank = me;
+  c.world = R;
+  c.n_push = c.n_recv = 0;
+  for (int q = 0; q < R; ++q) {
+    auto* base = reinterpret_cast<unsigned char*>(s->peer_seg[q]);
+    c.hdr[q] = reinterpret_cast<SegHeader*>(base);
+    for (int v = 0; v < NVEC; ++v)
+      c.vec[v][q] = reinterpret_cast<double*>(base + SEG_VEC_OFFSET) + (size_t)v * (size_t)s->ext_cap;
+  }
+  for (int q = 0; q < R; ++q) {
+    if (q == me) continue;
+    const int64_t rs_q = L[q * 4 + 0], re_q = L[q * 4 + 1], lo_q = L[q * 4 + 2], hi_q = L[q * 4 + 3];
+    const int64_t a = std::max<int64_t>(s->rs, lo_q), b = std::min<int64_t>(s->re, hi_q);  // what q needs from my rows
+    if (a < b) {
+      const int k = c.n_push++;
+      c.push_peer[k] = q;
+      c.push_dst_off[k] = a - lo_q;
+      c.push_src_off[k] = a - s->shift;
+      c.push_len[k] = (int)(b - a);
+    }
+    const int64_t a2 = std::max<int64_t>(rs_q, s->shift), b2 = std::min<int64_t>(re_q, s->hi);  // what I need from q
+    if (a2 < b2) c.recv_peer[c.n_recv++] = q;
+  }
+  const size_t n = (size_t)(s->n > 0 ? s->n : 1);
+  if (n + 2 > s->vec_cap) {  // local vectors (owned rows)
+    int rc = 0;
+    for (double** v : {&s->xw, &s->bw}) {
+      dev_free(*v);
+      *v = nullptr;
+      if (!rc) rc = dev_alloc(v, n + 2);
+    }
+    if (rc) return rc;
+    s->vec_cap = n + 2;
+  }
+  s->z = s->vec(V_Z) + s->off;  // z and q are extended vectors too: their boundaries travel with the all-reduces
+  s->q = s->vec(V_Q) + s->off;
+  dev_free(s->d);
+  s->d = nullptr;
+  s->have_d = false;
+  s->A = s->G = s->GT = nullptr;
+  dist_drop_graphs(s);
+  return 0;
+}
+
 int b200spai_dist_connect(b200spai_dist_t s, const unsigned char* handles, const int64_t* layout) {
   B2_ARG(s && layout && (handles || s->world == 1), "dist_connect: NULL argument");
   B2_ARG(!s->connected, "dist_connect: already connected");
@@ -396,48 +511,10 @@ int b200spai_dist_connect(b200spai_dist_t s, const unsigned char* handles, const
     memcpy(&h, handles + (size_t)q * 64, 64);
     B2_CUDA(cudaIpcOpenMemHandle(&s->peer_seg[q], h, cudaIpcMemLazyEnablePeerAccess));
   }
-  const int64_t* L = layout;
-  s->rs = L[me * 4 + 0];
-  s->re = L[me * 4 + 1];
-  s->shift = L[me * 4 + 2];
-  s->hi = L[me * 4 + 3];
-  B2_ARG(s->rs <= s->re && s->shift <= s->rs && s->hi >= s->re, "dist_connect: inconsistent layout");
-  B2_ARG(s->hi - s->shift <= s->ext_cap, "dist_connect: extended range exceeds the segment capacity");
-  B2_ARG(((s->rs - s->shift) & 1) == 0, "dist_connect: the owned slice must start at an even extended index");
-  s->n = (int)(s->re - s->rs);
-  s->off = (int)(s->rs - s->shift);
+  s->ctx = DistCtx{};
+  B2_TRY(dist_apply_layout(s, layout));
   DistCtx& c = s->ctx;
-  c = DistCtx{};
-  c.rank = me;
-  c.world = R;
-  for (int q = 0; q < R; ++q) {
-    auto* base = reinterpret_cast<unsigned char*>(s->peer_seg[q]);
-    c.hdr[q] = reinterpret_cast<SegHeader*>(base);
-    for (int v = 0; v < NVEC; ++v)
-      c.vec[v][q] = reinterpret_cast<double*>(base + SEG_VEC_OFFSET) + (size_t)v * (size_t)s->ext_cap;
-  }
-  for (int q = 0; q < R; ++q) {
-    if (q == me) continue;
-    const int64_t rs_q = L[q * 4 + 0], re_q = L[q * 4 + 1], lo_q = L[q * 4 + 2], hi_q = L[q * 4 + 3];
-    // what q needs from my owned rows
-    const int64_t a = std::max<int64_t>(s->rs, lo_q), b = std::min<int64_t>(s->re, hi_q);
-    if (a < b) {
-      const int k = c.n_push++;
-      c.push_peer[k] = q;
-      c.push_dst_off[k] = a - lo_q;
-      c.push_src_off[k] = a - s->shift;
-      c.push_len[k] = (int)(b - a);
-    }
-    // what I need from q's owned rows
-    const int64_t a2 = std::max<int64_t>(rs_q, s->shift), b2 = std::min<int64_t>(re_q, s->hi);
-    if (a2 < b2) c.recv_peer[c.n_recv++] = q;
-  }
-  // local solver state
-  const size_t n = (size_t)(s->n > 0 ? s->n : 1);
-  int rc = 0;
-  for (double** v : {&s->z, &s->q, &s->xw, &s->bw})
-    if (!rc) rc = dev_alloc(v, n + 2);
-  if (!rc) rc = dev_alloc(&s->sc, 1);
+  int rc = dev_alloc(&s->sc, 1);
   if (!rc) rc = dev_alloc(&s->partials, 8192);
   if (!rc) rc = dev_alloc(&s->ticket, 1);
   if (!rc) rc = dev_alloc(&s->ticket_halo, 1);
@@ -469,6 +546,18 @@ int b200spai_dist_connect(b200spai_dist_t s, const unsigned char* handles, const
   c.spin_limit = (long long)(secs * 1e3 * (double)khz);
   s->connected = true;
   return 0;
+}
+
+// A connected handle is reusable for the next system (same ranks, another partition): the new layout of every rank,
+// collective like dist_connect.  The mapped segments, the epoch counters and the streams are kept, so the per-system
+// cost is the index arithmetic of the plan; the matrices must be attached again with b200spai_dist_pcg_setup.
+int b200spai_dist_relayout(b200spai_dist_t s, const int64_t* layout) {
+  B2_ARG(s && layout && s->connected, "dist_relayout: not connected or NULL layout");
+  B2_CUDA(cudaDeviceSynchronize());  // no kernel of the previous solve may still use the old plan
+  // stale vectors of the previous system: a peer only writes into this segment after the first all-reduce of the
+  // next solve, which needs this rank's contribution, so clearing here cannot race with its pushes
+  B2_CUDA(cudaMemset(s->seg + SEG_VEC_OFFSET, 0, s->seg_bytes - SEG_VEC_OFFSET));
+  return dist_apply_layout(s, layout);
 }
 
 int b200spai_dist_info(b200spai_dist_t s, int32_t* n_push, int32_t* n_recv, int64_t* push_elems, int32_t* owned_offset) {
@@ -694,13 +783,53 @@ int b200spai_dist_pcg_solve(b200spai_dist_t s, int precond, const double* b_loca
   return 0;
 }
 
+// Measurement hook (collective): `iterations` PCG updates from x0 = 0 with no convergence test, every launch followed
+// by a CUDA event; kernel_ms8 = mean device time per launch class in the order of dist_enqueue_iteration's marks
+// (a synchronisation kernel's time includes waiting for the slowest neighbour).
+int b200spai_dist_pcg_profile_iterations(b200spai_dist_t s, int precond, const double* b_local_dev, double* x_local_dev,
+                                         int32_t iterations, float* kernel_ms8, void* stream) {
+  B2_ARG(s && s->connected && s->A && b_local_dev && x_local_dev && kernel_ms8 && iterations > 0 && iterations <= 256,
+         "dist_pcg_profile_iterations: bad argument");
+  B2_ARG(precond >= B200SPAI_PRECOND_EXT_SPAI && s->G && s->GT, "dist_pcg_profile_iterations: needs ext_spai with G and G^T");
+  cudaStream_t st = as_stream(stream);
+  B2_TRY(dist_ensure_hist(s, (long long)iterations + 2));
+  B2_TRY(dist_warm(s, precond, st));
+  PcgScalars init{};
+  init.rtol = 0.0;
+  init.max_iter = iterations + 1;
+  init.dist = 1;
+  B2_CUDA(cudaMemcpyAsync(s->sc, &init, sizeof(PcgScalars), cudaMemcpyHostToDevice, st));
+  std::vector<cudaEvent_t> ev((size_t)iterations * 8 + 1);
+  for (auto& e : ev) B2_CUDA(cudaEventCreate(&e));
+  int nl = 0;
+  int rc = dist_enqueue_init(s, b_local_dev, x_local_dev, st, &nl);
+  cudaEventRecord(ev[0], st);
+  for (int it = 0; it < iterations && !rc; ++it) rc = dist_enqueue_iteration(s, precond, x_local_dev, st, &nl, &ev[1 + (size_t)it * 8]);
+  cudaError_t e = cudaStreamSynchronize(st);
+  for (int k = 0; k < 8; ++k) kernel_ms8[k] = 0.0f;
+  if (!rc && e == cudaSuccess) {
+    for (int it = 0; it < iterations; ++it)
+      for (int k = 0; k < 8; ++k) {
+        float ms = 0.0f;
+        cudaEventElapsedTime(&ms, ev[(size_t)it * 8 + k], ev[(size_t)it * 8 + k + 1]);
+        kernel_ms8[k] += ms / (float)iterations;
+      }
+  }
+  for (auto& x : ev) cudaEventDestroy(x);
+  s->launches += nl;
+  count_launches(nl);
+  if (rc) return rc;
+  B2_CUDA(e);
+  return 0;
+}
+
 int b200spai_dist_destroy(b200spai_dist_t s) {
   if (!s) return 0;
   dist_drop_graphs(s);
   for (int q = 0; q < s->world; ++q)
     if (q != s->rank && s->peer_seg[q]) cudaIpcCloseMemHandle(s->peer_seg[q]);
   cudaFree(s->seg);
-  for (double* v : {s->z, s->q, s->xw, s->bw, s->d, s->partials, s->hist}) dev_free(v);
+  for (double* v : {s->xw, s->bw, s->d, s->partials, s->hist}) dev_free(v);
   dev_free(s->sc);
   dev_free(s->ticket);
   dev_free(s->ticket_halo);

@@ -97,8 +97,12 @@ static __global__ void __launch_bounds__(VTHREADS) pcg_jacobi_kernel(const doubl
 }
 
 // The two vector kernels move 16 bytes per thread and access (double2) with two independent pairs in flight.
+// lo_halo / hi_halo (row-partitioned solve): the same update is also applied to the halo entries [-lo_halo, 0) and
+// [n, n + hi_halo) of the extended vectors, whose z arrived with the rho all-reduce -- identical roundings, so a halo
+// entry carries the bits its owner computes and p needs no exchange of its own.
 static __global__ void __launch_bounds__(VTHREADS) pcg_update_p_kernel(const double* __restrict__ z, double* __restrict__ p,
-                                                                int n, const PcgScalars* sc) {
+                                                                int n, const PcgScalars* sc, int lo_halo = 0,
+                                                                int hi_halo = 0) {
   if (sc->done) return;
   const bool first = (sc->iter == 0);
   const double beta = sc->beta;
@@ -121,12 +125,17 @@ static __global__ void __launch_bounds__(VTHREADS) pcg_update_p_kernel(const dou
     const double zv = z[n - 1];
     p[n - 1] = first ? zv : __dadd_rn(__dmul_rn(p[n - 1], beta), zv);
   }
+  for (long long h = (long long)blockIdx.x * blockDim.x + threadIdx.x; h < (long long)lo_halo + hi_halo; h += stride) {
+    const long long i = h < lo_halo ? h - lo_halo : n + (h - lo_halo);
+    const double zv = z[i];
+    p[i] = first ? zv : __dadd_rn(__dmul_rn(p[i], beta), zv);
+  }
 }
 
 static __global__ void __launch_bounds__(VTHREADS) pcg_update_xr_kernel(double* __restrict__ x, double* __restrict__ r,
                                                                  const double* __restrict__ p, const double* __restrict__ q,
                                                                  int n, PcgScalars* sc, double* partials, unsigned* ticket,
-                                                                 double* hist) {
+                                                                 double* hist, int lo_halo = 0, int hi_halo = 0) {
   __shared__ double red[34];
   if (sc->done) {  // never inside the loop of a healthy solve; keeps a WHILE body from spinning if it happens
     if (sc->use_cond && blockIdx.x == 0 && threadIdx.x == 0)
@@ -160,6 +169,11 @@ static __global__ void __launch_bounds__(VTHREADS) pcg_update_xr_kernel(double* 
     const double rv = __dsub_rn(r[i], __dmul_rn(alpha, q[i]));
     r[i] = rv;
     acc += rv * rv;
+  }
+  // halo entries of r (row-partitioned solve; q's halo arrived with the p.q all-reduce): not part of ||r||^2
+  for (long long h = (long long)blockIdx.x * blockDim.x + threadIdx.x; h < (long long)lo_halo + hi_halo; h += stride) {
+    const long long i = h < lo_halo ? h - lo_halo : n + (h - lo_halo);
+    r[i] = __dsub_rn(r[i], __dmul_rn(alpha, q[i]));
   }
   double cta = block_sum(acc, red);
   double total;

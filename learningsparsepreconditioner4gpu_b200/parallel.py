@@ -100,13 +100,25 @@ class DistPCG:
     ``A``, ``G`` are the GLOBAL matrices resident on this rank's GPU (v1: every rank assembles the whole system and
     keeps only its rows); ``row_starts`` comes from ``partition_rows`` and must be identical on every rank."""
 
+    _connections: dict = {}   # (rank, world, group id) -> (handle, capacity): parked by close() when reuse=True
+
+    @classmethod
+    def drop_connections(cls):
+        """Tear down the parked connections (collective: call on every rank, after a barrier)."""
+        lib = _lib.load()
+        for h, _ in cls._connections.values():
+            lib.b200spai_dist_destroy(h)
+        cls._connections.clear()
+
     def __init__(self, A: Optional[DeviceCSR], G: Optional[DeviceCSR], epsilon: float, row_starts: Sequence[int],
                  ext: Tuple[int, int], group=None, rank: Optional[int] = None, world: Optional[int] = None, mode: int = 0,
                  local: Optional[Tuple[DeviceCSR, Optional[DeviceCSR], Optional[DeviceCSR]]] = None,
-                 layout: Optional[Layout] = None):
+                 layout: Optional[Layout] = None, reuse: bool = False):
         """``local`` = (A_loc, G_loc, GT_loc): the owned rows already assembled in the extended column layout
         (``PartitionedSystem.assemble``); then ``A`` / ``G`` are ignored and nothing global is needed on this rank.
-        ``layout`` overrides the layout derived from ``ext`` (block systems keep it node-aligned)."""
+        ``layout`` overrides the layout derived from ``ext`` (block systems keep it node-aligned).
+        ``reuse``: ``close`` parks the connection (peer-visible segment + IPC mappings, ~70 ms to set up) for the next
+        ``DistPCG(..., reuse=True)`` of the same ranks instead of tearing it down -- every rank must pass the same flag."""
         self._lib = _lib.load()
         _lib.require_cuda()
         if world is None:
@@ -122,15 +134,27 @@ class DistPCG:
         self.layouts: List[Layout] = ([self.layout] if self.world == 1 else
                                       [tuple(int(v) for v in t) for t in _all_gather_object(self.layout, group)])
         ext_cap = max(l[3] - l[2] for l in self.layouts)
-        self._h = C.c_void_p()
-        _lib.check(self._lib.b200spai_dist_create(self.rank, self.world, ext_cap, C.byref(self._h)), "dist_create")
-        handles = None
-        if self.world > 1:
-            hb = (C.c_ubyte * 64)()
-            _lib.check(self._lib.b200spai_dist_ipc_handle(self._h, hb), "dist_ipc_handle")
-            handles = b"".join(_all_gather_object(bytes(hb), group))
         lay = (C.c_int64 * (4 * self.world))(*[v for l in self.layouts for v in l])
-        _lib.check(self._lib.b200spai_dist_connect(self._h, handles, lay), "dist_connect")
+        self._key = (self.rank, self.world, id(group))
+        cached = DistPCG._connections.pop(self._key, None) if reuse else None
+        if cached is not None and cached[1] < ext_cap:      # identical decision on every rank (ext_cap is global)
+            self._lib.b200spai_dist_destroy(cached[0])
+            cached = None
+        self._reuse = bool(reuse)
+        if cached is not None:
+            # the CUDA-IPC mappings of the peers' segments survive from the previous system: only the plan changes
+            self._h, self._cap = cached
+            _lib.check(self._lib.b200spai_dist_relayout(self._h, lay), "dist_relayout")
+        else:
+            self._cap = ext_cap + ext_cap // 4 if reuse else ext_cap
+            self._h = C.c_void_p()
+            _lib.check(self._lib.b200spai_dist_create(self.rank, self.world, self._cap, C.byref(self._h)), "dist_create")
+            handles = None
+            if self.world > 1:
+                hb = (C.c_ubyte * 64)()
+                _lib.check(self._lib.b200spai_dist_ipc_handle(self._h, hb), "dist_ipc_handle")
+                handles = b"".join(_all_gather_object(bytes(hb), group))
+            _lib.check(self._lib.b200spai_dist_connect(self._h, handles, lay), "dist_connect")
         # local matrices: owned rows, columns shifted into the extended layout
         _, _, shift, hi = self.layout
         self.n_local, self.ext_len = re - rs, hi - shift
@@ -177,6 +201,16 @@ class DistPCG:
             hist = hist[: res.iterations + 1]
         return x, res, hist
 
+    PROFILE_KEYS = ("GT_r", "halo_t", "G_t", "allreduce_rho+push_z", "update_p", "A_p", "allreduce_pq+push_q", "update_xr")
+
+    def profile_iterations(self, b_local: torch.Tensor, iterations: int = 50, precond: str = "ext_spai") -> dict:
+        """Mean device time (ms) of every launch of one iteration (collective; measurement only)."""
+        x = torch.empty(max(self.n_local, 1), dtype=torch.float64, device=b_local.device)
+        out = (C.c_float * 8)()
+        _lib.check(self._lib.b200spai_dist_pcg_profile_iterations(self._h, PRECOND[precond], _ptr(b_local.contiguous()), _ptr(x),
+                                                                  int(iterations), out, _stream()), "dist_pcg_profile_iterations")
+        return {k: round(float(v), 5) for k, v in zip(self.PROFILE_KEYS, out)}
+
     def gather(self, x_local: torch.Tensor) -> torch.Tensor:
         """The full solution vector on every rank (plumbing for checks; NCCL all_gather of ragged pieces)."""
         if self.world == 1:
@@ -193,7 +227,13 @@ class DistPCG:
 
     def close(self):
         if self._h:
-            self._lib.b200spai_dist_destroy(self._h)
+            if getattr(self, "_reuse", False):
+                old = DistPCG._connections.pop(self._key, None)
+                if old is not None:
+                    self._lib.b200spai_dist_destroy(old[0])
+                DistPCG._connections[self._key] = (self._h, self._cap)
+            else:
+                self._lib.b200spai_dist_destroy(self._h)
             self._h = C.c_void_p()
         for m in (self.A, self.G, self.GT):
             if m is not None:
@@ -409,9 +449,9 @@ class PartitionedSystem:
         GT_loc = self._local_rows(self.ei_tT, g_t[self.order_t].transpose(1, 2).contiguous(), mask_ext)
         return A_loc, G_loc, GT_loc
 
-    def make_solver(self, local, epsilon: float, mode: int = 0) -> "DistPCG":
+    def make_solver(self, local, epsilon: float, mode: int = 0, reuse: bool = False) -> "DistPCG":
         return DistPCG(None, None, epsilon, self.row_starts, (0, 0), group=self.group, rank=self.rank, world=self.world,
-                       mode=mode, local=local, layout=self.layout)
+                       mode=mode, local=local, layout=self.layout, reuse=reuse)
 
     def close(self):
         if self._graph is not None:

@@ -38,7 +38,7 @@ def main():
     ext = par.extended_range(sample.edge_index, rs, re)
     out = {"rank": rank, "world": world, "grid": grid, "rows": [rs, re], "ext": list(ext)}
     for precond in ("ext_spai", "none", "diagonal"):
-        solver = par.DistPCG(A, G if precond == "ext_spai" else None, ws.epsilon, starts, ext, mode=mode)
+        solver = par.DistPCG(A, G if precond == "ext_spai" else None, ws.epsilon, starts, ext, mode=mode, reuse=True)
         x_loc, res, hist = solver.solve(rhs[rs:re].contiguous(), precond, rtol=1e-8, history=True)
         x = solver.gather(x_loc)
         iters = [None] * world
@@ -63,6 +63,7 @@ def main():
     if rank == 0:
         print(json.dumps(out), flush=True)
     dist.barrier()
+    par.DistPCG.drop_connections()
     dist.destroy_process_group()
 
 

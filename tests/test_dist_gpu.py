@@ -149,3 +149,26 @@ def test_multi_rank_partitioned_gnn_and_assembly(kind):
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
     assert out["world"] == world and out["sent"] > 0 and out["edges_gnn"] < out["E"]
+
+
+def test_connection_reuse_across_systems():
+    """close() with reuse parks the connected handle; the next solver of another size relayouts it and gives the same
+    bits as a fresh one."""
+    from learningsparsepreconditioner4gpu_b200 import parallel as par
+
+    out = []
+    for grid in (12, 9, 13):       # 13^3 exceeds the parked capacity (12^3 * 1.25): handle is rebuilt
+        s, ws, A, G, rhs = _system(grid)
+        n = s.num_nodes
+        ext = par.extended_range(s.edge_index, 0, n)
+        d = par.DistPCG(A, G, ws.epsilon, [0, n], ext, rank=0, world=1, reuse=True)
+        x, res, hist = d.solve(rhs, "ext_spai", rtol=1e-8, history=True)
+        d.close()
+        f = par.DistPCG(A, G, ws.epsilon, [0, n], ext, rank=0, world=1)
+        x1, res1, hist1 = f.solve(rhs, "ext_spai", rtol=1e-8, history=True)
+        f.close()
+        assert res.iterations == res1.iterations and torch.equal(hist, hist1) and torch.equal(x, x1)
+        out.append(len(par.DistPCG._connections))
+    assert out == [1, 1, 1]
+    par.DistPCG.drop_connections()
+    assert not par.DistPCG._connections
