@@ -1,9 +1,10 @@
-// GNN inference (NodeEdgeProcessing, neural_cg/nn/gnns.py:77-97) as six fused kernels.
+// GNN inference (NodeEdgeProcessing, neural_cg/nn/gnns.py:77-97): 2 + 2 L kernels.
 //
-//   node_enc                       thread per node:   x0 = MLP(x)                       (gnns.py:83)
-//   mp layer 0 (+ edge encoder)    thread per edge:   e = MLP(edge_attr) on the fly     (gnns.py:84)
-//   mp layer 1..L-1                thread per edge, CTA per block of target nodes       (basic_layers.py:193-225)
-//   decoder                        thread per edge:   G = MLP([e, x[row], x[col]])      (gnns.py:88-95)
+//   node_enc                       thread per node:   x0 = MLP(x)                                   (gnns.py:83)
+//   per MP layer: edge kernel      thread per edge:   msg MLP -> msg[p], edge MLP -> e += ...       (basic_layers.py:193-222)
+//                 (layer 0 also runs the edge encoder e = MLP(edge_attr) on the fly, gnns.py:84)
+//                 node kernel      thread per node:   ordered sum of its messages, LayerNorm16, node MLP, residual (:203-206,224-225)
+//   decoder                        thread per edge:   G = MLP([e, x[row], x[col]])                  (gnns.py:88-95)
 //
 // Data layout in HBM (all fp32):
 //   * edges live in TARGET-SORTED order (stable sort by edge_index[1], built once per topology by
@@ -12,14 +13,11 @@
 //     exactly the order in which the CPU scatter_add_ of the reference accumulates them.
 //   * edge features: tiles of 32 edges, [tile][4 chunks][32 lanes][4 floats], so a thread-per-edge warp
 //     reads/writes 512 contiguous bytes per instruction; updated in place.
+//   * messages: [E][16] row-major in target-sorted order (a node's messages are contiguous), written by the edge
+//     kernel and read once by the node kernel of the same layer.
 //   * node features: [N][16] row-major, ping-pong between layers (the edge MLP must see the OLD ones).
 //
-// One MP-layer kernel does, per block of whole target nodes (<= 56 nodes, ~224 edges):
-//   gather x[dst], x[src], e -> LayerNorm statistics of the 48-vector (shared by both MLPs) ->
-//   msg MLP and edge MLP (LayerNorm affine folded into the first Linear on the host) ->
-//   e += edge MLP (in place) ; messages to shared memory -> ordered segmented sum per target node
-//   (no atomics, deterministic) -> node MLP (LayerNorm16 + 3 Linear) -> x_out = x_in + node MLP.
-// The [E,48] concatenations, the [E,16] messages and the aggregate never touch HBM.
+// The [E,48] concatenations never touch HBM; LayerNorm affines are folded into the first Linear on the host.
 //
 // Arithmetic is fp32 FFMA on purpose: the parity bar is 1e-5 relative on G, which TF32 tensor-core
 // math (10-bit mantissa) cannot meet, and the GEMMs are K<=48, N=16.
@@ -35,8 +33,6 @@ namespace b200spai {
 
 constexpr int F = 16;                // hidden width (config/gnn.yaml gnn_features)
 constexpr int MP_THREADS = 256;
-constexpr int NB_TARGET = 224;       // node-block target on key = segptr[r] + 4 r
-constexpr int NB_MAXN = 64;          // >= NB_TARGET / 4 nodes per block
 constexpr int MLP16 = 3 * (F * F + F);        // 816 floats: three 16x16 Linear (+bias)
 constexpr int MLP48 = 48 * F + F + 2 * (F * F + F);  // 1328 floats: 48->16, 16->16, 16->16
 constexpr int LAYER_FLOATS = 2 * MLP48 + MLP16;      // msg, edge, node
@@ -50,9 +46,7 @@ struct b200spai_graph_s {
   // row-sorted view (GraphSpmv without transpose aggregates at edge_index[0]): position p is original edge
   // rperm[p], its column is rcol[p]; rows own rsegptr[i]..rsegptr[i+1]
   int *rperm = nullptr, *rcol = nullptr, *rsegptr = nullptr;
-  int4* nb = nullptr;
-  int nnb = 0;
-  float *ef = nullptr, *x0 = nullptr, *x1 = nullptr;
+  float *ef = nullptr, *msg = nullptr, *x0 = nullptr, *x1 = nullptr;  // edge features, messages [E,16], node features
 };
 
 struct b200spai_gnn_s {
@@ -116,7 +110,7 @@ static void graph_free(b200spai_graph_s* g) {
   dev_free(g->rperm);
   dev_free(g->rcol);
   dev_free(g->rsegptr);
-  dev_free(g->nb);
+  dev_free(g->msg);
   dev_free(g->ef);
   dev_free(g->x0);
   dev_free(g->x1);
@@ -137,6 +131,7 @@ static int graph_create_impl(long long N, long long E, const long long* edge_ind
   if (!rc) rc = dev_alloc(&g->rcol, (size_t)E);
   if (!rc) rc = dev_alloc(&g->rsegptr, (size_t)N + 1);
   if (!rc) rc = dev_alloc(&g->ef, (size_t)Epad * F);
+  if (!rc) rc = dev_alloc(&g->msg, (size_t)Epad * F);
   if (!rc) rc = dev_alloc(&g->x0, (size_t)N * F);
   if (!rc) rc = dev_alloc(&g->x1, (size_t)N * F);
   int *keys = nullptr, *iota = nullptr, *bad = nullptr;
@@ -203,11 +198,6 @@ static int graph_create_impl(long long N, long long E, const long long* edge_ind
     return B200SPAI_ERR_ARG;
   }
   count_launches(E > 0 ? 8 : 1);
-  rc = build_row_blocks(g->segptr, (int)N, E, NB_TARGET, 4, &g->nb, &g->nnb, st);
-  if (rc) {
-    graph_free(g);
-    return rc;
-  }
   *out = g;
   return 0;
 }
@@ -221,16 +211,22 @@ using namespace b200spai;
 namespace {
 
 template <bool FIRST, int G>
-int launch_mp(const MpParams& P, int nnb, cudaStream_t st) {
-  static int occ = 0;
-  if (!occ) {
-    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gnn_mp_kernel<FIRST, G>, MP_THREADS, 0));
-    if (occ < 1) occ = 1;
+int launch_mp(const MpParams& P, cudaStream_t st) {
+  static int occ_e = 0, occ_n = 0;
+  if (!occ_e) {
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_e, gnn_edge_kernel<FIRST, G>, MP_THREADS, 0));
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_n, gnn_node_kernel<G>, 256, 0));
+    if (occ_e < 1) occ_e = 1;
+    if (occ_n < 1) occ_n = 1;
   }
-  int grid = sm_count() * occ;
-  if (grid > nnb) grid = nnb;
-  if (grid < 1) grid = 1;
-  gnn_mp_kernel<FIRST, G><<<grid, MP_THREADS, 0, st>>>(P);
+  if (P.E > 0) {
+    long long grid = (P.E + MP_THREADS - 1) / MP_THREADS;
+    if (grid > (long long)sm_count() * occ_e) grid = (long long)sm_count() * occ_e;
+    gnn_edge_kernel<FIRST, G><<<(int)grid, MP_THREADS, 0, st>>>(P);
+  }
+  long long grid = (P.N + 255) / 256;
+  if (grid > (long long)sm_count() * occ_n) grid = (long long)sm_count() * occ_n;
+  gnn_node_kernel<G><<<(int)grid, 256, 0, st>>>(P);
   return 0;
 }
 
@@ -269,9 +265,10 @@ int gnn_stage(b200spai_gnn_t m, b200spai_graph_t g, int stage, const float* x_de
     P.dst = g->dst;
     P.segptr = g->segptr;
     P.perm = g->perm;
-    P.nb = g->nb;
-    P.nnb = g->nnb;
+    P.E = E;
+    P.N = N;
     P.ef = g->ef;
+    P.msg = g->msg;
     P.xin = xb[(stage - 1) & 1];
     P.xout = xb[stage & 1];
     P.w_layer = m->w_layer(l);
@@ -280,17 +277,18 @@ int gnn_stage(b200spai_gnn_t m, b200spai_graph_t g, int stage, const float* x_de
     P.edge_in = m->edge_in;
     int rc;
     if (l == 0)
-      rc = (cfg & 2) ? launch_mp<true, 1>(P, g->nnb, st) : launch_mp<true, 0>(P, g->nnb, st);
+      rc = (cfg & 2) ? launch_mp<true, 1>(P, st) : launch_mp<true, 0>(P, st);
     else
-      rc = (cfg & 2) ? launch_mp<false, 1>(P, g->nnb, st) : launch_mp<false, 0>(P, g->nnb, st);
+      rc = (cfg & 2) ? launch_mp<false, 1>(P, st) : launch_mp<false, 0>(P, st);
     if (rc) return rc;
   } else if (E > 0) {
     int rc = (cfg & 2) ? launch_dec<1>(m, g, xb[m->L & 1], g_out_dev, st) : launch_dec<0>(m, g, xb[m->L & 1], g_out_dev, st);
     if (rc) return rc;
   }
   B2_LAUNCH_CHECK();
-  m->launches += 1;
-  count_launches(1);
+  const int nl = (stage >= 1 && stage <= m->L) ? (E > 0 ? 2 : 1) : 1;
+  m->launches += nl;
+  count_launches(nl);
   return 0;
 }
 

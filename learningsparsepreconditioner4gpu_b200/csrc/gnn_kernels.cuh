@@ -116,15 +116,24 @@ __global__ void __launch_bounds__(256) gnn_node_enc_kernel(const float* __restri
   }
 }
 
-// ---- message-passing layer ---------------------------------------------------------------------------
+// ---- message-passing layer = edge kernel + node kernel ------------------------------------------------------------
+// Edge kernel: thread per edge (target-sorted position p), grid-stride, no barrier inside the loop.  Gathers x[dst],
+// x[src], e; LayerNorm(48) statistics shared by both MLPs (their affines are folded into W1/b1 on the host); msg MLP ->
+// msg[p] (row-major [E][16], 64 contiguous bytes per thread); edge MLP -> e += ... in place (it sees the OLD node
+// features, basic_layers.py:208).  Layer 0 fuses the edge encoder (gnns.py:84).
+// Node kernel: thread per target node: ordered sum of its segment's messages (ascending edge order = the CPU
+// scatter_add_ order of the reference, no atomics), LayerNorm(16), node MLP, residual.
+// The messages make one round trip through HBM (128 B per edge and layer, ~3 ms at 216^3): an earlier single-kernel
+// version kept them in shared memory but paid for it with CTA-wide barriers and a serial per-block node phase that
+// left the FMA pipe at 36 % (profiles/r01_gnn_mp_ncu_full.txt).
 struct MpParams {
   const int* src;
   const int* dst;
   const int* segptr;
   const int* perm;
-  const int4* nb;
-  int nnb;
+  long long E, N;
   float* ef;
+  float* msg;
   const float* xin;
   float* xout;
   const float* w_layer;
@@ -135,143 +144,117 @@ struct MpParams {
 
 // G: GELU evaluation (0 = erff, 1 = rational erfc).
 template <bool FIRST, int G>
-__global__ void __launch_bounds__(MP_THREADS, 2) gnn_mp_kernel(const MpParams P) {
-  constexpr int THREADS = MP_THREADS;
-  __shared__ __align__(16) float s_w[LAYER_FLOATS + (FIRST ? MLP16 : 0)];
-  __shared__ float s_msg[THREADS][F + 1];
-  __shared__ float s_agg[NB_MAXN][F];
-  __shared__ float s_h[NB_MAXN][F];
+__global__ void __launch_bounds__(MP_THREADS, 2) gnn_edge_kernel(const MpParams P) {
+  __shared__ __align__(16) float s_w[2 * MLP48 + (FIRST ? MLP16 : 0)];
   const int tid = threadIdx.x;
-  for (int i = tid; i < LAYER_FLOATS; i += THREADS) s_w[i] = P.w_layer[i];
+  for (int i = tid; i < 2 * MLP48; i += MP_THREADS) s_w[i] = P.w_layer[i];
   if (FIRST)
-    for (int i = tid; i < MLP16; i += THREADS) s_w[LAYER_FLOATS + i] = P.w_eenc[i];
+    for (int i = tid; i < MLP16; i += MP_THREADS) s_w[2 * MLP48 + i] = P.w_eenc[i];
   __syncthreads();
-  const float* w_msg = s_w;
-  const float* w_edge = s_w + MLP48;
-  const float* w_eenc = s_w + LAYER_FLOATS;
-  const float* w_node = s_w + 2 * MLP48;
-
-  for (int kb = blockIdx.x; kb < P.nnb; kb += gridDim.x) {
-    const int4 info = P.nb[kb];
-    const int n0 = info.x, e_lo = info.y, n1 = info.z, e_hi = info.w;
-    const int nn = n1 - n0;
-    for (int i = tid; i < nn * F; i += THREADS) (&s_agg[0][0])[i] = 0.0f;
-    __syncthreads();
-
-    for (int c_lo = e_lo; c_lo < e_hi; c_lo += THREADS) {
-      const int p = c_lo + tid;
-      if (p < e_hi) {
-        float v[48];  // [x_i = x[dst], x_j = x[src], e]  (basic_layers.py:216-222)
-        const int d = __ldg(P.dst + p), s = __ldg(P.src + p);
-        load16(P.xin + (long long)d * F, v);
-        load16(P.xin + (long long)s * F, v + 16);
-        if (FIRST) {  // edge encoder fused: e = MLP(edge_attr[original edge])  (gnns.py:84)
-          float a[F], e0[F];
-          const long long eo = __ldg(P.perm + p);
+  const long long stride = (long long)gridDim.x * MP_THREADS;
+  for (long long p = (long long)blockIdx.x * MP_THREADS + tid; p < P.E; p += stride) {
+    float v[48];  // [x_i = x[dst], x_j = x[src], e]  (basic_layers.py:216-222)
+    const int d = __ldg(P.dst + p), s = __ldg(P.src + p);
+    load16(P.xin + (long long)d * F, v);
+    load16(P.xin + (long long)s * F, v + 16);
+    if (FIRST) {
+      float a[F], e0[F];
+      const long long eo = __ldg(P.perm + p);
 #pragma unroll
-          for (int k = 0; k < F; ++k) a[k] = (k < P.edge_in) ? __ldg(P.edge_attr + eo * P.edge_in + k) : 0.0f;
-          mlp3<F, G>(w_eenc, a, e0);
+      for (int k = 0; k < F; ++k) a[k] = (k < P.edge_in) ? __ldg(P.edge_attr + eo * P.edge_in + k) : 0.0f;
+      mlp3<F, G>(s_w + 2 * MLP48, a, e0);
 #pragma unroll
-          for (int k = 0; k < F; ++k) v[32 + k] = e0[k];
-        } else {
+      for (int k = 0; k < F; ++k) v[32 + k] = e0[k];
+    } else {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const float4 t = *ef_chunk(P.ef, p, q);
-            v[32 + 4 * q + 0] = t.x;
-            v[32 + 4 * q + 1] = t.y;
-            v[32 + 4 * q + 2] = t.z;
-            v[32 + 4 * q + 3] = t.w;
-          }
-        }
-        float ev[F];
+      for (int q = 0; q < 4; ++q) {
+        const float4 t = *ef_chunk(P.ef, p, q);
+        v[32 + 4 * q + 0] = t.x;
+        v[32 + 4 * q + 1] = t.y;
+        v[32 + 4 * q + 2] = t.z;
+        v[32 + 4 * q + 3] = t.w;
+      }
+    }
+    float ev[F];
 #pragma unroll
-        for (int k = 0; k < F; ++k) ev[k] = v[32 + k];
-        // LayerNorm(48) statistics, shared by msg_mlp and edge_mlp (their affines are folded into W1/b1)
-        float mean = 0.0f;
+    for (int k = 0; k < F; ++k) ev[k] = v[32 + k];
+    float mean = 0.0f;
 #pragma unroll
-        for (int k = 0; k < 48; ++k) mean += v[k];
-        mean *= (1.0f / 48.0f);
-        float var = 0.0f;
+    for (int k = 0; k < 48; ++k) mean += v[k];
+    mean *= (1.0f / 48.0f);
+    float var = 0.0f;
 #pragma unroll
-        for (int k = 0; k < 48; ++k) {
-          const float c = v[k] - mean;
-          var = fmaf(c, c, var);
-        }
-        const float rstd = 1.0f / sqrtf(var * (1.0f / 48.0f) + 1e-5f);
+    for (int k = 0; k < 48; ++k) {
+      const float c = v[k] - mean;
+      var = fmaf(c, c, var);
+    }
+    const float rstd = 1.0f / sqrtf(var * (1.0f / 48.0f) + 1e-5f);
 #pragma unroll
-        for (int k = 0; k < 48; ++k) v[k] = (v[k] - mean) * rstd;
-        float o[F];
-        mlp3<48, G>(w_msg, v, o);
+    for (int k = 0; k < 48; ++k) v[k] = (v[k] - mean) * rstd;
+    // msg MLP, then edge MLP, through one copy of the MLP code (the weight offset changes)
+#pragma unroll 1
+    for (int m = 0; m < 2; ++m) {
+      float o[F];
+      mlp3<48, G>(s_w + m * MLP48, v, o);
+      if (m == 0) {
+        float4* mp = reinterpret_cast<float4*>(P.msg + p * F);
 #pragma unroll
-        for (int j = 0; j < F; ++j) s_msg[tid][j] = o[j];
-        mlp3<48, G>(w_edge, v, o);  // edge update sees the OLD node features (basic_layers.py:208)
+        for (int q = 0; q < 4; ++q) mp[q] = make_float4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+      } else {
 #pragma unroll
         for (int q = 0; q < 4; ++q)
           *ef_chunk(P.ef, p, q) = make_float4(ev[4 * q] + o[4 * q], ev[4 * q + 1] + o[4 * q + 1],
                                               ev[4 * q + 2] + o[4 * q + 2], ev[4 * q + 3] + o[4 * q + 3]);
       }
-      __syncthreads();
-      // ordered segmented sum: thread (node, channel) adds its node's messages of this chunk in edge order
-      {
-        const int c = tid & 15;
-        for (int nl = tid >> 4; nl < nn; nl += THREADS / 16) {
-          int sb = __ldg(P.segptr + n0 + nl), se = __ldg(P.segptr + n0 + nl + 1);
-          sb = max(sb, c_lo);
-          se = min(se, c_lo + THREADS);
-          float acc = s_agg[nl][c];
-          for (int q = sb; q < se; ++q) acc += s_msg[q - c_lo][c];
-          s_agg[nl][c] = acc;
-        }
-      }
-      __syncthreads();
     }
+  }
+}
 
-    // node update: x_out = x_in + node_mlp(LayerNorm16(agg))   (basic_layers.py:203-206,224-225)
-    {
-      const int j = tid & 15;
-      const int nn_pad = (nn + 1) & ~1;  // both half-warps of a warp take the same number of trips
-      for (int nl = tid >> 4; nl < nn_pad; nl += THREADS / 16) {
-        const bool act = nl < nn;
-        const int nr = act ? nl : 0;
-        float a[F];
-        float mean = 0.0f;
+// x_out = x_in + node_mlp(LayerNorm16(sum of the messages of the node))   (basic_layers.py:203-206,224-225)
+template <int G>
+__global__ void __launch_bounds__(256) gnn_node_kernel(const MpParams P) {
+  __shared__ __align__(16) float s_w[MLP16];
+  for (int i = threadIdx.x; i < MLP16; i += blockDim.x) s_w[i] = P.w_layer[2 * MLP48 + i];
+  __syncthreads();
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < P.N; i += stride) {
+    float a[F];
 #pragma unroll
-        for (int k = 0; k < F; ++k) {
-          a[k] = s_agg[nr][k];
-          mean += a[k];
-        }
-        mean *= (1.0f / 16.0f);
-        float var = 0.0f;
+    for (int k = 0; k < F; ++k) a[k] = 0.0f;
+    const int sb = __ldg(P.segptr + i), se = __ldg(P.segptr + i + 1);
+    for (int p = sb; p < se; ++p) {  // ascending edge order, one rounded add per message and channel
+      const float4* mp = reinterpret_cast<const float4*>(P.msg + (long long)p * F);
 #pragma unroll
-        for (int k = 0; k < F; ++k) {
-          const float c = a[k] - mean;
-          var = fmaf(c, c, var);
-        }
-        const float rstd = 1.0f / sqrtf(var * (1.0f / 16.0f) + 1e-5f);
-        float h = w_node[F * F + j];
-#pragma unroll
-        for (int k = 0; k < F; ++k) h = fmaf((a[k] - mean) * rstd, w_node[k * F + j], h);
-        __syncwarp();
-        if (act) s_h[nr][j] = gelu<G>(h);
-        __syncwarp();
-        const float* W2 = w_node + F * F + F;
-        h = W2[F * F + j];
-#pragma unroll
-        for (int k = 0; k < F; ++k) h = fmaf(s_h[nr][k], W2[k * F + j], h);
-        __syncwarp();
-        if (act) s_agg[nr][j] = gelu<G>(h);
-        __syncwarp();
-        const float* W3 = W2 + F * F + F;
-        h = W3[F * F + j];
-#pragma unroll
-        for (int k = 0; k < F; ++k) h = fmaf(s_agg[nr][k], W3[k * F + j], h);
-        if (act) {
-          const long long idx = (long long)(n0 + nl) * F + j;
-          P.xout[idx] = __ldg(P.xin + idx) + h;
-        }
+      for (int q = 0; q < 4; ++q) {
+        const float4 t = mp[q];
+        a[4 * q + 0] += t.x;
+        a[4 * q + 1] += t.y;
+        a[4 * q + 2] += t.z;
+        a[4 * q + 3] += t.w;
       }
     }
-    __syncthreads();
+    float mean = 0.0f;
+#pragma unroll
+    for (int k = 0; k < F; ++k) mean += a[k];
+    mean *= (1.0f / 16.0f);
+    float var = 0.0f;
+#pragma unroll
+    for (int k = 0; k < F; ++k) {
+      const float c = a[k] - mean;
+      var = fmaf(c, c, var);
+    }
+    const float rstd = 1.0f / sqrtf(var * (1.0f / 16.0f) + 1e-5f);
+#pragma unroll
+    for (int k = 0; k < F; ++k) a[k] = (a[k] - mean) * rstd;
+    float o[F];
+    mlp3<F, G>(s_w, a, o);
+    const float4* xi = reinterpret_cast<const float4*>(P.xin + i * F);
+    float4* xo = reinterpret_cast<float4*>(P.xout + i * F);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float4 t = __ldg(xi + q);
+      xo[q] = make_float4(t.x + o[4 * q], t.y + o[4 * q + 1], t.z + o[4 * q + 2], t.w + o[4 * q + 3]);
+    }
   }
 }
 
