@@ -18,7 +18,7 @@ def main(path):
             continue
         name = re.sub(r"\(.*", "", row["Kernel Name"])
         name = name.replace("void ", "").replace("b200spai::", "")
-        ours = "b200spai" in row["Kernel Name"]
+        ours = not any(t in row["Kernel Name"] for t in ("cub::", "at::", "thrust::", "nccl"))
         v = float(row["Metric Value"].replace(",", ""))
         v *= {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3}.get(row["Metric Unit"], 1.0)
         a = agg.setdefault(name[:90], [0, 0.0, ours])
