@@ -553,6 +553,73 @@ def main_rowpart(args):
     dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------------------------
+# --mode batch_small: BASELINE config C2 -- a batch of small independent Poisson systems per GPU
+# ---------------------------------------------------------------------------------------------------------
+def main_batch_small(args):
+    """Every rank solves its own shard of a batch of independent systems (N between 4 k and 32 k nodes, the size range
+    of the reference's poisson3d_tetmesh set, preprocess/msh_to_npy.py:77-86), one after the other through
+    ``workspace.solve``: GNN -> G -> assembly -> PCG to rtol.  No data-path collective; solves/s over all ranks."""
+    from learningsparsepreconditioner4gpu_b200 import _lib, systems
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    _lib.require_cuda()
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    grids = [16, 20, 25, 32]                         # 4096, 8000, 15625, 32768 nodes
+    per_rank = max(args.batch // world, 1)
+    samples = [systems.poisson_sample(grids[(rank * per_rank + k) % 4], seed=1000 + rank * per_rank + k, device="cuda")
+               for k in range(per_rank)]
+    ws = systems.default_workspace(samples[0])
+
+    def one_pass():
+        its = 0
+        for s in samples:
+            x, res, _, A, G = ws.solve(s, rtol=args.rtol)
+            its += int(res.iterations)
+            assert res.converged == 1
+        return its
+
+    for _ in range(max(args.warmup, 1)):
+        one_pass()
+    launches0 = _lib.total_launches()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    its = 0
+    for _ in range(args.steps):
+        its += one_pass()
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    if rank == 0:
+        total = per_rank * world * args.steps
+        print(json.dumps({
+            "metric": "learned-SPAI PCG solves/s to rtol 1e-6, batch of small independent systems (BASELINE config C2)",
+            "mode": "batch_small", "value": round(total / (ms * 1e-3), 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 1), "ms_per_step": round(ms / args.steps, 3), "ms_per_system": round(ms / args.steps / per_rank, 3),
+            "higher_is_better": True, "scaling": "weak", "dtype": "f64 (PCG) / f32 (GNN)", "data": "synthetic",
+            "config": {"workload": f"{per_rank} Poisson systems per GPU, N in {{4096, 8000, 15625, 32768}}, Dirichlet patch, "
+                                   f"random-init GNN, rhs = A*mask, rtol {args.rtol:g}; one system at a time per GPU"},
+            "mean_iterations": round(its / (per_rank * args.steps), 1),
+            "gpu_launches": int(_lib.total_launches() - launches0)}), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -562,13 +629,17 @@ def main():
     ap.add_argument("--rtol", type=float, default=1e-6)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--mode", default="batch", choices=["batch", "rowpart"],
-                    help="batch: one independent system per GPU (the bench contract); rowpart: one system over all GPUs")
+    ap.add_argument("--mode", default="batch", choices=["batch", "rowpart", "batch_small"],
+                    help="batch: one independent 10 M-DOF system per GPU (the bench contract); rowpart: one system over all "
+                         "GPUs; batch_small: a batch of small systems per GPU (BASELINE config C2)")
+    ap.add_argument("--batch", type=int, default=64, help="batch_small: systems per step over all ranks")
     args = ap.parse_args()
     if args.impl == "reference":
         main_reference(args)
     elif args.mode == "rowpart":
         main_rowpart(args)
+    elif args.mode == "batch_small":
+        main_batch_small(args)
     else:
         main_ours(args)
 

@@ -53,7 +53,15 @@ size_t pool_limit() {
   }
   return P.limit;
 }
-size_t round_size(size_t bytes) { return (bytes + 511) & ~(size_t)511; }
+// Size classes: multiples of 512 B up to 4 KB, above that 8 classes per power of two (<= 12.5 % slack), so that a
+// stream of systems of DIFFERENT sizes (a batch of meshes) still hits the cache instead of cudaMalloc / cudaFree.
+size_t round_size(size_t bytes) {
+  bytes = (bytes + 511) & ~(size_t)511;
+  if (bytes <= 4096) return bytes;
+  int p = 63 - __builtin_clzll((unsigned long long)bytes);
+  const size_t step = (size_t)1 << (p - 3);
+  return (bytes + step - 1) & ~(step - 1);
+}
 }  // namespace
 
 cudaError_t pool_malloc(void** p, size_t bytes) {

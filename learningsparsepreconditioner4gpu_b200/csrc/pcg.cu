@@ -19,6 +19,9 @@
 #include <vector>
 
 #include "csr.h"
+#include <mutex>
+#include <vector>
+
 #include "pcg_kernels.cuh"
 
 using namespace b200spai;
@@ -41,6 +44,7 @@ struct b200spai_pcg_s {
   int* h_done = nullptr;        // pinned [2]
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_chunk[2] = {nullptr, nullptr};
   cudaStream_t body_stream = nullptr, cap_stream = nullptr;  // graphs are captured on private streams
+  int scaffold_dev = 0;
   int mode = 0;
   long long launches = 0;
   float setup_ms = 0.f;
@@ -51,6 +55,95 @@ struct b200spai_pcg_s {
 };
 
 namespace b200spai {
+
+// Host-side scaffolding of a solver (three small pinned buffers, four events, two capture streams): creating it costs
+// ~1.7 ms, which is most of a small system's setup, so destroyed solvers park theirs for the next pcg_create.
+struct PcgScaffold {
+  int dev = 0;
+  PcgScalars *h_in = nullptr, *h_out = nullptr;
+  int* h_done = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_chunk[2] = {nullptr, nullptr};
+  cudaStream_t body_stream = nullptr, cap_stream = nullptr;
+};
+static std::mutex g_scaffold_mu;
+static std::vector<PcgScaffold>& scaffold_cache() {
+  static auto* v = new std::vector<PcgScaffold>();  // leaked on purpose (see the memory pool)
+  return *v;
+}
+
+static int scaffold_acquire(b200spai_pcg_s* s) {
+  int dev = 0;
+  B2_CUDA(cudaGetDevice(&dev));
+  PcgScaffold f;
+  bool hit = false;
+  {
+    std::lock_guard<std::mutex> lock(g_scaffold_mu);
+    auto& c = scaffold_cache();
+    for (size_t i = 0; i < c.size(); ++i)
+      if (c[i].dev == dev) {
+        f = c[i];
+        c.erase(c.begin() + (long)i);
+        hit = true;
+        break;
+      }
+  }
+  if (!hit) {
+    f.dev = dev;
+    B2_CUDA(cudaMallocHost((void**)&f.h_in, sizeof(PcgScalars)));
+    B2_CUDA(cudaMallocHost((void**)&f.h_out, sizeof(PcgScalars)));
+    B2_CUDA(cudaMallocHost((void**)&f.h_done, 2 * sizeof(int)));
+    B2_CUDA(cudaEventCreate(&f.ev0));
+    B2_CUDA(cudaEventCreate(&f.ev1));
+    B2_CUDA(cudaEventCreateWithFlags(&f.ev_chunk[0], cudaEventDisableTiming));
+    B2_CUDA(cudaEventCreateWithFlags(&f.ev_chunk[1], cudaEventDisableTiming));
+    B2_CUDA(cudaStreamCreateWithFlags(&f.body_stream, cudaStreamNonBlocking));
+    B2_CUDA(cudaStreamCreateWithFlags(&f.cap_stream, cudaStreamNonBlocking));
+  }
+  s->scaffold_dev = f.dev;
+  s->h_in = f.h_in;
+  s->h_out = f.h_out;
+  s->h_done = f.h_done;
+  s->ev0 = f.ev0;
+  s->ev1 = f.ev1;
+  s->ev_chunk[0] = f.ev_chunk[0];
+  s->ev_chunk[1] = f.ev_chunk[1];
+  s->body_stream = f.body_stream;
+  s->cap_stream = f.cap_stream;
+  return 0;
+}
+
+static void scaffold_release(b200spai_pcg_s* s) {
+  if (!s->h_in) return;
+  PcgScaffold f;
+  f.dev = s->scaffold_dev;
+  f.h_in = s->h_in;
+  f.h_out = s->h_out;
+  f.h_done = s->h_done;
+  f.ev0 = s->ev0;
+  f.ev1 = s->ev1;
+  f.ev_chunk[0] = s->ev_chunk[0];
+  f.ev_chunk[1] = s->ev_chunk[1];
+  f.body_stream = s->body_stream;
+  f.cap_stream = s->cap_stream;
+  s->h_in = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_scaffold_mu);
+    if (scaffold_cache().size() < 16 && f.h_out && f.h_done && f.ev0 && f.ev1 && f.ev_chunk[0] && f.ev_chunk[1] &&
+        f.body_stream && f.cap_stream) {
+      scaffold_cache().push_back(f);
+      return;
+    }
+  }
+  if (f.h_in) cudaFreeHost(f.h_in);
+  if (f.h_out) cudaFreeHost(f.h_out);
+  if (f.h_done) cudaFreeHost(f.h_done);
+  if (f.ev0) cudaEventDestroy(f.ev0);
+  if (f.ev1) cudaEventDestroy(f.ev1);
+  if (f.ev_chunk[0]) cudaEventDestroy(f.ev_chunk[0]);
+  if (f.ev_chunk[1]) cudaEventDestroy(f.ev_chunk[1]);
+  if (f.body_stream) cudaStreamDestroy(f.body_stream);
+  if (f.cap_stream) cudaStreamDestroy(f.cap_stream);
+}
 
 // auto mode: the graph driver, unless B200SPAI_PCG_MODE=1 asks for stream-enqueued kernels (ncu cannot see the
 // kernel nodes of a graph that holds a conditional node, so the profiling passes run in mode 1)
@@ -291,15 +384,10 @@ int b200spai_pcg_create(b200spai_csr_t a, b200spai_pcg_t* out) {
   B2_CUDA(cudaMemset(s->ticket, 0, sizeof(unsigned)));
   B2_CUDA(cudaMemset(s->sc, 0, sizeof(PcgScalars)));
   B2_CUDA(cudaMemset(s->p, 0, n * sizeof(double)));
-  B2_CUDA(cudaMallocHost((void**)&s->h_in, sizeof(PcgScalars)));
-  B2_CUDA(cudaMallocHost((void**)&s->h_out, sizeof(PcgScalars)));
-  B2_CUDA(cudaMallocHost((void**)&s->h_done, 2 * sizeof(int)));
-  B2_CUDA(cudaEventCreate(&s->ev0));
-  B2_CUDA(cudaEventCreate(&s->ev1));
-  B2_CUDA(cudaEventCreateWithFlags(&s->ev_chunk[0], cudaEventDisableTiming));
-  B2_CUDA(cudaEventCreateWithFlags(&s->ev_chunk[1], cudaEventDisableTiming));
-  B2_CUDA(cudaStreamCreateWithFlags(&s->body_stream, cudaStreamNonBlocking));
-  B2_CUDA(cudaStreamCreateWithFlags(&s->cap_stream, cudaStreamNonBlocking));
+  if (scaffold_acquire(s)) {
+    b200spai_pcg_destroy(s);
+    return B200SPAI_ERR_CUDA;
+  }
   *out = s;
   return 0;
 }
@@ -462,15 +550,8 @@ int b200spai_pcg_destroy(b200spai_pcg_t s) {
   for (double* v : {s->r, s->z, s->p, s->q, s->t, s->d, s->bw, s->xw, s->partials, s->hist}) dev_free(v);
   dev_free(s->sc);
   dev_free(s->ticket);
-  if (s->h_in) cudaFreeHost(s->h_in);
-  if (s->h_out) cudaFreeHost(s->h_out);
-  if (s->h_done) cudaFreeHost(s->h_done);
-  if (s->ev0) cudaEventDestroy(s->ev0);
-  if (s->ev1) cudaEventDestroy(s->ev1);
-  if (s->ev_chunk[0]) cudaEventDestroy(s->ev_chunk[0]);
-  if (s->ev_chunk[1]) cudaEventDestroy(s->ev_chunk[1]);
-  if (s->body_stream) cudaStreamDestroy(s->body_stream);
-  if (s->cap_stream) cudaStreamDestroy(s->cap_stream);
+  // the scaffold's streams and events are idle here: every solve synchronises before it returns
+  scaffold_release(s);
   delete s;
   return 0;
 }
