@@ -122,8 +122,11 @@ int b200spai_pcg_create(b200spai_csr_t a, b200spai_pcg_t* out);
 /* Attach G (the `ext_spai=(spai, epsilon)` argument, validate.py:117).  G^T is built on the device.
  * The solver keeps references to g (must outlive it) and owns G^T. */
 int b200spai_pcg_set_spai(b200spai_pcg_t s, b200spai_csr_t g, double epsilon, void* stream);
-/* mode: 0 = auto, 1 = stream-enqueued kernels with a device-side done flag polled every few
- * iterations, 2 = one CUDA graph with a device-driven WHILE node (no host involvement at all). */
+/* mode: 0 = auto (3 for systems of <= 131072 rows, else 2; B200SPAI_PCG_MODE=1 forces 1), 1 = stream-enqueued
+ * kernels with a device-side done flag polled every few iterations, 2 = one CUDA graph with a device-driven WHILE
+ * node (no host involvement at all), 3 = the whole solve in ONE cooperative kernel with 2-3 grid barriers per
+ * iteration (small systems, where mode 2 is bound by the latency of its five graph nodes per iteration).
+ * b200spai_pcg_result.reserved reports the mode that ran. */
 int b200spai_pcg_set_mode(b200spai_pcg_t s, int mode);
 /* Solve A x = b.  x_dev is overwritten (x0 = 0).  resid_hist_dev: NULL or max_iter+1 doubles
  * receiving ||r_k|| (k = 0..iterations).  max_iter <= 0 means n (validate.py:100-101). */

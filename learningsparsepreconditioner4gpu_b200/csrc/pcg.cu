@@ -23,6 +23,7 @@
 #include <vector>
 
 #include "pcg_kernels.cuh"
+#include "pcg_small.cuh"
 
 using namespace b200spai;
 
@@ -287,6 +288,53 @@ static int build_graph(b200spai_pcg_s* s, int precond, cudaStream_t st) {
   return 0;
 }
 
+// Small systems: the whole solve in one cooperative kernel (pcg_small.cuh).  Eligible when every row can be given a
+// thread of a co-resident grid a few times over and the device supports cooperative launches.
+static int small_grid(const b200spai_pcg_s* s) {
+  static int occ = -1, coop = -1;
+  if (occ < 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pcg_small_kernel, SMALL_THREADS, 0) != cudaSuccess) occ = 0;
+  }
+  if (!coop || occ < 1 || s->n < 1 || s->n > 131072) return 0;
+  long long g = ((long long)s->n + SMALL_THREADS - 1) / SMALL_THREADS;
+  const long long cap = std::min<long long>((long long)sm_count() * occ, SMALL_MAX_CTAS);
+  if (g > cap) g = cap;
+  return (int)g;
+}
+
+static int solve_small(b200spai_pcg_s* s, int precond, const double* b, double* x, int grid, cudaStream_t st) {
+  SmallArgs a{};
+  a.A = s->A->view();
+  if (precond >= B200SPAI_PRECOND_EXT_SPAI) {
+    a.G = s->G->view();
+    a.GT = s->GT->view();
+  }
+  a.b = b;
+  a.x = x;
+  a.r0 = s->r;
+  a.r1 = s->bw;
+  a.p0 = s->p;
+  a.p1 = s->xw;
+  a.z = s->z;
+  a.q = s->q;
+  a.t = s->t;
+  a.d = (precond == B200SPAI_PRECOND_DIAGONAL || precond == B200SPAI_PRECOND_EXT_SPAI_SCALED) ? s->d : nullptr;
+  a.eps = s->eps;
+  a.precond = precond;
+  a.sc = s->sc;
+  a.partials = s->partials;
+  a.hist = s->hist;
+  static_assert(6 * SMALL_MAX_CTAS <= MAX_PARTIALS, "three two-value reduction slots must fit the partials buffer");
+  void* args[] = {&a};
+  B2_CUDA(cudaLaunchCooperativeKernel((const void*)pcg_small_kernel, dim3((unsigned)grid), dim3(SMALL_THREADS), args, 0, st));
+  s->launches += 1;
+  count_launches(1);
+  return 0;
+}
+
 static int solve_impl(b200spai_pcg_s* s, int precond, const double* b, double* x, double rtol, int max_iter,
                       double* hist_out, cudaStream_t st, b200spai_pcg_result* res) {
   B2_ARG(s && b && x && res, "pcg_solve: NULL argument");
@@ -296,7 +344,9 @@ static int solve_impl(b200spai_pcg_s* s, int precond, const double* b, double* x
   if (max_iter <= 0) max_iter = s->n;
   B2_TRY(ensure_hist(s, (long long)max_iter + 1));
   int mode = s->mode;
-  if (mode == 0) mode = default_mode();
+  const int sgrid = (mode == 0 || mode == 3) ? small_grid(s) : 0;
+  if (mode == 3) B2_ARG(sgrid > 0, "pcg_solve: mode 3 (single cooperative kernel) needs a system of <= 131072 rows");
+  if (mode == 0) mode = (sgrid > 0 && !getenv("B200SPAI_NO_SMALL") && default_mode() == 2) ? 3 : default_mode();
 
   PcgScalars init{};
   init.rtol = rtol;
@@ -309,7 +359,9 @@ static int solve_impl(b200spai_pcg_s* s, int precond, const double* b, double* x
   *s->h_in = init;
   B2_CUDA(cudaEventRecord(s->ev0, st));
   B2_CUDA(cudaMemcpyAsync(s->sc, s->h_in, sizeof(PcgScalars), cudaMemcpyHostToDevice, st));
-  if (mode == 2) {
+  if (mode == 3) {
+    B2_TRY(solve_small(s, precond, b, x, sgrid, st));
+  } else if (mode == 2) {
     B2_CUDA(cudaMemcpyAsync(s->bw, b, (size_t)s->n * sizeof(double), cudaMemcpyDeviceToDevice, st));
     B2_CUDA(cudaGraphLaunch(s->exec[precond], st));
     B2_CUDA(cudaMemcpyAsync(x, s->xw, (size_t)s->n * sizeof(double), cudaMemcpyDeviceToDevice, st));
@@ -420,7 +472,7 @@ int b200spai_pcg_set_spai(b200spai_pcg_t s, b200spai_csr_t g, double epsilon, vo
 }
 
 int b200spai_pcg_set_mode(b200spai_pcg_t s, int mode) {
-  B2_ARG(s && mode >= 0 && mode <= 2, "pcg_set_mode: mode must be 0, 1 or 2");
+  B2_ARG(s && mode >= 0 && mode <= 3, "pcg_set_mode: mode must be 0, 1, 2 or 3");
   s->mode = mode;
   return 0;
 }

@@ -149,7 +149,7 @@ def test_edges_to_csr_creates_missing_masked_diagonal():
     assert np.array_equal(got.indptr, ref.indptr) and np.array_equal(got.indices, ref.indices) and np.array_equal(got.data, ref.data)
 
 
-@pytest.mark.parametrize("mode", [1, 2])
+@pytest.mark.parametrize("mode", [1, 2, 3])       # stream-enqueued, graph WHILE loop, single cooperative kernel
 @pytest.mark.parametrize("name", GOLDEN_CASES)
 def test_pcg_matches_reference_iterations(name, mode):
     d = _dev()
@@ -165,6 +165,7 @@ def test_pcg_matches_reference_iterations(name, mode):
     solver.set_spai(Gd, eps)
     for kind, key in (("ext_spai", "iters_pcg"), ("none", "iters_cg"), ("ext_spai_scaled", "iters_pcg_scaled")):
         x, res, hist = solver.solve(torch.from_numpy(b).cuda(), kind, rtol=1e-6, history=True)
+        assert res.reserved == mode                  # the driver that really ran
         ref_it = int(g[key])
         assert abs(res.iterations - ref_it) <= 1, (name, kind, res.iterations, ref_it)
         assert res.breakdown == 0
@@ -230,11 +231,34 @@ def test_pcg_large_poisson_property():
     A = d.DeviceCSR.from_edges(s.edge_index, vals, s.num_nodes, mask)
     b = A.matvec(mask.reshape(-1).double())
     its = []
-    for mode in (1, 2):
+    for mode in (1, 2, 3):
         solver = d.DevicePCG(A, mode=mode)
         x, res, hist = solver.solve(b, "diagonal", rtol=1e-8, history=True)
         r = b - A.matvec(x)
         assert res.converged == 1 and float(r.norm() / b.norm()) < 2e-8
         assert hist.shape[0] == res.iterations + 1
         its.append(res.iterations)
-    assert its[0] == its[1]
+    assert its[0] == its[1] and abs(its[2] - its[0]) <= 1
+
+
+def test_small_kernel_edge_cases():
+    """mode 3 (whole solve in one cooperative kernel): zero rhs, max_iter cut-off, auto selection, size limit."""
+    d = _dev()
+    g = load_golden("poisson_b1")
+    A, G = golden_csr(g, "A"), golden_csr(g, "G")
+    b = torch.from_numpy(A @ g["mask"].reshape(-1).astype(np.float64)).cuda()
+    Ad = d.DeviceCSR.from_scipy(A)
+    solver = d.DevicePCG(Ad, mode=3)
+    solver.set_spai(d.DeviceCSR.from_scipy(G), float(g["epsilon"]))
+    x, res, hist = solver.solve(torch.zeros_like(b), "ext_spai", history=True)
+    assert res.iterations == 0 and res.converged == 1 and float(x.abs().max()) == 0.0 and hist.shape[0] == 1
+    x, res, hist = solver.solve(b, "ext_spai", rtol=1e-12, max_iter=5, history=True)
+    assert res.iterations == 5 and res.converged == 0 and hist.shape[0] == 6
+    x1, r1, h1 = solver.solve(b, "ext_spai", rtol=1e-6, history=True)
+    x2, r2, h2 = solver.solve(b, "ext_spai", rtol=1e-6, history=True)
+    assert r1.iterations == r2.iterations and torch.equal(x1, x2) and torch.equal(h1, h2)       # deterministic
+    auto = d.DevicePCG(Ad)                                    # auto mode picks the single kernel for small systems
+    xa, ra, _ = auto.solve(b, "none", rtol=1e-6)
+    assert ra.reserved == 3 and ra.converged == 1
+    rel = float((b - Ad.matvec(xa)).norm() / b.norm())
+    assert rel < 5e-6
