@@ -57,38 +57,47 @@ __device__ __forceinline__ double small_grid_sum(cooperative_groups::grid_group&
   return total;
 }
 
-__device__ __forceinline__ double small_row(const CsrView& M, int row, const double* __restrict__ x) {
+// One row of M times a vector whose entry c is produced by `entry(c)`.  The row is walked in batches of 8 entries: the
+// 8 column indices / values and then the 8 gathered vector entries are loaded before any of them is used, so a row costs
+// ~2 L2 round trips instead of one per entry (the vectors change every iteration and are written by other SMs, so they
+// are read with ld.cg from L2).  The sum itself stays sequential: rounded product, rounded add, in entry order.
+template <class Entry>
+__device__ __forceinline__ double small_row_gen(const CsrView& M, int row, Entry entry) {
   double sum = 0.0;
   const int e = M.rowptr[row + 1];
-  for (int k = M.rowptr[row]; k < e; ++k) sum = __dadd_rn(sum, __dmul_rn(M.val[k], __ldcg(x + M.col[k])));
+  for (int k = M.rowptr[row]; k < e; k += 8) {
+    int c[8];
+    double v[8], u[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const bool in = k + j < e;
+      c[j] = in ? M.col[k + j] : 0;
+      v[j] = in ? M.val[k + j] : 0.0;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) u[j] = (k + j < e) ? entry(c[j]) : 0.0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (k + j < e) sum = __dadd_rn(sum, __dmul_rn(v[j], u[j]));
+  }
   return sum;
+}
+
+__device__ __forceinline__ double small_row(const CsrView& M, int row, const double* __restrict__ x) {
+  return small_row_gen(M, row, [x](int c) { return __ldcg(x + c); });
 }
 
 // row of M times the vector u[c] = a[c] - alpha * b[c] formed on the fly (r' = r - alpha q)
 __device__ __forceinline__ double small_row_sub(const CsrView& M, int row, const double* __restrict__ a,
                                                 const double* __restrict__ b, double alpha) {
-  double sum = 0.0;
-  const int e = M.rowptr[row + 1];
-  for (int k = M.rowptr[row]; k < e; ++k) {
-    const int c = M.col[k];
-    const double u = __dsub_rn(__ldcg(a + c), __dmul_rn(alpha, __ldcg(b + c)));
-    sum = __dadd_rn(sum, __dmul_rn(M.val[k], u));
-  }
-  return sum;
+  return small_row_gen(M, row, [a, b, alpha](int c) { return __dsub_rn(__ldcg(a + c), __dmul_rn(alpha, __ldcg(b + c))); });
 }
 
 // row of M times the vector u[c] = p[c] * beta + z[c] formed on the fly (p' = z + beta p; first iteration p' = z)
 __device__ __forceinline__ double small_row_axpy(const CsrView& M, int row, const double* __restrict__ z,
                                                  const double* __restrict__ p, double beta, bool first) {
-  double sum = 0.0;
-  const int e = M.rowptr[row + 1];
-  for (int k = M.rowptr[row]; k < e; ++k) {
-    const int c = M.col[k];
-    const double zv = __ldcg(z + c);
-    const double u = first ? zv : __dadd_rn(__dmul_rn(__ldcg(p + c), beta), zv);
-    sum = __dadd_rn(sum, __dmul_rn(M.val[k], u));
-  }
-  return sum;
+  if (first) return small_row_gen(M, row, [z](int c) { return __ldcg(z + c); });
+  return small_row_gen(M, row, [z, p, beta](int c) { return __dadd_rn(__dmul_rn(__ldcg(p + c), beta), __ldcg(z + c)); });
 }
 
 __global__ void __launch_bounds__(SMALL_THREADS) pcg_small_kernel(SmallArgs a) {
