@@ -74,17 +74,21 @@ __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_re
 // Wait until *flag >= epoch: relaxed polls (a system-scope acquire costs microseconds, so it is not repeated per
 // poll) and ONE acquire fence once the flag is there.  On timeout the solve is marked broken so that every later
 // kernel returns at once.
-__device__ __forceinline__ void dist_wait(const DistCtx& c, const unsigned long long* flag, unsigned long long epoch) {
+// Returns false on timeout.
+__device__ __forceinline__ bool dist_wait(const DistCtx& c, const unsigned long long* flag, unsigned long long epoch) {
   const long long t0 = clock64();
+  bool ok = true;
   while (ld_relaxed_sys(flag) < epoch) {
     if (clock64() - t0 > c.spin_limit) {
       c.sc->breakdown = 3;
       c.sc->done = 1;
       if (c.sc->use_cond) cudaGraphSetConditional((cudaGraphConditionalHandle)c.sc->cond_handle, 0u);
+      ok = false;
       break;
     }
   }
   fence_acq_rel_sys();
+  return ok;
 }
 
 // ---- halo exchange of one extended vector ---------------------------------------------------------------------
@@ -155,42 +159,49 @@ __global__ void __launch_bounds__(256) dist_reduce_kernel(const __grid_constant_
   }
   if (threadIdx.x >= 32) return;
   const int t = threadIdx.x;
-  if (t == 0) s_epoch = ++c.epoch[NVEC + kind];
+  // Lane 0 takes a private copy of the scalar block NOW (independent loads, in flight while the exchange runs): the
+  // scalar update after the exchange then works on registers and is written back with independent stores, instead of
+  // a chain of dependent L2 round trips on the critical path of every iteration.
+  PcgScalars loc;
+  if (t == 0) {
+    loc = *sc;
+    s_epoch = ++c.epoch[NVEC + kind];
+  }
   __syncwarp();
   const unsigned long long ep = s_epoch;
   const double local = sc->local_total;
   const bool with_rr = (kind == RED_RHO) && sc->have_rr;  // identical on every rank
   const double local2 = with_rr ? sc->local_rr : 0.0;
+  bool ok = true;
   if (t < c.world) {
     c.hdr[t]->red_val[kind][c.rank] = local;
     if (with_rr) c.hdr[t]->red_val2[kind][c.rank] = local2;
     st_release_sys(&c.hdr[t]->red_epoch[kind][c.rank], ep);  // orders the two stores above (same thread) and the pushes
-  }
-  if (t < c.world) {
-    dist_wait(c, &c.hdr[c.rank]->red_epoch[kind][t], ep);
+    ok = dist_wait(c, &c.hdr[c.rank]->red_epoch[kind][t], ep);
     s_val[t] = *reinterpret_cast<volatile double*>(&c.hdr[c.rank]->red_val[kind][t]);
     if (with_rr) s_val2[t] = *reinterpret_cast<volatile double*>(&c.hdr[c.rank]->red_val2[kind][t]);
   }
   __syncwarp();
-  if (t != 0) return;
-  if (sc->breakdown == 3) return;  // a wait timed out
+  ok = __all_sync(0xffffffffu, ok);
+  if (t != 0 || !ok) return;  // a wait timed out: the solve is already marked broken in global memory
   double total = 0.0, total2 = 0.0;
   for (int r = 0; r < c.world; ++r) total += s_val[r];
   if (with_rr)
     for (int r = 0; r < c.world; ++r) total2 += s_val2[r];
-  sc->dist = 0;  // the shared update code below must apply the update, not store a local total
+  loc.dist = 0;  // the shared update code below must apply the update, not store a local total
   if (kind == RED_INIT) {
-    pcg_final_init(sc, total, c.hist);
+    pcg_final_init(&loc, total, c.hist);
   } else if (kind == RED_RHO) {
     if (with_rr) {
-      sc->have_rr = 0;
-      pcg_final_rr(sc, total2, c.hist);
+      loc.have_rr = 0;
+      pcg_final_rr(&loc, total2, c.hist);
     }
-    if (!sc->done) pcg_final_scalar(sc, FINAL_RHO, total);
+    if (!loc.done) pcg_final_scalar(&loc, FINAL_RHO, total);
   } else {
-    pcg_final_scalar(sc, FINAL_PQ, total);
+    pcg_final_scalar(&loc, FINAL_PQ, total);
   }
-  sc->dist = 1;
+  loc.dist = 1;
+  *sc = loc;
 }
 
 // diag[i] = A_local[i, i + off]
