@@ -577,15 +577,40 @@ def main_batch_small(args):
     per_rank = max(args.batch // world, 1)
     samples = [systems.poisson_sample(grids[(rank * per_rank + k) % 4], seed=1000 + rank * per_rank + k, device="cuda")
                for k in range(per_rank)]
-    ws = systems.default_workspace(samples[0])
+    K = max(int(args.streams), 1)
+    # one workspace + one CUDA stream per host thread: handles are independent, ctypes releases the GIL, so K systems are
+    # in flight at once and their latency chains (small kernels, grid barriers, host round trips) overlap
+    workspaces = [systems.default_workspace(samples[0]) for _ in range(K)]
+    streams = [torch.cuda.Stream() for _ in range(K)]
+    ref_iters = {}
+
+    def worker(k):
+        its = 0
+        with torch.cuda.stream(streams[k]):
+            for j in range(k, len(samples), K):
+                x, res, _, A, G = workspaces[k].solve(samples[j], rtol=args.rtol)
+                assert res.converged == 1
+                if j in ref_iters:
+                    assert ref_iters[j] == int(res.iterations), (j, ref_iters[j], int(res.iterations))
+                its += int(res.iterations)
+                del A, G
+            streams[k].synchronize()
+        return its
+
+    # sequential reference pass on the default stream: the concurrent passes must reproduce its iteration counts
+    for j, s_ in enumerate(samples):
+        x, res, _, A, G = workspaces[0].solve(s_, rtol=args.rtol)
+        ref_iters[j] = int(res.iterations)
+        del A, G
+    torch.cuda.synchronize()
+    from concurrent.futures import ThreadPoolExecutor
+
+    pool = ThreadPoolExecutor(max_workers=K)
 
     def one_pass():
-        its = 0
-        for s in samples:
-            x, res, _, A, G = ws.solve(s, rtol=args.rtol)
-            its += int(res.iterations)
-            assert res.converged == 1
-        return its
+        if K == 1:
+            return worker(0)
+        return sum(pool.map(worker, range(K)))
 
     for _ in range(max(args.warmup, 1)):
         one_pass()
@@ -613,7 +638,8 @@ def main_batch_small(args):
             "warmup": max(args.warmup, 1), "ms_per_step": round(ms / args.steps, 3), "ms_per_system": round(ms / args.steps / per_rank, 3),
             "higher_is_better": True, "scaling": "weak", "dtype": "f64 (PCG) / f32 (GNN)", "data": "synthetic",
             "config": {"workload": f"{per_rank} Poisson systems per GPU, N in {{4096, 8000, 15625, 32768}}, Dirichlet patch, "
-                                   f"random-init GNN, rhs = A*mask, rtol {args.rtol:g}; one system at a time per GPU"},
+                                   f"random-init GNN, rhs = A*mask, rtol {args.rtol:g}; {K} system(s) in flight per GPU "
+                                   f"(host threads x CUDA streams)"},
             "mean_iterations": round(its / (per_rank * args.steps), 1),
             "gpu_launches": int(_lib.total_launches() - launches0)}), flush=True)
     if dist is not None:
@@ -633,6 +659,7 @@ def main():
                     help="batch: one independent 10 M-DOF system per GPU (the bench contract); rowpart: one system over all "
                          "GPUs; batch_small: a batch of small systems per GPU (BASELINE config C2)")
     ap.add_argument("--batch", type=int, default=64, help="batch_small: systems per step over all ranks")
+    ap.add_argument("--streams", type=int, default=4, help="batch_small: systems in flight per GPU (host threads x CUDA streams)")
     args = ap.parse_args()
     if args.impl == "reference":
         main_reference(args)

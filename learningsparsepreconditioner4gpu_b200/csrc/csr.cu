@@ -134,6 +134,9 @@ int csr_alloc(int n_rows, int n_cols, long long nnz, b200spai_csr_s** out) {
   cudaMemset(a->rowptr + n_rows + 1, 0, PAD * sizeof(int));
   cudaMemset(a->col + nnz, 0, PAD * sizeof(int));
   cudaMemset(a->val + nnz, 0, PAD * sizeof(double));
+  // these memsets run on the legacy default stream, which does NOT order with non-blocking streams: finish them
+  // before the caller's stream touches the arrays
+  cudaStreamSynchronize(cudaStreamLegacy);
   *out = a;
   return 0;
 }

@@ -433,6 +433,7 @@ int b200spai_dist_create(int32_t rank, int32_t world, int64_t ext_cap, b200spai_
   // plain cudaMalloc (not the pool): the segment is exported to the peer processes through CUDA IPC
   cudaError_t e = cudaMalloc((void**)&s->seg, s->seg_bytes);
   if (e == cudaSuccess) e = cudaMemset(s->seg, 0, s->seg_bytes);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(cudaStreamLegacy);
   if (e != cudaSuccess) {
     set_error(std::string("dist_create: ") + cudaGetErrorString(e));
     delete s;
@@ -535,6 +536,7 @@ int b200spai_dist_connect(b200spai_dist_t s, const unsigned char* handles, const
   B2_CUDA(cudaMemset(s->ticket_halo, 0, sizeof(unsigned)));
   B2_CUDA(cudaMemset(s->epoch, 0, (NVEC + NRED) * sizeof(unsigned long long)));
   B2_CUDA(cudaMemset(s->sc, 0, sizeof(PcgScalars)));
+  B2_CUDA(cudaStreamSynchronize(cudaStreamLegacy));  // default-stream memsets do not order with non-blocking streams
   B2_CUDA(cudaMallocHost((void**)&s->h_in, sizeof(PcgScalars)));
   B2_CUDA(cudaMallocHost((void**)&s->h_out, sizeof(PcgScalars)));
   B2_CUDA(cudaMallocHost((void**)&s->h_done, 2 * sizeof(int)));
@@ -568,6 +570,7 @@ int b200spai_dist_relayout(b200spai_dist_t s, const int64_t* layout) {
   // stale vectors of the previous system: a peer only writes into this segment after the first all-reduce of the
   // next solve, which needs this rank's contribution, so clearing here cannot race with its pushes
   B2_CUDA(cudaMemset(s->seg + SEG_VEC_OFFSET, 0, s->seg_bytes - SEG_VEC_OFFSET));
+  B2_CUDA(cudaStreamSynchronize(cudaStreamLegacy));
   return dist_apply_layout(s, layout);
 }
 

@@ -436,6 +436,9 @@ int b200spai_pcg_create(b200spai_csr_t a, b200spai_pcg_t* out) {
   B2_CUDA(cudaMemset(s->ticket, 0, sizeof(unsigned)));
   B2_CUDA(cudaMemset(s->sc, 0, sizeof(PcgScalars)));
   B2_CUDA(cudaMemset(s->p, 0, n * sizeof(double)));
+  // legacy-default-stream memsets do not order with a caller's non-blocking stream: finish them here, or the zeroing
+  // of p could land in the middle of the first solve
+  B2_CUDA(cudaStreamSynchronize(cudaStreamLegacy));
   if (scaffold_acquire(s)) {
     b200spai_pcg_destroy(s);
     return B200SPAI_ERR_CUDA;
