@@ -66,6 +66,17 @@ def test_get_workspace_names():
         infer.run_inference(None, [], device="cpu")
 
 
+def test_run_inference_fails_loudly_without_cuda():
+    from learningsparsepreconditioner4gpu_b200 import _lib, systems
+
+    if torch.cuda.is_available():
+        pytest.skip("needs a CPU-only box")
+    s = systems.poisson_sample(5, seed=1)
+    ws = systems.default_workspace(s)
+    with pytest.raises((_lib.B200SpaiError, RuntimeError, AssertionError)):      # .to("cuda") or require_cuda, never a CPU solve
+        infer.run_inference(ws, [s], warmup=0)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("rhs", ["mask", "neighbour"])
 def test_run_inference_on_gpu(tmp_path, rhs):
