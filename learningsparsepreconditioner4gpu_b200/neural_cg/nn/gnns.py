@@ -165,7 +165,19 @@ class NodeEdgeProcessing(nn.Module):
 
     # ---- device engine ------------------------------------------------------------------------------
     def _weights_version(self):
-        return tuple((p.data_ptr(), p._version) for p in self.parameters())
+        """Cheap fingerprint of the weights (storage pointer + in-place version counter of every parameter).  The
+        parameter list is collected once -- walking the module tree costs ~0.7 ms per call, which is more than the whole
+        GNN forward of a small mesh -- and again after ``_apply`` (``.to`` / ``.cuda`` / ``.float``).  Weights are
+        expected to change through ``load_state_dict`` or in-place ops (both bump ``_version``)."""
+        plist = self.__dict__.get("_plist")
+        if plist is None:
+            plist = list(self.parameters())
+            self.__dict__["_plist"] = plist
+        return tuple([(p.data_ptr(), p._version) for p in plist])
+
+    def _apply(self, fn, *args, **kwargs):
+        self.__dict__["_plist"] = None
+        return super()._apply(fn, *args, **kwargs)
 
     def _get_engine(self):
         ver = self._weights_version()
