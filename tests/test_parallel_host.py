@@ -261,3 +261,60 @@ def test_gloo_world3_g_swap_and_feature_halo():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert all(a and b for _, a, b in res), res
+
+
+def _random_spd_pattern(n, density, seed):
+    rng = np.random.default_rng(seed)
+    M = sp.random(n, n, density=density, random_state=rng, format="csr")
+    A = sp.csr_matrix(M.T @ M + sp.identity(n))
+    A.sort_indices()
+    return A
+
+
+@pytest.mark.parametrize("world", [1, 3, 4])
+@pytest.mark.parametrize("kind", ["grid", "irregular"])
+def test_partitioned_system_local_edge_lists(kind, world):
+    """PartitionedSystem's index side on CPU (no kernels): the row-owned list reproduces the owned rows of the matrix in
+    the extended column window, the target-owned list reproduces the owned rows of the TRANSPOSE (what G^T is assembled
+    from), both are row-major / column-ascending as b200spai_edges_to_csr requires, and ext_slice pads a negative shift."""
+    A = _grid_laplacian(6) if kind == "grid" else _random_spd_pattern(300, 0.01, 7)
+    ei = _edges(A)
+    n, E = A.shape[0], ei.shape[1]
+    vals = torch.arange(1, E + 1, dtype=torch.float64)        # distinct value per edge
+    Aval = sp.csr_matrix((vals.numpy(), (ei[0].numpy(), ei[1].numpy())), shape=(n, n))
+    starts = par.partition_rows(par.row_weights_from_edges(ei, n), world)
+    for rank in range(world):
+        ps = par.PartitionedSystem.__new__(par.PartitionedSystem)
+        # the constructor's collective (all_gather of layouts) needs a process group: build the layouts by hand
+        lay = [par.rank_layout(starts[r], starts[r + 1], *par.extended_range(ei, starts[r], starts[r + 1])) for r in range(world)]
+        ps.rank, ps.world, ps.group = rank, world, None
+        ps.N, ps.b, ps.starts = n, 1, list(starts)
+        ps.layout_nodes, ps.layouts_nodes = lay[rank], lay
+        rs, re, shift, hi = lay[rank]
+        ps.shift, ps.hi, ps.ext_nodes = shift, hi, hi - shift
+        ps.plan = par.g_exchange_plan(ei, starts, rank)
+        ps.e0, ps.e1, ps.ids_t = ps.plan[0], ps.plan[1], ps.plan[2]
+        ei_t = ei[:, ps.ids_t] - shift
+        ei_r = ei[:, ps.e0:ps.e1] - shift
+        order = torch.argsort(ei_t[1], stable=True)
+        ei_tT = torch.stack([ei_t[1][order], ei_t[0][order]])
+        ext = hi - shift
+        for e in (ei_r, ei_tT):                               # sorted row-major / column-ascending, in range
+            if e.shape[1]:
+                key = e[0] * ext + e[1]
+                assert bool((key[1:] > key[:-1]).all()) and int(e.min()) >= 0 and int(e.max()) < ext
+        lo = max(shift, 0)
+        # owned rows of A from the row-owned list
+        L = sp.csr_matrix((vals[ps.e0:ps.e1].numpy(), (ei_r[0].numpy(), ei_r[1].numpy())), shape=(ext, ext))[rs - shift:re - shift]
+        ref = sp.hstack([sp.csr_matrix((re - rs, lo - shift)), Aval[rs:re, lo:hi]]).tocsr()
+        assert (abs(L - ref)).nnz == 0 and L.nnz == Aval[rs:re].nnz
+        # owned rows of A^T from the target-owned list (values permuted with the same stable order)
+        vt = vals[ps.ids_t][order]
+        LT = sp.csr_matrix((vt.numpy(), (ei_tT[0].numpy(), ei_tT[1].numpy())), shape=(ext, ext))[rs - shift:re - shift]
+        refT = sp.hstack([sp.csr_matrix((re - rs, lo - shift)), Aval.T.tocsr()[rs:re, lo:hi]]).tocsr()
+        assert (abs(LT - refT)).nnz == 0
+        # ext_slice: rows [shift, hi) with zero rows in front when shift < 0
+        x = torch.arange(n * 2, dtype=torch.float32).reshape(n, 2) + 1
+        xs = ps.ext_slice(x)
+        assert xs.shape == (ext, 2) and torch.equal(xs[lo - shift:], x[lo:hi]) and float(xs[: lo - shift].abs().sum()) == 0.0
+        assert ps.row_starts == list(starts) and ps.layout == lay[rank]
