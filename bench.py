@@ -578,39 +578,23 @@ def main_batch_small(args):
     samples = [systems.poisson_sample(grids[(rank * per_rank + k) % 4], seed=1000 + rank * per_rank + k, device="cuda")
                for k in range(per_rank)]
     K = max(int(args.streams), 1)
-    # one workspace + one CUDA stream per host thread: handles are independent, ctypes releases the GIL, so K systems are
-    # in flight at once and their latency chains (small kernels, grid barriers, host round trips) overlap
-    workspaces = [systems.default_workspace(samples[0]) for _ in range(K)]
-    streams = [torch.cuda.Stream() for _ in range(K)]
-    ref_iters = {}
+    # K systems in flight per GPU: one workspace + one non-blocking CUDA stream per host thread (batch.BatchSolver)
+    from learningsparsepreconditioner4gpu_b200.batch import BatchSolver
 
-    def worker(k):
-        its = 0
-        with torch.cuda.stream(streams[k]):
-            for j in range(k, len(samples), K):
-                x, res, _, A, G = workspaces[k].solve(samples[j], rtol=args.rtol)
-                assert res.converged == 1
-                if j in ref_iters:
-                    assert ref_iters[j] == int(res.iterations), (j, ref_iters[j], int(res.iterations))
-                its += int(res.iterations)
-                del A, G
-            streams[k].synchronize()
-        return its
-
-    # sequential reference pass on the default stream: the concurrent passes must reproduce its iteration counts
-    for j, s_ in enumerate(samples):
-        x, res, _, A, G = workspaces[0].solve(s_, rtol=args.rtol)
-        ref_iters[j] = int(res.iterations)
+    solver = BatchSolver(lambda: systems.default_workspace(samples[0]), streams=K)
+    # sequential reference pass: the concurrent passes must reproduce its iteration counts
+    ref_iters = []
+    for s_ in samples:
+        x, res, _, A, G = solver.workspaces[0].solve(s_, rtol=args.rtol)
+        ref_iters.append(int(res.iterations))
         del A, G
     torch.cuda.synchronize()
-    from concurrent.futures import ThreadPoolExecutor
-
-    pool = ThreadPoolExecutor(max_workers=K)
 
     def one_pass():
-        if K == 1:
-            return worker(0)
-        return sum(pool.map(worker, range(K)))
+        results = solver.solve(samples, rtol=args.rtol)
+        its = [int(r.iterations) for _, r in results]
+        assert all(r.converged == 1 for _, r in results) and its == ref_iters, (its, ref_iters)
+        return sum(its)
 
     for _ in range(max(args.warmup, 1)):
         one_pass()

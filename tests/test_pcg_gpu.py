@@ -265,33 +265,24 @@ def test_small_kernel_edge_cases():
 
 
 def test_concurrent_solves_on_threads_and_streams_reproduce_sequential_results():
-    """Independent handles on different host threads / non-blocking CUDA streams (the batch_small bench mode) give the
-    bits of the sequential run -- catches work left on the legacy default stream and pool blocks recycled too early."""
-    from concurrent.futures import ThreadPoolExecutor
-
+    """batch.BatchSolver: independent handles on different host threads / non-blocking CUDA streams give the bits of the
+    sequential run -- catches work left on the legacy default stream and pool blocks recycled too early."""
     from learningsparsepreconditioner4gpu_b200 import systems
+    from learningsparsepreconditioner4gpu_b200.batch import BatchSolver, solve_batch
 
     samples = [systems.poisson_sample(g, seed=40 + i, device="cuda") for i, g in enumerate([8, 11, 9, 12, 10, 13, 8, 12] * 3)]
-    K = 8
-    wss = [systems.default_workspace(samples[0]) for _ in range(K)]
+    make = lambda: systems.default_workspace(samples[0])  # noqa: E731
+    ws = make()
     ref = []
     for s in samples:
-        x, res, _, A, G = wss[0].solve(s, rtol=1e-8)
+        x, res, _, A, G = ws.solve(s, rtol=1e-8)
         ref.append((int(res.iterations), x.clone()))
-    torch.cuda.synchronize()
-    streams = [torch.cuda.Stream() for _ in range(K)]
-
-    def worker(k):
-        bad = []
-        with torch.cuda.stream(streams[k]):
-            for rep in range(3):
-                for j in range(k, len(samples), K):
-                    x, res, _, A, G = wss[k].solve(samples[j], rtol=1e-8)
-                    if int(res.iterations) != ref[j][0] or not torch.equal(x, ref[j][1]):
-                        bad.append((j, int(res.iterations), ref[j][0]))
-            streams[k].synchronize()
-        return bad
-
-    with ThreadPoolExecutor(max_workers=K) as pool:
-        bad = sum(pool.map(worker, range(K)), [])
-    assert bad == []
+    solver = BatchSolver(make, streams=8)
+    for rep in range(3):
+        got = solver.solve(samples, rtol=1e-8)
+        bad = [(j, int(r.iterations), ref[j][0]) for j, (x, r) in enumerate(got)
+               if int(r.iterations) != ref[j][0] or not torch.equal(x, ref[j][1])]
+        assert bad == []
+    solver.close()
+    one = solve_batch(make, samples[:5], streams=1, rtol=1e-8)               # K = 1 runs in the calling thread
+    assert [int(r.iterations) for _, r in one] == [r[0] for r in ref[:5]]
