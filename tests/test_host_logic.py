@@ -161,3 +161,13 @@ def test_diagonal_of():
     assert np.array_equal(d, g["raw_diag"])
     dt = diagonal_of(torch.from_numpy(g["raw_edge_index"]), torch.from_numpy(g["raw_values"]), g["raw_mask"].shape[0])
     assert np.array_equal(dt.numpy(), g["raw_diag"])
+
+
+def test_batch_solver_needs_cuda():
+    from learningsparsepreconditioner4gpu_b200 import _lib
+    from learningsparsepreconditioner4gpu_b200.batch import BatchSolver
+
+    if torch.cuda.is_available():
+        pytest.skip("needs a CPU-only box")
+    with pytest.raises(_lib.B200SpaiError):
+        BatchSolver(lambda: None, streams=2)
