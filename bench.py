@@ -239,6 +239,12 @@ def main_ours(args):
     converged = int(res.converged)
     value = n_gpus * args.steps / (dev_ms * 1e-3)
 
+    pcg_mode = int(res.reserved)
+    fused_phases = None
+    if pcg_mode == 4:
+        fp_ms, fp_it = solver.fused_profile()
+        fused_phases = {"iterations": fp_it, "ms_per_iteration": {k: round(v / max(fp_it, 1), 4) for k, v in
+                                                                  zip(("sweep_GT+barrier", "sweep_G+barrier", "sweep_A+barrier"), fp_ms)}}
     # ---- per-kernel times of the PCG iteration (roofline), on the last step's matrices ----------------------
     kms = solver.profile_iterations(rhs, "ext_spai", iterations=20)
     nnzA, nnzG, n = A.nnz, G.nnz, N * ws.block_size
@@ -334,6 +340,7 @@ def main_ours(args):
                        "l2": "inputs larger than L2 (A + G + G^T = %.1f GB)" % ((nnzA + 2 * nnzG) * 12 / 1e9)},
             "time_to_tol_ms": round(float(np.mean(pcg_ms)), 3), "iterations": round(total_iters, 1), "converged": converged,
             "ms_per_iteration": round(float(np.mean(pcg_ms)) / max(float(np.mean(iters)), 1.0), 4),
+            "pcg_mode": pcg_mode, "fused_phases": fused_phases,
             "phases_ms_per_step": {k: round(v / args.steps, 3) for k, v in ph.items()},
             "e2e": {"value": round(e2e_value, 4), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": round(e2e_ms / args.steps, 3), "api": "SimpleTrainingWorkspace.solve path on a pinned-host sample"},

@@ -23,11 +23,12 @@
 #include <cstring>
 #include <vector>
 
-#include "pcg_kernels.cuh"
+#include "pcg_fused.cuh"
 
 namespace b200spai {
 
 constexpr int MAXR = 16;
+static_assert(MAXR == FUSED_MAXR, "the fused kernel's exchange block is sized for the same number of ranks");
 enum { V_P = 0, V_R = 1, V_T = 2, V_Z = 3, V_Q = 4, NVEC = 5 };
 enum { RED_INIT = 0, RED_RHO = 1 /* + ||r||^2 */, RED_PQ = 2, NRED = 3 };
 
@@ -38,7 +39,9 @@ struct SegHeader {
   double red_val[NRED][MAXR];
   double red_val2[NRED][MAXR];  // second scalar of a fused exchange (||r||^2 travelling with rho)
 };
-constexpr size_t SEG_VEC_OFFSET = (sizeof(SegHeader) + 255) / 256 * 256;
+// segment = SegHeader | FusedXchg (exchange block of the fused persistent kernel, mode 4) | NVEC extended vectors
+constexpr size_t SEG_XCHG_OFFSET = (sizeof(SegHeader) + 255) / 256 * 256;
+constexpr size_t SEG_VEC_OFFSET = SEG_XCHG_OFFSET + (sizeof(FusedXchg) + 255) / 256 * 256;
 
 struct DistCtx {
   int rank, world, n_push, n_recv;
@@ -265,6 +268,13 @@ struct b200spai_dist_s {
   int launches_per_iter[4] = {0, 0, 0, 0};
   int mode = 0;
   long long launches = 0;
+  // fused persistent kernel (mode 4): local second copies of r and p (extended), barrier block, plan
+  double *r1 = nullptr, *p1 = nullptr;
+  long long rp_cap = 0;
+  FusedSync* fsync = nullptr;
+  unsigned long long *fprof = nullptr, *fepoch = nullptr;
+  FusedPlan fplan;
+  bool fplan_valid = false;
   double* vec(int v) const { return reinterpret_cast<double*>(seg + SEG_VEC_OFFSET) + (size_t)v * (size_t)ext_cap; }
 };
 
@@ -509,6 +519,7 @@ static int dist_apply_layout(b200spai_dist_s* s, const int64_t* L) {
   s->d = nullptr;
   s->have_d = false;
   s->A = s->G = s->GT = nullptr;
+  s->fplan_valid = false;
   dist_drop_graphs(s);
   return 0;
 }
@@ -639,13 +650,111 @@ int b200spai_dist_pcg_setup(b200spai_dist_t s, b200spai_csr_t a_local, b200spai_
   s->GT = gt_local;
   s->eps = epsilon;
   s->have_d = false;
+  s->fplan_valid = false;
   dist_drop_graphs(s);
   return 0;
 }
 
 int b200spai_dist_pcg_set_mode(b200spai_dist_t s, int mode) {
-  B2_ARG(s && mode >= 0 && mode <= 2, "dist_pcg_set_mode: mode must be 0, 1 or 2");
+  B2_ARG(s && (mode == 0 || mode == 1 || mode == 2 || mode == 4), "dist_pcg_set_mode: mode must be 0, 1, 2 or 4");
   s->mode = mode;
+  return 0;
+}
+
+static int dist_fused_plan(b200spai_dist_s* s, cudaStream_t st) {
+  if (!s->fplan_valid) {
+    s->fplan = FusedPlan{};
+    if (s->A && s->G && s->GT && s->n > 0) B2_TRY(fused_plan(s->A, s->G, s->GT, st, &s->fplan));
+    s->fplan_valid = true;
+  }
+  return 0;
+}
+
+int b200spai_dist_pcg_fused_ok(b200spai_dist_t s, void* stream, int32_t* ok) {
+  B2_ARG(s && s->connected && ok, "dist_pcg_fused_ok: not connected or NULL argument");
+  *ok = 0;
+  if (!s->A) return 0;
+  B2_TRY(dist_fused_plan(s, as_stream(stream)));
+  // 2: the matrices are in the streaming regime (nnz >= 2^18), where the automatic choice takes the fused kernel
+  *ok = s->fplan.which >= 0 ? ((spmv_auto_kernel(s->A) == 2) ? 2 : 1) : 0;
+  return 0;
+}
+
+int b200spai_dist_pcg_fused_profile(b200spai_dist_t s, double* phase_ms3, int32_t* iterations, void* stream) {
+  B2_ARG(s && phase_ms3, "dist_pcg_fused_profile: NULL argument");
+  B2_ARG(s->fprof, "dist_pcg_fused_profile: no fused solve has run on this handle");
+  unsigned long long h[4] = {0, 0, 0, 0};
+  B2_CUDA(cudaMemcpyAsync(h, s->fprof, sizeof(h), cudaMemcpyDeviceToHost, as_stream(stream)));
+  B2_CUDA(cudaStreamSynchronize(as_stream(stream)));
+  for (int k = 0; k < 3; ++k) phase_ms3[k] = (double)h[k] * 1e-6;
+  if (iterations) *iterations = (int32_t)h[3];
+  return 0;
+}
+
+// Mode 4: the whole row-partitioned solve in ONE persistent kernel per rank (pcg_fused.cuh).
+static int dist_solve_fused(b200spai_dist_s* s, int precond, const double* b, double* x, cudaStream_t st) {
+  const long long ext = s->hi - s->shift;
+  if (ext + 2 > s->rp_cap) {
+    for (double** v : {&s->r1, &s->p1}) {
+      dev_free(*v);
+      *v = nullptr;
+      B2_TRY(dev_alloc(v, (size_t)ext + 2));
+    }
+    s->rp_cap = ext + 2;
+  }
+  if (!s->fsync) B2_TRY(dev_alloc(&s->fsync, 1));
+  if (!s->fprof) B2_TRY(dev_alloc(&s->fprof, 4));
+  if (!s->fepoch) {
+    B2_TRY(dev_alloc(&s->fepoch, FB_KINDS));
+    B2_CUDA(cudaMemsetAsync(s->fepoch, 0, FB_KINDS * sizeof(unsigned long long), st));
+  }
+  B2_CUDA(cudaMemsetAsync(s->fsync, 0, sizeof(FusedSync), st));
+  B2_CUDA(cudaMemsetAsync(s->fprof, 0, 4 * sizeof(unsigned long long), st));
+  FusedArgs a{};
+  a.A = fused_mat(s->A, s->fplan);
+  a.G = fused_mat(s->G, s->fplan);
+  a.GT = fused_mat(s->GT, s->fplan);
+  a.n = s->n;
+  a.off = s->off;
+  a.hi_halo = (int)(s->hi - s->re);
+  a.b = b;
+  a.x = x;
+  a.r0 = s->vec(V_R);
+  a.r1 = s->r1;
+  a.p0 = s->vec(V_P);
+  a.p1 = s->p1;
+  a.z = s->vec(V_Z);
+  a.q = s->vec(V_Q);
+  a.t = s->vec(V_T);
+  a.d = (precond == B200SPAI_PRECOND_EXT_SPAI_SCALED) ? s->d : nullptr;
+  a.eps = s->eps;
+  a.precond = precond;
+  a.sc = s->sc;
+  a.partials = s->partials;
+  a.hist = s->hist;
+  a.sync = s->fsync;
+  a.prof = s->fprof;
+  a.spin_limit = s->ctx.spin_limit;
+  FusedPeer& P = a.peer;
+  const DistCtx& c = s->ctx;
+  P.rank = s->rank;
+  P.world = s->world;
+  P.n_push = c.n_push;
+  for (int k = 0; k < c.n_push; ++k) {
+    const int q = c.push_peer[k];
+    P.push_lo[k] = (int)(c.push_src_off[k] - s->off);
+    P.push_hi[k] = P.push_lo[k] + c.push_len[k];
+    P.push_r[k] = c.vec[V_R][q] + c.push_dst_off[k];
+    P.push_t[k] = c.vec[V_T][q] + c.push_dst_off[k];
+    P.push_z[k] = c.vec[V_Z][q] + c.push_dst_off[k];
+    P.push_q[k] = c.vec[V_Q][q] + c.push_dst_off[k];
+  }
+  for (int q = 0; q < s->world; ++q)
+    P.xchg[q] = reinterpret_cast<FusedXchg*>(reinterpret_cast<unsigned char*>(s->peer_seg[q]) + SEG_XCHG_OFFSET);
+  P.epoch = s->fepoch;
+  B2_TRY(fused_launch(a, s->fplan, st));
+  s->launches += 1;
+  count_launches(1);
   return 0;
 }
 
@@ -667,7 +776,13 @@ int b200spai_dist_pcg_solve(b200spai_dist_t s, int precond, const double* b_loca
     const char* e = getenv("B200SPAI_PCG_MODE");
     mode = (e && atoi(e) == 1) ? 1 : 2;
   }
-  B2_TRY(dist_warm(s, precond, st));
+  if (mode == 4 && precond < B200SPAI_PRECOND_EXT_SPAI) mode = 2;  // the fused kernel is the SPAI iteration; same choice on every rank
+  if (mode == 4) {
+    B2_TRY(dist_fused_plan(s, st));
+    B2_ARG(s->fplan.which >= 0, "dist_pcg_solve: mode 4 does not apply to these matrices (ask b200spai_dist_pcg_fused_ok on every rank)");
+  } else {
+    B2_TRY(dist_warm(s, precond, st));
+  }
   PcgScalars init{};
   init.rtol = rtol;
   init.max_iter = max_iter;
@@ -737,7 +852,9 @@ int b200spai_dist_pcg_solve(b200spai_dist_t s, int precond, const double* b_loca
   *s->h_in = init;
   B2_CUDA(cudaEventRecord(s->ev0, st));
   B2_CUDA(cudaMemcpyAsync(s->sc, s->h_in, sizeof(PcgScalars), cudaMemcpyHostToDevice, st));
-  if (mode == 2) {
+  if (mode == 4) {
+    B2_TRY(dist_solve_fused(s, precond, b_local_dev, x_local_dev, st));
+  } else if (mode == 2) {
     if (s->n > 0) B2_CUDA(cudaMemcpyAsync(s->bw, b_local_dev, nbytes, cudaMemcpyDeviceToDevice, st));
     B2_CUDA(cudaGraphLaunch(s->exec[precond], st));
     if (s->n > 0) B2_CUDA(cudaMemcpyAsync(x_local_dev, s->xw, nbytes, cudaMemcpyDeviceToDevice, st));
@@ -843,8 +960,11 @@ int b200spai_dist_destroy(b200spai_dist_t s) {
   for (int q = 0; q < s->world; ++q)
     if (q != s->rank && s->peer_seg[q]) cudaIpcCloseMemHandle(s->peer_seg[q]);
   cudaFree(s->seg);
-  for (double* v : {s->xw, s->bw, s->d, s->partials, s->hist}) dev_free(v);
+  for (double* v : {s->xw, s->bw, s->d, s->partials, s->hist, s->r1, s->p1}) dev_free(v);
   dev_free(s->sc);
+  dev_free(s->fsync);
+  dev_free(s->fprof);
+  dev_free(s->fepoch);
   dev_free(s->ticket);
   dev_free(s->ticket_halo);
   dev_free(s->epoch);

@@ -24,6 +24,7 @@
 
 #include "pcg_kernels.cuh"
 #include "pcg_small.cuh"
+#include "pcg_fused.cuh"
 
 using namespace b200spai;
 
@@ -53,6 +54,11 @@ struct b200spai_pcg_s {
   cudaGraph_t graph[4] = {nullptr, nullptr, nullptr, nullptr};
   unsigned long long cond[4] = {0, 0, 0, 0};
   int launches_per_iter[4] = {0, 0, 0, 0};
+  // fused persistent kernel (mode 4)
+  FusedSync* fsync = nullptr;
+  unsigned long long* fprof = nullptr;  // [4] device
+  FusedPlan fplan;
+  bool fplan_valid = false;
 };
 
 namespace b200spai {
@@ -234,21 +240,32 @@ static int enqueue_iteration(b200spai_pcg_s* s, int precond, double* x, cudaStre
 
 static int build_graph(b200spai_pcg_s* s, int precond, cudaStream_t st) {
   if (s->exec[precond]) return 0;
-  // make sure lazily built partitions exist before capture (their build synchronises)
-  if (spmv_auto_kernel(s->A) == 2) {
+  // make sure the lazily built partitions / compressed streams of EVERY matrix that takes the streaming kernel exist
+  // before capture (their build launches kernels and synchronises, which would invalidate the capture)
+  {
     SpmvArgs warm{};
-    warm.x = s->p;
-    warm.y = s->q;
-    B2_TRY(spmv_launch(s->A, warm, SPMV_PLAIN, 0, st));
-    if (precond >= B200SPAI_PRECOND_EXT_SPAI) {
-      warm.x = s->r;
-      warm.y = s->t;
-      if (spmv_auto_kernel(s->GT) == 2) B2_TRY(spmv_launch(s->GT, warm, SPMV_PLAIN, 0, st));
-      warm.x = s->t;
-      warm.y = s->z;
-      if (spmv_auto_kernel(s->G) == 2) B2_TRY(spmv_launch(s->G, warm, SPMV_PLAIN, 0, st));
+    bool any = false;
+    if (spmv_auto_kernel(s->A) == 2) {
+      warm.x = s->p;
+      warm.y = s->q;
+      B2_TRY(spmv_launch(s->A, warm, SPMV_PLAIN, 0, st));
+      any = true;
     }
-    B2_CUDA(cudaStreamSynchronize(st));
+    if (precond >= B200SPAI_PRECOND_EXT_SPAI) {
+      if (spmv_auto_kernel(s->GT) == 2) {
+        warm.x = s->r;
+        warm.y = s->t;
+        B2_TRY(spmv_launch(s->GT, warm, SPMV_PLAIN, 0, st));
+        any = true;
+      }
+      if (spmv_auto_kernel(s->G) == 2) {
+        warm.x = s->t;
+        warm.y = s->z;
+        B2_TRY(spmv_launch(s->G, warm, SPMV_PLAIN, 0, st));
+        any = true;
+      }
+    }
+    if (any) B2_CUDA(cudaStreamSynchronize(st));
   }
   cudaGraph_t graph = nullptr;
   cudaStream_t cs = s->cap_stream;  // the caller's stream may be the legacy default stream (not capturable)
@@ -335,6 +352,57 @@ static int solve_small(b200spai_pcg_s* s, int precond, const double* b, double* 
   return 0;
 }
 
+// Large systems with a SPAI preconditioner: the whole solve in the persistent fused kernel (pcg_fused.cuh).
+static int fused_plan_for(b200spai_pcg_s* s, cudaStream_t st) {
+  if (!s->fplan_valid) {
+    B2_TRY(fused_plan(s->A, s->G, s->GT, st, &s->fplan));
+    s->fplan_valid = true;
+  }
+  return 0;
+}
+
+static int solve_fused(b200spai_pcg_s* s, int precond, const double* b, double* x, cudaStream_t st) {
+  if (!s->fsync) B2_TRY(dev_alloc(&s->fsync, 1));
+  if (!s->fprof) B2_TRY(dev_alloc(&s->fprof, 4));
+  B2_CUDA(cudaMemsetAsync(s->fsync, 0, sizeof(FusedSync), st));
+  B2_CUDA(cudaMemsetAsync(s->fprof, 0, 4 * sizeof(unsigned long long), st));
+  FusedArgs a{};
+  a.A = fused_mat(s->A, s->fplan);
+  a.G = fused_mat(s->G, s->fplan);
+  a.GT = fused_mat(s->GT, s->fplan);
+  a.n = s->n;
+  a.off = 0;
+  a.hi_halo = 0;
+  a.b = b;
+  a.x = x;
+  a.r0 = s->r;
+  a.r1 = s->bw;
+  a.p0 = s->p;
+  a.p1 = s->xw;
+  a.z = s->z;
+  a.q = s->q;
+  a.t = s->t;
+  a.d = (precond == B200SPAI_PRECOND_EXT_SPAI_SCALED) ? s->d : nullptr;
+  a.eps = s->eps;
+  a.precond = precond;
+  a.sc = s->sc;
+  a.partials = s->partials;
+  a.hist = s->hist;
+  a.sync = s->fsync;
+  a.prof = s->fprof;
+  int khz = 1965000, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
+  a.spin_limit = (long long)(20.0 * 1e3 * (double)khz);  // 20 s: a CTA that never arrives ends the solve instead of hanging the GPU
+  a.peer.rank = 0;
+  a.peer.world = 1;
+  a.peer.n_push = 0;
+  B2_TRY(fused_launch(a, s->fplan, st));
+  s->launches += 1;
+  count_launches(1);
+  return 0;
+}
+
 static int solve_impl(b200spai_pcg_s* s, int precond, const double* b, double* x, double rtol, int max_iter,
                       double* hist_out, cudaStream_t st, b200spai_pcg_result* res) {
   B2_ARG(s && b && x && res, "pcg_solve: NULL argument");
@@ -347,6 +415,15 @@ static int solve_impl(b200spai_pcg_s* s, int precond, const double* b, double* x
   const int sgrid = (mode == 0 || mode == 3) ? small_grid(s) : 0;
   if (mode == 3) B2_ARG(sgrid > 0, "pcg_solve: mode 3 (single cooperative kernel) needs a system of <= 131072 rows");
   if (mode == 0) mode = (sgrid > 0 && !getenv("B200SPAI_NO_SMALL") && default_mode() == 2) ? 3 : default_mode();
+  if ((mode == 2 && s->mode == 0) || mode == 4) {  // auto: large SPAI solves take the fused persistent kernel when it applies
+    bool fused = false;
+    if (precond >= B200SPAI_PRECOND_EXT_SPAI) {
+      B2_TRY(fused_plan_for(s, st));
+      fused = s->fplan.which >= 0;
+    }
+    if (mode == 4) B2_ARG(fused, "pcg_solve: mode 4 (fused persistent kernel) needs a SPAI preconditioner and matrices that share one stream format");
+    if (fused) mode = 4;
+  }
 
   PcgScalars init{};
   init.rtol = rtol;
@@ -361,6 +438,8 @@ static int solve_impl(b200spai_pcg_s* s, int precond, const double* b, double* x
   B2_CUDA(cudaMemcpyAsync(s->sc, s->h_in, sizeof(PcgScalars), cudaMemcpyHostToDevice, st));
   if (mode == 3) {
     B2_TRY(solve_small(s, precond, b, x, sgrid, st));
+  } else if (mode == 4) {
+    B2_TRY(solve_fused(s, precond, b, x, st));
   } else if (mode == 2) {
     B2_CUDA(cudaMemcpyAsync(s->bw, b, (size_t)s->n * sizeof(double), cudaMemcpyDeviceToDevice, st));
     B2_CUDA(cudaGraphLaunch(s->exec[precond], st));
@@ -464,6 +543,7 @@ int b200spai_pcg_set_spai(b200spai_pcg_t s, b200spai_csr_t g, double epsilon, vo
     s->graph[i] = nullptr;
   }
   B2_TRY(b200spai_csr_transpose(g, stream, &s->GT));
+  s->fplan_valid = false;
   s->G = g;
   s->eps = epsilon;
   B2_CUDA(cudaEventRecord(e1, st));
@@ -475,7 +555,7 @@ int b200spai_pcg_set_spai(b200spai_pcg_t s, b200spai_csr_t g, double epsilon, vo
 }
 
 int b200spai_pcg_set_mode(b200spai_pcg_t s, int mode) {
-  B2_ARG(s && mode >= 0 && mode <= 3, "pcg_set_mode: mode must be 0, 1, 2 or 3");
+  B2_ARG(s && mode >= 0 && mode <= 4, "pcg_set_mode: mode must be 0, 1, 2, 3 or 4");
   s->mode = mode;
   return 0;
 }
@@ -589,6 +669,17 @@ int b200spai_pcg_profile_iterations(b200spai_pcg_t s, int precond, const double*
   return 0;
 }
 
+int b200spai_pcg_fused_profile(b200spai_pcg_t s, double* phase_ms3, int32_t* iterations, void* stream) {
+  B2_ARG(s && phase_ms3, "pcg_fused_profile: NULL argument");
+  B2_ARG(s->fprof, "pcg_fused_profile: no fused solve has run on this handle");
+  unsigned long long h[4] = {0, 0, 0, 0};
+  B2_CUDA(cudaMemcpyAsync(h, s->fprof, sizeof(h), cudaMemcpyDeviceToHost, as_stream(stream)));
+  B2_CUDA(cudaStreamSynchronize(as_stream(stream)));
+  for (int k = 0; k < 3; ++k) phase_ms3[k] = (double)h[k] * 1e-6;
+  if (iterations) *iterations = (int32_t)h[3];
+  return 0;
+}
+
 int b200spai_pcg_launch_count(b200spai_pcg_t s, int64_t* launches) {
   B2_ARG(s && launches, "pcg_launch_count: NULL argument");
   *launches = s->launches;
@@ -605,6 +696,8 @@ int b200spai_pcg_destroy(b200spai_pcg_t s) {
   for (double* v : {s->r, s->z, s->p, s->q, s->t, s->d, s->bw, s->xw, s->partials, s->hist}) dev_free(v);
   dev_free(s->sc);
   dev_free(s->ticket);
+  dev_free(s->fsync);
+  dev_free(s->fprof);
   // the scaffold's streams and events are idle here: every solve synchronises before it returns
   scaffold_release(s);
   delete s;

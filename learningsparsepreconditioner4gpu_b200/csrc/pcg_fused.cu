@@ -1,0 +1,119 @@
+// Host side of the fused persistent PCG kernel (pcg_fused.cuh): eligibility, instantiation table, cooperative launch.
+#include "pcg_fused.cuh"
+
+namespace b200spai {
+
+namespace {
+
+constexpr int F_STAGES = 2;
+constexpr int F_NCW = 8;
+
+template <int CAP, typename VT, typename CT>
+struct Inst {
+  static constexpr int threads = (F_NCW + 1) * 32;
+  static int smem() { return StreamCfg<CAP, VT, CT>::smem_bytes(F_STAGES) + 64; }
+  static const void* fn() { return (const void*)pcg_fused_kernel<CAP, F_STAGES, F_NCW, VT, CT>; }
+  static int grid(int* out) {
+    static int cached[64] = {0};
+    int dev = 0;
+    B2_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (cached[dev] == 0) {
+      B2_CUDA(cudaFuncSetAttribute(fn(), cudaFuncAttributeMaxDynamicSharedMemorySize, smem()));
+      int occ = 0;
+      B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn(), threads, smem()));
+      int coop = 0;
+      B2_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+      cached[dev] = (coop && occ > 0) ? sm_count() * occ : -1;
+    }
+    *out = cached[dev];
+    return 0;
+  }
+  static int launch(const FusedArgs& a, int grid, cudaStream_t st) {
+    void* args[] = {(void*)&a};
+    B2_CUDA(cudaLaunchCooperativeKernel(fn(), dim3((unsigned)grid), dim3(threads), args, (size_t)smem(), st));
+    return 0;
+  }
+};
+
+template <int CAP>
+int grid_for(int fmt, int* out) {
+  switch (fmt) {
+    case 3: return Inst<CAP, float, unsigned short>::grid(out);
+    case 1: return Inst<CAP, float, int>::grid(out);
+    case 2: return Inst<CAP, double, unsigned short>::grid(out);
+    default: return Inst<CAP, double, int>::grid(out);
+  }
+}
+template <int CAP>
+int launch_for(int fmt, const FusedArgs& a, int grid, cudaStream_t st) {
+  switch (fmt) {
+    case 3: return Inst<CAP, float, unsigned short>::launch(a, grid, st);
+    case 1: return Inst<CAP, float, int>::launch(a, grid, st);
+    case 2: return Inst<CAP, double, unsigned short>::launch(a, grid, st);
+    default: return Inst<CAP, double, int>::launch(a, grid, st);
+  }
+}
+
+bool fused_disabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200SPAI_NO_FUSED");
+    v = (e && atoi(e) != 0) ? 1 : 0;
+  }
+  return v == 1;
+}
+
+}  // namespace
+
+int fused_plan(b200spai_csr_s* A, b200spai_csr_s* G, b200spai_csr_s* GT, cudaStream_t st, FusedPlan* plan) {
+  plan->which = -1;
+  if (fused_disabled() || !A || !G || !GT) return 0;
+  b200spai_csr_s* ms[3] = {A, G, GT};
+  long long nnz_max = 0;
+  for (auto* m : ms) {
+    if (m->n_rows <= 0) return 0;
+    nnz_max = std::max(nnz_max, m->nnz);
+  }
+  const int which = (nnz_max >= (1LL << 22)) ? 2 : 1;
+  for (auto* m : ms) {
+    B2_TRY(csr_ensure_partition(m, which, st));
+    B2_TRY(csr_ensure_f32(m, st));
+    B2_TRY(csr_ensure_col16(m, st));
+  }
+  // one instantiation serves the three sweeps: the matrices must share a stream format (true on this path: A and G
+  // are widened fp32 tensors on one pattern); otherwise the launch-per-kernel drivers take over
+  const int f32 = A->f32_state, c16 = A->c16_state;
+  for (auto* m : ms)
+    if (m->f32_state != f32 || m->c16_state != c16) return 0;
+  const int fmt = (f32 == 1 ? 1 : 0) | (c16 == 1 ? 2 : 0);
+  int grid = 0;
+  if (which == 2) B2_TRY(grid_for<4096>(fmt, &grid));
+  else B2_TRY(grid_for<2048>(fmt, &grid));
+  if (grid <= 0 || 2 * grid > MAX_PARTIALS) return 0;
+  plan->which = which;
+  plan->fmt = fmt;
+  plan->grid = grid;
+  plan->threads = (F_NCW + 1) * 32;
+  return 0;
+}
+
+FusedMat fused_mat(const b200spai_csr_s* M, const FusedPlan& plan) {
+  FusedMat m{};
+  m.rowptr = M->rowptr;
+  m.col = M->col;
+  m.val = M->val;
+  m.sval = (plan.fmt & 1) ? (const void*)M->val32 : (const void*)M->val;
+  m.scol = (plan.fmt & 2) ? (const void*)M->col16 : (const void*)M->col;
+  m.rowfirst = M->rowfirst;
+  m.blk = M->blk[plan.which];
+  m.nblk = M->nblk[plan.which];
+  return m;
+}
+
+int fused_launch(const FusedArgs& args, const FusedPlan& plan, cudaStream_t st) {
+  if (plan.which == 2) return launch_for<4096>(plan.fmt, args, plan.grid, st);
+  return launch_for<2048>(plan.fmt, args, plan.grid, st);
+}
+
+}  // namespace b200spai

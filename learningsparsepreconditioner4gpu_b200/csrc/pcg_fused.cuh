@@ -1,0 +1,701 @@
+// Whole PCG solve of a LARGE system in ONE persistent kernel (driver "mode 4"), single GPU or row-partitioned over the
+// GPUs of an NVSwitch box.  It replaces the 5-launch iteration of pcg.cu / the 8-launch iteration of dist.cu:
+//
+//   P1   [x += alpha p ; r' = r - alpha q ; ||r'||^2]  and  t = G^T r'  [/ d]
+//        r' of a NEIGHBOUR row is recomputed inside the gather from (r, q) with the two roundings its owner uses
+//   --- grid barrier B1: ||r'||^2 -> iteration count, history, convergence / max_iter test (scipy cg order) ---
+//   P2   z = G t + eps r' [/ d] ; rho = r'.z
+//   --- grid barrier B2: rho -> beta ---
+//   P3   p' = z + beta p  and  q = A p'  (p' of a neighbour column recomputed from (z, p)) ; p'.q
+//   --- grid barrier B3: p'.q -> alpha (breakdown if <= 0) ---
+//
+// so the two pure vector passes of the 5-kernel iteration (72 n bytes) disappear into the SpMV prologues, an iteration
+// is 3 matrix sweeps, and nothing is launched, captured or polled by the host while the solve runs.
+//
+// Each sweep is the TMA-staged streaming SpMV of spmv.cuh (row blocks staged by one producer lane with cp.async.bulk +
+// mbarrier, consumer warps row-parallel out of shared memory, lossless fp32-value / 16-bit-column-step streams, row
+// sums in scipy's sequential rounded order).  The matrices never change, so the producer simply runs ahead through the
+// cyclic schedule G^T, G, A, G^T, ... : the first blocks of the next sweep are already in shared memory while the CTA
+// waits at a barrier (no pipeline ramp per sweep, no launch tail).
+//
+// Grid barrier = monotonic arrive counter + release word in global memory (cooperative launch guarantees
+// co-residency).  Every CTA deposits its two partial sums before arriving; warp 0 of CTA 0 sums them in CTA order
+// (deterministic), and all CTAs read the totals that travel with the release -> identical scalars and identical
+// branches everywhere.  Gathered vectors are read with plain ld.global (L1-cached); the acquire that ends every barrier
+// invalidates L1, which is what makes re-reading vectors other SMs rewrote legal (ld.global.nc would not be).
+//
+// Row-partitioned (world > 1): every rank runs this kernel on its own rows.  The thread that computes an owned BOUNDARY
+// entry of t, z or q also stores it straight into the neighbours' extended vectors (peer stores over NVLink, "dual
+// store"), fences at system scope and arrives; CTA 0's warp then all-reduces the two totals through every rank's
+// peer-mapped exchange block (value + epoch per (barrier kind, source rank), summed in RANK order -> identical bits on
+// all ranks) before it releases the local grid.  The release/acquire chain (peer store -> fence.sys -> arrive ->
+// master acquire -> st.release.sys epoch -> peer's acquire -> peer's release of its grid) also orders the halo data,
+// so one barrier = halo exchange + all-reduce + grid sync.  Halo entries of r' and p' are recomputed locally from the
+// halo of (r, q) and (z, p): they carry the bits their owner computes and are never sent.
+#pragma once
+#include "pcg_kernels.cuh"
+
+namespace b200spai {
+
+constexpr int FUSED_MAXR = 16;
+#ifndef FUSED_U2
+#define FUSED_U2 8
+#endif
+#ifndef FUSED_MINB
+#define FUSED_MINB 3
+#endif
+enum { FB_INIT = 0, FB_RR = 1, FB_RHO = 2, FB_PQ = 3, FB_READY = 4, FB_KINDS = 5 };
+
+struct FusedMat {
+  const int* rowptr;
+  const int* col;
+  const double* val;    // canonical arrays (rows longer than a stage)
+  const void* sval;     // streamed values: float or double
+  const void* scol;     // streamed columns: u16 steps or int
+  const int* rowfirst;  // first column of each row (u16 stream only)
+  const int4* blk;      // row blocks {r0, rowptr[r0], r1, rowptr[r1]}, any order
+  int nblk;
+};
+
+struct FusedSync {  // one per solver, zeroed before every launch
+  unsigned long long arrive;
+  unsigned long long pad0[15];
+  unsigned long long release;
+  unsigned long long pad1[15];
+  double bcast[2][4];  // [generation & 1][total0, total1, ok, -]
+};
+
+struct FusedXchg {  // one per rank, inside the peer-mapped segment; never reset (epochs are monotonic across solves)
+  unsigned long long epoch[FB_KINDS][FUSED_MAXR];
+  double val[FB_KINDS][FUSED_MAXR][2];
+};
+
+struct FusedPeer {
+  int rank, world, n_push;
+  int push_lo[FUSED_MAXR], push_hi[FUSED_MAXR];  // owned local rows [lo, hi) a neighbour's extended range contains
+  double* push_r[FUSED_MAXR];                    // address of row push_lo[s] inside the neighbour's extended vector
+  double* push_t[FUSED_MAXR];
+  double* push_z[FUSED_MAXR];
+  double* push_q[FUSED_MAXR];
+  FusedXchg* xchg[FUSED_MAXR];  // exchange block of every rank (own included)
+  unsigned long long* epoch;    // [FB_KINDS] local monotonic counters (device memory, survive across solves)
+};
+
+struct FusedArgs {
+  FusedMat A, G, GT;
+  int n;                 // owned rows
+  int off;               // extended index of owned row 0 (= number of low halo entries)
+  int hi_halo;           // extended entries behind the owned slice
+  const double* b;       // [n]
+  double* x;             // [n]
+  double *r0, *r1, *p0, *p1, *z, *q, *t;  // EXTENDED vectors (index 0 = first low halo entry)
+  const double* d;       // [n] diagonal (scaled SPAI) or nullptr
+  double eps;
+  int precond;
+  PcgScalars* sc;
+  double* partials;      // [2 * gridDim.x]
+  double* hist;
+  FusedSync* sync;
+  long long spin_limit;  // clock64 ticks before a wait gives up
+  unsigned long long* prof;  // optional [4]: ns spent in P1+B1, P2+B2, P3+B3 (CTA 0's view), number of iterations
+  FusedPeer peer;
+};
+
+// ---- memory-model helpers -------------------------------------------------------------------------------------
+__device__ __forceinline__ double ld_coh(const double* p) {  // coherent (L1-cached) load; NOT ld.global.nc
+  double v;
+  asm volatile("ld.global.f64 %0, [%1];" : "=d"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_gpu_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_release_gpu_add_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void f_st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long f_ld_relaxed_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+template <int NT>
+__device__ __forceinline__ void bar_consumers() {
+  asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
+}
+
+// Grid barrier + deterministic reduction of (v0, v1) + (world > 1) all-reduce over the ranks.  Called by every
+// CONSUMER thread of every CTA; returns false when a wait timed out (peer or CTA gone): the solve is then abandoned.
+// `pushed`: this thread stored into a peer's memory since the last barrier.
+template <int NCW>
+__device__ __forceinline__ bool fused_barrier(const FusedArgs& a, unsigned long long& gen, int kind, double v0, double v1,
+                                              bool pushed, double* red, double& t0, double& t1) {
+  constexpr int NCT = NCW * 32;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const unsigned G = gridDim.x;
+  gen += 1;
+  v0 = warp_sum(v0);
+  v1 = warp_sum(v1);
+  if (lane == 0) {
+    red[warp] = v0;
+    red[16 + warp] = v1;
+  }
+  if (pushed) __threadfence_system();  // this thread's peer stores are performed before its CTA arrives
+  bar_consumers<NCT>();
+  if (warp == 0) {
+    double c0 = (lane < NCW) ? red[lane] : 0.0, c1 = (lane < NCW) ? red[16 + lane] : 0.0;
+    c0 = warp_sum(c0);
+    c1 = warp_sum(c1);
+    if (lane == 0) {
+      a.partials[blockIdx.x] = c0;
+      a.partials[G + blockIdx.x] = c1;
+      red_release_gpu_add_u64(&a.sync->arrive, 1ull);  // release: partials, vector writes and (fenced) peer stores
+    }
+    if (blockIdx.x == 0) {
+      // ---- master: wait for every CTA, sum in CTA order, exchange with the other ranks, release ----
+      int ok = 1;
+      if (lane == 0) {
+        const long long w0 = clock64();
+        while (ld_acquire_gpu_u64(&a.sync->arrive) < gen * (unsigned long long)G)
+          if (clock64() - w0 > a.spin_limit) {
+            ok = 0;
+            break;
+          }
+      }
+      __syncwarp();
+      double s0 = 0.0, s1 = 0.0;
+      for (unsigned i = lane; i < G; i += 32) {
+        s0 += __ldcg(a.partials + i);
+        s1 += __ldcg(a.partials + G + i);
+      }
+      s0 = warp_sum(s0);
+      s1 = warp_sum(s1);
+      const FusedPeer& P = a.peer;
+      if (P.world > 1) {
+        unsigned long long ep = 0;
+        if (lane == 0) ep = ++P.epoch[kind];
+        ep = __shfl_sync(0xffffffffu, ep, 0);
+        double r0v = 0.0, r1v = 0.0;
+        if (lane < P.world) {
+          FusedXchg* X = P.xchg[lane];
+          X->val[kind][P.rank][0] = s0;
+          X->val[kind][P.rank][1] = s1;
+          f_st_release_sys(&X->epoch[kind][P.rank], ep);  // cumulative: also publishes the halo stores the arrivals ordered
+          const FusedXchg* M = P.xchg[P.rank];
+          const long long w0 = clock64();
+          while (f_ld_relaxed_sys(&M->epoch[kind][lane]) < ep)
+            if (clock64() - w0 > a.spin_limit) {
+              ok = 0;
+              break;
+            }
+          asm volatile("fence.acq_rel.sys;" ::: "memory");
+          r0v = *reinterpret_cast<const volatile double*>(&M->val[kind][lane][0]);
+          r1v = *reinterpret_cast<const volatile double*>(&M->val[kind][lane][1]);
+        }
+        s0 = 0.0;
+        s1 = 0.0;
+        for (int r = 0; r < P.world; ++r) {  // rank order: identical bits on every rank
+          s0 += __shfl_sync(0xffffffffu, r0v, r);
+          s1 += __shfl_sync(0xffffffffu, r1v, r);
+        }
+      }
+      ok = __all_sync(0xffffffffu, ok);
+      if (lane == 0) {
+        double* bc = a.sync->bcast[gen & 1];
+        bc[0] = s0;
+        bc[1] = s1;
+        bc[2] = ok ? 1.0 : 0.0;
+        st_release_gpu_u64(&a.sync->release, gen);
+      }
+    }
+    if (lane == 0) {
+      const long long w0 = clock64();
+      bool seen = true;
+      while (ld_acquire_gpu_u64(&a.sync->release) < gen)
+        if (clock64() - w0 > 3 * a.spin_limit) {
+          seen = false;
+          break;
+        }
+      const double* bc = a.sync->bcast[gen & 1];
+      red[32] = __ldcg(bc + 0);
+      red[33] = __ldcg(bc + 1);
+      red[34] = seen ? __ldcg(bc + 2) : 0.0;
+    }
+  }
+  bar_consumers<NCT>();
+  t0 = red[32];
+  t1 = red[33];
+  const bool ok = red[34] != 0.0;
+  return ok;
+}
+
+template <int CAP, int STAGES, typename VT, typename CT>
+struct FusedSmem {
+  using C = StreamCfg<CAP, VT, CT>;
+  VT* vals;
+  unsigned char* cols;
+  int* rptr;
+  int* first;
+  int4* hdr;
+  uint64_t *full, *empty;
+};
+
+// One matrix sweep by the consumer threads: blocks first, first + G, ... of M.  PH = 1 (G^T), 2 (G), 3 (A).
+// FLAG: PH 1 -> an (alpha, p, q) update is pending; PH 3 -> first iteration (p' = z).
+template <int PH, bool FLAG, int CAP, int STAGES, int NCW, typename VT, typename CT>
+__device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& M, const FusedSmem<CAP, STAGES, VT, CT>& sm,
+                                            long long& item, const double* r, double* rn, const double* p, double* pn,
+                                            double alpha, double beta, double& acc, bool& pushed) {
+  using C = StreamCfg<CAP, VT, CT>;
+  constexpr bool DELTA = C::DELTA;
+  constexpr int NCT = NCW * 32;
+  constexpr int CA = 16 / (int)sizeof(CT);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int G = gridDim.x, firstb = blockIdx.x;
+  const int n_items = (firstb < M.nblk) ? (M.nblk - firstb + G - 1) / G : 0;
+  const VT* Aval = reinterpret_cast<const VT*>(M.sval);
+  const int off = a.off;
+  const double* q = a.q;
+  const double* z = a.z;
+  const double* t = a.t;
+  const bool scaled = a.d != nullptr;
+  const int np = a.peer.n_push;
+
+  // the gathered vector entry at extended column c
+  auto entry = [&](int c) -> double {
+    if (PH == 1) {
+      if (FLAG) return __dsub_rn(ld_coh(r + c), __dmul_rn(alpha, ld_coh(q + c)));
+      return ld_coh(r + c);
+    } else if (PH == 2) {
+      return ld_coh(t + c);
+    } else {
+      if (FLAG) return ld_coh(z + c);
+      return __dadd_rn(__dmul_rn(ld_coh(p + c), beta), ld_coh(z + c));
+    }
+  };
+  // owner work of local row i whose matrix-row sum is `sum`; o0..o3 were loaded before the row walk
+  auto finish = [&](int i, double sum, double o0, double o1, double o2, double o3) {
+    const int e = off + i;
+    double out;
+    double* const* dst;
+    if (PH == 1) {  // o0 = r, o1 = q, o2 = p, o3 = x
+      if (FLAG) {
+        a.x[i] = __dadd_rn(o3, __dmul_rn(alpha, o2));
+        const double rv = __dsub_rn(o0, __dmul_rn(alpha, o1));
+        rn[e] = rv;
+        acc += rv * rv;
+      }
+      out = scaled ? sum / a.d[i] : sum;
+      a.t[e] = out;
+      dst = a.peer.push_t;
+    } else if (PH == 2) {  // o0 = r'
+      double ev = __dmul_rn(a.eps, o0);
+      if (scaled) ev = ev / a.d[i];
+      out = __dadd_rn(sum, ev);
+      a.z[e] = out;
+      acc += o0 * out;
+      dst = a.peer.push_z;
+    } else {  // o0 = z, o1 = p
+      const double pv = FLAG ? o0 : __dadd_rn(__dmul_rn(o1, beta), o0);
+      pn[e] = pv;
+      out = sum;
+      a.q[e] = out;
+      acc += pv * out;
+      dst = a.peer.push_q;
+    }
+    for (int s = 0; s < np; ++s)
+      if (i >= a.peer.push_lo[s] && i < a.peer.push_hi[s]) {
+        dst[s][i - a.peer.push_lo[s]] = out;
+        pushed = true;
+      }
+  };
+  auto prefetch = [&](int i, double& o0, double& o1, double& o2, double& o3) {
+    const int e = off + i;
+    o0 = o1 = o2 = o3 = 0.0;
+    if (PH == 1) {
+      o0 = ld_coh(r + e);
+      if (FLAG) {
+        o1 = ld_coh(q + e);
+        o2 = ld_coh(p + e);
+        o3 = ld_coh(a.x + i);
+      }
+    } else if (PH == 2) {
+      o0 = ld_coh(r + e);
+    } else {
+      o0 = ld_coh(z + e);
+      if (!FLAG) o1 = ld_coh(p + e);
+    }
+  };
+
+  for (int it = 0; it < n_items; ++it, ++item) {
+    const int slot = (int)(item % STAGES);
+    mbar_wait(sm.full + slot, (uint32_t)((item / STAGES) & 1));
+    const int4 info = sm.hdr[slot];
+    const int r0 = info.x, lo = info.y, r1 = info.z, hi = info.w;
+    const int cnt = hi - lo;
+    if (cnt > 0 && cnt <= CAP) {
+      const VT* vals = sm.vals + slot * C::VALS + (lo & 3);
+      const CT* cols = reinterpret_cast<const CT*>(sm.cols + slot * C::COLS_BYTES) + (lo & (CA - 1));
+      const int* rptr = sm.rptr + slot * C::RPTR + (r0 & 3);
+      const int* rfirst = sm.first + slot * C::RPTR + (r0 & 3);
+      for (int rr = tid; rr < r1 - r0; rr += NCT) {
+        const int row = r0 + rr;
+        double o0, o1, o2, o3;
+        prefetch(row, o0, o1, o2, o3);
+        int k = rptr[rr] - lo;
+        const int e = rptr[rr + 1] - lo;
+        int cprev = DELTA ? rfirst[rr] : 0;
+        double sum = 0.0;
+        // chunk width: 16 entries (a mesh row in one pass) when an entry is one gather, 8 when it is two (r and q, z and
+        // p) -- the gathers of a chunk are all in flight before the first add, and 2 x 16 of them do not fit the
+        // register budget of three resident CTAs per SM
+        constexpr int U = ((PH == 1 && FLAG) || (PH == 3 && !FLAG)) ? FUSED_U2 : 16;
+#pragma unroll 1
+        for (; k < e; k += U) {
+          int c[U];
+          double pr[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int raw = (int)cols[k + u];
+            if (DELTA) {
+              cprev += (k + u < e) ? raw : 0;
+            } else {
+              cprev = (k + u < e) ? raw : cprev;
+            }
+            c[u] = cprev;
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u) pr[u] = __dmul_rn((k + u < e) ? (double)vals[k + u] : 0.0, entry(c[u]));
+#pragma unroll
+          for (int u = 0; u < U; ++u) sum = __dadd_rn(sum, pr[u]);
+        }
+        finish(row, sum, o0, o1, o2, o3);
+      }
+    } else {
+      // a row longer than the stage capacity (or a block of empty rows): warp per row from global memory, products
+      // added in entry order so these rows too carry scipy's bits
+      for (int row = r0 + warp; row < r1; row += NCW) {
+        const int s = __ldg(M.rowptr + row), e = __ldg(M.rowptr + row + 1);
+        double sum = 0.0;
+        for (int k0 = s; k0 < e; k0 += 32) {
+          const int k = k0 + lane;
+          const double pv = (k < e) ? __dmul_rn((double)__ldg(Aval + k), entry(__ldg(M.col + k))) : 0.0;
+          const int m = min(32, e - k0);
+          for (int j = 0; j < m; ++j) sum = __dadd_rn(sum, __shfl_sync(0xffffffffu, pv, j));
+        }
+        if (lane == 0) {
+          double o0, o1, o2, o3;
+          prefetch(row, o0, o1, o2, o3);
+          finish(row, sum, o0, o1, o2, o3);
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(sm.empty + slot);
+  }
+}
+
+template <int CAP, int STAGES, int NCW, typename VT, typename CT>
+__global__ void __launch_bounds__((NCW + 1) * 32, FUSED_MINB) pcg_fused_kernel(const __grid_constant__ FusedArgs a) {
+  using C = StreamCfg<CAP, VT, CT>;
+  constexpr bool DELTA = C::DELTA;
+  constexpr int NCT = NCW * 32;
+  constexpr int CA = 16 / (int)sizeof(CT);
+  static_assert(NCW <= 16, "reduction scratch holds 16 warps");
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  unsigned char* sp = smem_raw;
+  FusedSmem<CAP, STAGES, VT, CT> sm;
+  sm.vals = reinterpret_cast<VT*>(sp);               sp += STAGES * C::VALS_BYTES;
+  sm.cols = sp;                                      sp += STAGES * C::COLS_BYTES;
+  sm.rptr = reinterpret_cast<int*>(sp);              sp += STAGES * C::RPTR * 4;
+  sm.first = reinterpret_cast<int*>(sp);             sp += DELTA ? STAGES * C::RPTR * 4 : 0;
+  sm.hdr = reinterpret_cast<int4*>(sp);              sp += STAGES * 16;
+  sm.full = reinterpret_cast<uint64_t*>(sp);         sp += STAGES * 8;
+  sm.empty = reinterpret_cast<uint64_t*>(sp);        sp += STAGES * 8;
+  double* red = reinterpret_cast<double*>(sp);       sp += 36 * 8;
+  volatile int* s_done = reinterpret_cast<volatile int*>(sp);
+
+  const int tid = threadIdx.x;
+  const int G = gridDim.x;
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(sm.full + s, 1);
+      mbar_init(sm.empty + s, NCW);
+    }
+    mbar_fence_init();
+    *s_done = 0;
+  }
+  __syncthreads();
+
+  if (tid >= NCT) {
+    // ------------------------------------------------ producer warp ------------------------------------------------
+    if (tid != NCT) return;
+    const uint64_t policy = policy_evict_first();
+    long long item = 0;
+    const int firstb = blockIdx.x;
+    bool stop = false;
+    while (!stop) {
+      bool any = false;
+      for (int ph = 0; ph < 3 && !stop; ++ph) {
+        const FusedMat& M = (ph == 0) ? a.GT : (ph == 1) ? a.G : a.A;
+        const VT* Aval = reinterpret_cast<const VT*>(M.sval);
+        const CT* Acol = reinterpret_cast<const CT*>(M.scol);
+        const int n_items = (firstb < M.nblk) ? (M.nblk - firstb + G - 1) / G : 0;
+        for (int j = 0; j < n_items; ++j, ++item) {
+          any = true;
+          const int slot = (int)(item % STAGES);
+          if (item >= STAGES) {
+            const uint32_t par = (uint32_t)(((item / STAGES) - 1) & 1);
+            while (!mbar_try_wait(sm.empty + slot, par))
+              if (*s_done) {
+                stop = true;
+                break;
+              }
+            if (stop) break;
+          }
+          const int4 cur = __ldg(M.blk + firstb + (long long)j * G);
+          sm.hdr[slot] = cur;
+          const int r0 = cur.x, lo = cur.y, r1 = cur.z, hi = cur.w;
+          const int cnt = hi - lo;
+          if (cnt > CAP || cnt <= 0) {
+            mbar_arrive(sm.full + slot);
+            continue;
+          }
+          const int v_lo = lo & ~3;
+          const int vn = (hi - v_lo + 3) & ~3;
+          const int c_lo = lo & ~(CA - 1);
+          const int cn = (hi - c_lo + CA - 1) & ~(CA - 1);
+          const int ra = r0 & ~3;
+          const int nr4 = (r1 + 1 - ra + 3) & ~3;
+          mbar_arrive_expect_tx(sm.full + slot, (uint32_t)(vn * (int)sizeof(VT) + cn * (int)sizeof(CT) + nr4 * 4 * (DELTA ? 2 : 1)));
+          bulk_g2s(sm.vals + slot * C::VALS, Aval + v_lo, (uint32_t)(vn * sizeof(VT)), sm.full + slot, policy);
+          bulk_g2s(sm.cols + slot * C::COLS_BYTES, Acol + c_lo, (uint32_t)(cn * sizeof(CT)), sm.full + slot, policy);
+          bulk_g2s(sm.rptr + slot * C::RPTR, M.rowptr + ra, (uint32_t)nr4 * 4, sm.full + slot, policy);
+          if (DELTA) bulk_g2s(sm.first + slot * C::RPTR, M.rowfirst + ra, (uint32_t)nr4 * 4, sm.full + slot, policy);
+        }
+      }
+      if (!any) {  // a CTA without row blocks only takes part in the barriers
+        while (!*s_done) __nanosleep(200);
+        stop = true;
+      }
+    }
+    // copies issued ahead of a solve that ended must land before the CTA's shared memory goes away
+    for (long long k = (item > STAGES ? item - STAGES : 0); k < item; ++k)
+      mbar_wait(sm.full + (int)(k % STAGES), (uint32_t)((k / STAGES) & 1));
+    return;
+  }
+
+  // -------------------------------------------------- consumer warps --------------------------------------------------
+  const int n = a.n, off = a.off;
+  const int n_halo = off + a.hi_halo;
+  const bool lead = (blockIdx.x == 0 && tid == 0);
+  const long long gtid = (long long)blockIdx.x * NCT + tid, gstride = (long long)G * NCT;
+  PcgScalars* sc = a.sc;
+  const double rtol = sc->rtol;
+  const int max_iter = sc->max_iter;
+  unsigned long long gen = 0;
+  long long item = 0;
+  double t0, t1;
+  bool ok = true;
+
+  // (row-partitioned) nobody stores into a peer before every rank is inside this solve
+  if (a.peer.world > 1) ok = fused_barrier<NCW>(a, gen, FB_READY, 0.0, 0.0, false, red, t0, t1);
+
+  // ---- init: r = b (owned; boundary entries also into the neighbours' halos), x = 0, ||b||^2 ----
+  double acc = 0.0;
+  bool pushed = false;
+  if (ok) {
+    for (long long i = gtid; i < n; i += gstride) {
+      const double v = a.b[i];
+      a.r0[off + i] = v;
+      a.x[i] = 0.0;
+      acc += v * v;
+      for (int s = 0; s < a.peer.n_push; ++s)
+        if (i >= a.peer.push_lo[s] && i < a.peer.push_hi[s]) {
+          a.peer.push_r[s][i - a.peer.push_lo[s]] = v;
+          pushed = true;
+        }
+    }
+    ok = fused_barrier<NCW>(a, gen, FB_INIT, acc, 0.0, pushed, red, t0, t1);
+  }
+  const double bb = t0;
+  const double bnorm = sqrt(bb);
+  const double atol = fmax(0.0, rtol * bnorm);
+  double rr = bb, rho = 0.0, rho_prev = 0.0, pq = 0.0, alpha = 0.0, beta = 0.0;
+  int iter = 0, done = 0, converged = 0, breakdown = 0;
+  if (!ok) {
+    done = 1;
+    breakdown = 3;
+  } else {
+    if (lead) a.hist[0] = bnorm;
+    if (bnorm == 0.0) {
+      done = 1;
+      converged = 1;
+    } else if (!(bnorm == bnorm)) {
+      done = 1;
+      breakdown = 1;
+    }
+  }
+  double *r = a.r0, *rn = a.r1, *p = a.p0, *pn = a.p1;
+  bool pending = false;
+  const bool prof = lead && a.prof != nullptr;
+  unsigned long long ns_prev = prof ? global_ns() : 0ull, ns_p[3] = {0ull, 0ull, 0ull};
+  auto stamp = [&](int k) {
+    if (prof) {
+      const unsigned long long now = global_ns();
+      ns_p[k] += now - ns_prev;
+      ns_prev = now;
+    }
+  };
+
+  while (!done) {
+    // ---- P1 ----
+    acc = 0.0;
+    pushed = false;
+    if (pending) {
+      // halo entries of r': same two roundings as the owner's (never sent)
+      for (long long h = gtid; h < n_halo; h += gstride) {
+        const long long e = h < off ? h : (long long)n + h;
+        rn[e] = __dsub_rn(ld_coh(r + e), __dmul_rn(alpha, ld_coh(a.q + e)));
+      }
+      fused_sweep<1, true, CAP, STAGES, NCW, VT, CT>(a, a.GT, sm, item, r, rn, p, pn, alpha, beta, acc, pushed);
+      double* tmp = r;
+      r = rn;
+      rn = tmp;
+    } else {
+      fused_sweep<1, false, CAP, STAGES, NCW, VT, CT>(a, a.GT, sm, item, r, rn, p, pn, alpha, beta, acc, pushed);
+    }
+    ok = fused_barrier<NCW>(a, gen, FB_RR, acc, 0.0, pushed, red, t0, t1);
+    stamp(0);
+    if (!ok) {
+      breakdown = 3;
+      break;
+    }
+    if (pending) {  // the update is complete: count it, test it (scipy: callback, then the test at the loop top)
+      if (!(t0 == t0)) {
+        breakdown = 1;
+        break;
+      }
+      rr = t0;
+      rho_prev = rho;
+      iter += 1;
+      const double nrm = sqrt(t0);
+      if (lead) a.hist[iter] = nrm;
+      if (nrm < atol) {
+        converged = 1;
+        break;
+      }
+      if (iter >= max_iter) break;
+    }
+    // ---- P2 ----
+    acc = 0.0;
+    pushed = false;
+    fused_sweep<2, false, CAP, STAGES, NCW, VT, CT>(a, a.G, sm, item, r, rn, p, pn, alpha, beta, acc, pushed);
+    ok = fused_barrier<NCW>(a, gen, FB_RHO, acc, 0.0, pushed, red, t0, t1);
+    stamp(1);
+    if (!ok) {
+      breakdown = 3;
+      break;
+    }
+    rho = t0;
+    const bool first = (iter == 0);
+    beta = first ? 0.0 : rho / rho_prev;
+    // ---- P3 ----
+    acc = 0.0;
+    pushed = false;
+    if (first) {
+      for (long long h = gtid; h < n_halo; h += gstride) {
+        const long long e = h < off ? h : (long long)n + h;
+        pn[e] = ld_coh(a.z + e);
+      }
+      fused_sweep<3, true, CAP, STAGES, NCW, VT, CT>(a, a.A, sm, item, r, rn, p, pn, alpha, beta, acc, pushed);
+    } else {
+      for (long long h = gtid; h < n_halo; h += gstride) {
+        const long long e = h < off ? h : (long long)n + h;
+        pn[e] = __dadd_rn(__dmul_rn(ld_coh(p + e), beta), ld_coh(a.z + e));
+      }
+      fused_sweep<3, false, CAP, STAGES, NCW, VT, CT>(a, a.A, sm, item, r, rn, p, pn, alpha, beta, acc, pushed);
+    }
+    {
+      double* tmp = p;
+      p = pn;
+      pn = tmp;
+    }
+    ok = fused_barrier<NCW>(a, gen, FB_PQ, acc, 0.0, pushed, red, t0, t1);
+    stamp(2);
+    if (!ok) {
+      breakdown = 3;
+      break;
+    }
+    pq = t0;
+    if (!(pq > 0.0) || !(rho == rho)) {  // p.q <= 0 or NaN: A or M not SPD
+      breakdown = 1;
+      alpha = 0.0;
+      break;
+    }
+    alpha = rho / pq;
+    pending = true;
+  }
+
+  if (tid == 0) *s_done = 1;  // the producer stops prefetching and drains
+  if (prof) {
+    a.prof[0] = ns_p[0];
+    a.prof[1] = ns_p[1];
+    a.prof[2] = ns_p[2];
+    a.prof[3] = (unsigned long long)iter;
+  }
+  if (lead) {
+    sc->bnorm = bnorm;
+    sc->atol = atol;
+    sc->rr = rr;
+    sc->rho = rho;
+    sc->rho_prev = rho_prev;
+    sc->pq = pq;
+    sc->alpha = alpha;
+    sc->beta = beta;
+    sc->iter = iter;
+    sc->done = 1;
+    sc->converged = converged;
+    sc->breakdown = breakdown;
+  }
+}
+
+// host side (pcg_fused.cu)
+struct FusedPlan {
+  int which = -1;   // partition index (1: 2048-entry stages, 2: 4096)
+  int fmt = 0;      // bit 0: fp32 values, bit 1: 16-bit column steps
+  int grid = 0;     // co-resident CTAs
+  int threads = 0;
+};
+// Builds the lazily created pieces of the three matrices and decides whether the fused kernel applies
+// (plan->which < 0: not eligible -- the caller falls back to the launch-per-kernel drivers).  Synchronises `st`.
+int fused_plan(b200spai_csr_s* A, b200spai_csr_s* G, b200spai_csr_s* GT, cudaStream_t st, FusedPlan* plan);
+FusedMat fused_mat(const b200spai_csr_s* M, const FusedPlan& plan);
+int fused_launch(const FusedArgs& args, const FusedPlan& plan, cudaStream_t st);
+
+}  // namespace b200spai

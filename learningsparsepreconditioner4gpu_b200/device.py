@@ -200,6 +200,13 @@ class DevicePCG:
                                                              int(iterations), ms, _stream()), "pcg_profile_iterations")
         return [float(v) for v in ms]
 
+    def fused_profile(self):
+        """Mode 4, after a solve: ([ms in sweep G^T, sweep G, sweep A] incl. their barriers, iterations covered)."""
+        ms = (C.c_double * 3)()
+        it = C.c_int32()
+        _lib.check(self._lib.b200spai_pcg_fused_profile(self._h, ms, C.byref(it), _stream()), "pcg_fused_profile")
+        return [float(v) for v in ms], it.value
+
     @property
     def launches(self) -> int:
         v = C.c_int64()

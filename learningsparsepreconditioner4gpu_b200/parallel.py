@@ -16,6 +16,7 @@ Host-side pieces (pure index arithmetic, testable on CPU):
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional, Sequence, Tuple
 
 import torch
@@ -172,6 +173,19 @@ class DistPCG:
             GT.close()
         _lib.check(self._lib.b200spai_dist_pcg_setup(self._h, self.A._h, self.G._h if self.G else None,
                                                      self.GT._h if self.GT else None, float(epsilon)), "dist_pcg_setup")
+        # mode 4 (one persistent kernel per rank, halo + all-reduce inside its grid barriers) must be taken by ALL ranks
+        # or by none: every rank asks the library whether its own matrices qualify and the answers are and-ed
+        if self.G is not None and mode in (0, 4) and not os.environ.get("B200SPAI_NO_FUSED"):
+            ok = C.c_int32()
+            _lib.check(self._lib.b200spai_dist_pcg_fused_ok(self._h, _stream(), C.byref(ok)), "dist_pcg_fused_ok")
+            oks = [ok.value] if self.world == 1 else _all_gather_object(int(ok.value), group)
+            if all(v == 2 for v in oks) or (mode == 4 and all(oks)):   # auto: only in the streaming regime (large systems)
+                mode = 4
+            elif mode == 4:
+                raise _lib.B200SpaiError(f"DistPCG: mode 4 requested but ranks {[i for i, v in enumerate(oks) if not v]} cannot run it")
+        elif mode == 4:
+            raise _lib.B200SpaiError("DistPCG: mode 4 needs G (ext_spai) and B200SPAI_NO_FUSED unset")
+        self.mode = mode
         if mode:
             _lib.check(self._lib.b200spai_dist_pcg_set_mode(self._h, mode), "dist_pcg_set_mode")
         self.group = group
@@ -210,6 +224,13 @@ class DistPCG:
         _lib.check(self._lib.b200spai_dist_pcg_profile_iterations(self._h, PRECOND[precond], _ptr(b_local.contiguous()), _ptr(x),
                                                                   int(iterations), out, _stream()), "dist_pcg_profile_iterations")
         return {k: round(float(v), 5) for k, v in zip(self.PROFILE_KEYS, out)}
+
+    def fused_profile(self):
+        """Mode 4, after a solve: ([ms in sweep G^T, sweep G, sweep A] incl. their barriers, iterations covered), this rank."""
+        ms = (C.c_double * 3)()
+        it = C.c_int32()
+        _lib.check(self._lib.b200spai_dist_pcg_fused_profile(self._h, ms, C.byref(it), _stream()), "dist_pcg_fused_profile")
+        return [float(v) for v in ms], it.value
 
     def gather(self, x_local: torch.Tensor) -> torch.Tensor:
         """The full solution vector on every rank (plumbing for checks; NCCL all_gather of ragged pieces)."""

@@ -38,7 +38,9 @@ def main():
     ext = par.extended_range(sample.edge_index, rs, re)
     out = {"rank": rank, "world": world, "grid": grid, "rows": [rs, re], "ext": list(ext)}
     for precond in ("ext_spai", "none", "diagonal"):
-        solver = par.DistPCG(A, G if precond == "ext_spai" else None, ws.epsilon, starts, ext, mode=mode, reuse=True)
+        spai = precond == "ext_spai"
+        solver = par.DistPCG(A, G if spai else None, ws.epsilon, starts, ext, mode=mode if (spai or mode != 4) else 0, reuse=True)
+        assert solver.mode == mode or not spai
         x_loc, res, hist = solver.solve(rhs[rs:re].contiguous(), precond, rtol=1e-8, history=True)
         x = solver.gather(x_loc)
         iters = [None] * world
@@ -50,6 +52,7 @@ def main():
         if precond == "ext_spai":
             ref.set_spai(G, ws.epsilon)
         x1, res1, hist1 = ref.solve(rhs, precond, rtol=1e-8, history=True)
+        assert res.reserved == (mode or 2) or not spai, (res.reserved, mode)
         assert abs(res.iterations - res1.iterations) <= 1, (precond, res.iterations, res1.iterations)
         k = min(6, len(hist), len(hist1))
         assert torch.allclose(hist[:k], hist1[:k], rtol=1e-10, atol=0), (hist[:k], hist1[:k])
