@@ -33,6 +33,7 @@ if ROOT not in sys.path:
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
+FUSED_PHASES = ("GT_r+barrier", "G_t+barrier", "update_p+barrier", "A_p+barrier", "update_xr+barrier")
 METRIC = "learned-SPAI PCG solves/s to rtol 1e-6 (GNN->G, assembly, PCG; time-to-1e-6 in extra keys)"
 UNIT = "solves/s"
 # PCG iterations of the default workload at rtol 1e-6, measured by the CUDA path (iteration parity with the oracle
@@ -244,7 +245,7 @@ def main_ours(args):
     if pcg_mode == 4:
         fp_ms, fp_it = solver.fused_profile()
         fused_phases = {"iterations": fp_it, "ms_per_iteration": {k: round(v / max(fp_it, 1), 4) for k, v in
-                                                                  zip(("sweep_GT+barrier", "sweep_G+barrier", "sweep_A+barrier"), fp_ms)}}
+                                                                  zip(FUSED_PHASES, fp_ms)}}
     # ---- per-kernel times of the PCG iteration (roofline), on the last step's matrices ----------------------
     kms = solver.profile_iterations(rhs, "ext_spai", iterations=20)
     nnzA, nnzG, n = A.nnz, G.nnz, N * ws.block_size

@@ -122,18 +122,19 @@ int b200spai_pcg_create(b200spai_csr_t a, b200spai_pcg_t* out);
 /* Attach G (the `ext_spai=(spai, epsilon)` argument, validate.py:117).  G^T is built on the device.
  * The solver keeps references to g (must outlive it) and owns G^T. */
 int b200spai_pcg_set_spai(b200spai_pcg_t s, b200spai_csr_t g, double epsilon, void* stream);
-/* mode: 0 = auto (3 for systems of <= 131072 rows; above that 4 for the SPAI preconditioners when A, G and G^T share
- * one stream format, else 2; B200SPAI_PCG_MODE=1 forces 1, B200SPAI_NO_FUSED=1 keeps 4 out of the auto choice),
- * 1 = stream-enqueued kernels with a device-side done flag polled every few iterations, 2 = one CUDA graph with a
- * device-driven WHILE node (no host involvement at all), 3 = the whole solve in ONE cooperative kernel with 2-3 grid
- * barriers per iteration (small systems, thread per row), 4 = the whole solve in ONE persistent kernel of three
- * TMA-staged matrix sweeps per iteration with the vector updates folded into the sweeps (large systems,
- * csrc/pcg_fused.cuh).  b200spai_pcg_result.reserved reports the mode that ran. */
+/* mode: 0 = auto (3 for systems of <= 131072 rows, else 2; B200SPAI_PCG_MODE=1 forces 1, B200SPAI_PCG_MODE=4 makes
+ * the auto choice for large SPAI solves 4 when it applies), 1 = stream-enqueued kernels with a device-side done flag
+ * polled every few iterations, 2 = one CUDA graph with a device-driven WHILE node (no host involvement at all),
+ * 3 = the whole solve in ONE cooperative kernel with 2-3 grid barriers per iteration (small systems, thread per row),
+ * 4 = the whole solve in ONE persistent kernel: three TMA-staged matrix sweeps and two vector phases per iteration
+ * separated by grid barriers, the stream producer running ahead across sweeps (large systems with a SPAI
+ * preconditioner whose A, G and G^T share one stream format; csrc/pcg_fused.cuh; the row-partitioned solver's default).
+ * b200spai_pcg_result.reserved reports the mode that ran. */
 int b200spai_pcg_set_mode(b200spai_pcg_t s, int mode);
-/* Mode 4 only, after a solve: milliseconds the last solve spent in each of its three sweeps including the grid barrier
- * that closes it ({t = G^T r' (+ x, r update), z = G t + eps r', q = A p' (+ p update)}; CTA 0's view, %globaltimer)
- * and the number of iterations they cover. */
-int b200spai_pcg_fused_profile(b200spai_pcg_t s, double* phase_ms3, int32_t* iterations, void* stream);
+/* Mode 4 only, after a solve: milliseconds the last solve spent in each of its five phases including the barrier that
+ * closes it ({t = G^T r, z = G t + eps r, p update, q = A p, x / r update}; CTA 0's view, %globaltimer) and the number
+ * of iterations they cover. */
+int b200spai_pcg_fused_profile(b200spai_pcg_t s, double* phase_ms5, int32_t* iterations, void* stream);
 /* Solve A x = b.  x_dev is overwritten (x0 = 0).  resid_hist_dev: NULL or max_iter+1 doubles
  * receiving ||r_k|| (k = 0..iterations).  max_iter <= 0 means n (validate.py:100-101). */
 int b200spai_pcg_solve_dev(b200spai_pcg_t s, int precond, const double* b_dev, double* x_dev, double rtol,
@@ -232,7 +233,7 @@ int b200spai_dist_pcg_set_mode(b200spai_dist_t d, int mode);
  * 2: they can and are in the streaming regime (nnz(A_local) >= 2^18) where the automatic choice takes mode 4. */
 int b200spai_dist_pcg_fused_ok(b200spai_dist_t d, void* stream, int32_t* ok);
 /* Mode 4, after a solve: as b200spai_pcg_fused_profile (this rank's view). */
-int b200spai_dist_pcg_fused_profile(b200spai_dist_t d, double* phase_ms3, int32_t* iterations, void* stream);
+int b200spai_dist_pcg_fused_profile(b200spai_dist_t d, double* phase_ms5, int32_t* iterations, void* stream);
 /* b / x: the owned rows only.  max_iter must be given (> 0).  resid_hist_dev: NULL or max_iter+1 doubles. */
 int b200spai_dist_pcg_solve(b200spai_dist_t d, int precond, const double* b_local_dev, double* x_local_dev, double rtol,
                             int32_t max_iter, double* resid_hist_dev, void* stream, b200spai_pcg_result* result);

@@ -58,6 +58,7 @@ __global__ void expand_rows_masked_kernel(const long long* __restrict__ col, con
   int w = FILL ? rowptr[i] : 0;
   for (int e = brp[r]; e < brp[r + 1]; ++e) {
     const long long cb = col[e];
+    if (cb < 0 || cb >= N) continue;  // out-of-range column: check_sorted_kernel has flagged it and the call fails; never index mask with it
     const float* blk = vals + ((long long)e * b + bi) * b;
     for (int bj = 0; bj < b; ++bj) {
       const long long j = cb * b + bj;
@@ -105,14 +106,25 @@ extern "C" int b200spai_edges_to_csr(int64_t num_nodes, int64_t num_edges, int32
   const long long* col = row + E;
   const int tb = 256;
 
-  int* bad = nullptr;
+  // temporaries are released on every return path (the B2_TRY / B2_CUDA macros return early)
+  struct Temps {
+    int *bad = nullptr, *brp = nullptr, *counts = nullptr;
+    void* tmp = nullptr;
+    ~Temps() {
+      dev_free(tmp);
+      dev_free(bad);
+      dev_free(brp);
+      dev_free(counts);
+    }
+  } T;
+  int*& bad = T.bad;
   B2_TRY(dev_alloc(&bad, 1));
   B2_CUDA(cudaMemsetAsync(bad, 0, sizeof(int), st));
   if (E > 0) check_sorted_kernel<<<(unsigned)((E + tb - 1) / tb), tb, 0, st>>>(row, col, E, N, bad);
-  int* brp = nullptr;
+  int*& brp = T.brp;
   B2_TRY(dev_alloc(&brp, (size_t)N + 1));
   block_rowptr_kernel<<<(unsigned)((N + 1 + tb - 1) / tb), tb, 0, st>>>(row, E, N, brp);
-  int* counts = nullptr;  // becomes the row pointer after the scan (n + 1 entries)
+  int*& counts = T.counts;  // becomes the row pointer after the scan (n + 1 entries)
   B2_TRY(dev_alloc(&counts, (size_t)n + 1));
   B2_CUDA(cudaMemsetAsync(counts, 0, ((size_t)n + 1) * sizeof(int), st));
   if (n > 0)
@@ -121,7 +133,7 @@ extern "C" int b200spai_edges_to_csr(int64_t num_nodes, int64_t num_edges, int32
   B2_LAUNCH_CHECK();
   size_t tmp_bytes = 0;
   B2_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, counts, counts, (int)(n + 1), st));
-  void* tmp = nullptr;
+  void*& tmp = T.tmp;
   B2_CUDA(pool_malloc(&tmp, tmp_bytes + 16));
   B2_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, counts, counts, (int)(n + 1), st));
   int h_bad = 0, h_nnz = 0;
@@ -149,10 +161,6 @@ extern "C" int b200spai_edges_to_csr(int64_t num_nodes, int64_t num_edges, int32
     }
   }
   count_launches(4);
-  dev_free(tmp);
-  dev_free(bad);
-  dev_free(brp);
-  dev_free(counts);
   if (!rc) *out = A;
   return rc;
 }

@@ -42,10 +42,15 @@ void count_launches(long long n);  // process-wide tally of this library's kerne
 
 // Device memory comes from a per-device caching pool (csr.cu): a solve step allocates and releases the same few
 // multi-GB blocks every time, and cudaMalloc / cudaFree of those cost ~100 ms per step (cudaFree also synchronises
-// the device).  Blocks are reused in the order of the ONE stream a handle works on (include/b200spai.h), which is what
-// makes handing a just-released block to the next allocation safe.  b200spai_pool_trim() returns cached blocks.
+// the device).  The pool is STREAM-AWARE: every block is tagged with the stream of the C-ABI call that allocated it
+// (as_stream() below records the calling thread's current stream) and a released block is handed only to a later
+// allocation made for the SAME stream -- stream order then guarantees that the kernels still queued on the block when
+// it was released (temporaries of csr_transpose / edges_to_csr are freed right after their kernels are enqueued) finish
+// before the new owner's work starts.  Handles of different host threads / streams (batch.BatchSolver) therefore never
+// recycle each other's in-flight blocks.  b200spai_pool_trim() returns cached blocks.
 cudaError_t pool_malloc(void** p, size_t bytes);
 void pool_free(void* p);
+void pool_note_stream(cudaStream_t s);  // the stream the calling thread's allocations belong to from now on
 
 template <typename T>
 inline int dev_alloc(T** p, size_t count) {
@@ -54,7 +59,11 @@ inline int dev_alloc(T** p, size_t count) {
 }
 inline void dev_free(void* p) { ::b200spai::pool_free(p); }
 
-static inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+static inline cudaStream_t as_stream(void* s) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(s);
+  pool_note_stream(st);
+  return st;
+}
 
 // ---------------------------------------------------------------------------------------------
 // device helpers

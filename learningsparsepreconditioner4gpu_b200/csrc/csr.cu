@@ -4,6 +4,7 @@
 #include <atomic>
 #include <cstdlib>
 #include <map>
+#include <tuple>
 #include <mutex>
 #include <unordered_map>
 #include <vector>
@@ -34,12 +35,20 @@ int sm_count() {
 
 // ---- caching device-memory pool ------------------------------------------------------------------------------
 namespace {
+struct LiveBlock {
+  size_t bytes;
+  int dev;
+  cudaStream_t stream;  // the stream of the call that allocated it: its kernels are ordered on this stream
+};
 struct Pool {
   std::mutex mu;
-  std::unordered_map<void*, std::pair<size_t, int>> live;            // ptr -> (bytes, device)
-  std::map<std::pair<int, size_t>, std::vector<void*>> free_blocks;  // (device, bytes) -> cached blocks
+  std::unordered_map<void*, LiveBlock> live;
+  // (device, bytes, stream) -> cached blocks.  A released block only goes back to an allocation for the SAME stream, so
+  // work still queued on it when it was released is ordered before the new owner's (see common.cuh).
+  std::map<std::tuple<int, size_t, cudaStream_t>, std::vector<void*>> free_blocks;
   size_t cached = 0, limit = 0;
 };
+thread_local cudaStream_t tls_stream = nullptr;
 Pool& pool() {
   static Pool* p = new Pool();  // leaked on purpose: handles may be destroyed after static destructors ran
   return *p;
@@ -64,20 +73,23 @@ size_t round_size(size_t bytes) {
 }
 }  // namespace
 
+void pool_note_stream(cudaStream_t s) { tls_stream = s; }
+
 cudaError_t pool_malloc(void** p, size_t bytes) {
   Pool& P = pool();
   bytes = round_size(bytes ? bytes : 1);
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
+  const cudaStream_t st = tls_stream;
   {
     std::lock_guard<std::mutex> lock(P.mu);
-    auto it = P.free_blocks.find({dev, bytes});
+    auto it = P.free_blocks.find(std::make_tuple(dev, bytes, st));
     if (it != P.free_blocks.end() && !it->second.empty()) {
       *p = it->second.back();
       it->second.pop_back();
       P.cached -= bytes;
-      P.live[*p] = {bytes, dev};
+      P.live[*p] = LiveBlock{bytes, dev, st};
       return cudaSuccess;
     }
   }
@@ -89,7 +101,7 @@ cudaError_t pool_malloc(void** p, size_t bytes) {
     if (e != cudaSuccess) return e;
   }
   std::lock_guard<std::mutex> lock(P.mu);
-  P.live[*p] = {bytes, dev};
+  P.live[*p] = LiveBlock{bytes, dev, st};
   return cudaSuccess;
 }
 
@@ -101,11 +113,11 @@ void pool_free(void* p) {
     std::lock_guard<std::mutex> lock(P.mu);
     auto it = P.live.find(p);
     if (it != P.live.end()) {
-      const size_t bytes = it->second.first;
-      const int dev = it->second.second;
+      const LiveBlock blk = it->second;
+      const size_t bytes = blk.bytes;
       P.live.erase(it);
       if (P.cached + bytes <= limit) {
-        P.free_blocks[{dev, bytes}].push_back(p);
+        P.free_blocks[std::make_tuple(blk.dev, bytes, blk.stream)].push_back(p);
         P.cached += bytes;
         return;
       }

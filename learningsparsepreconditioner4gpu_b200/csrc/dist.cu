@@ -268,9 +268,7 @@ struct b200spai_dist_s {
   int launches_per_iter[4] = {0, 0, 0, 0};
   int mode = 0;
   long long launches = 0;
-  // fused persistent kernel (mode 4): local second copies of r and p (extended), barrier block, plan
-  double *r1 = nullptr, *p1 = nullptr;
-  long long rp_cap = 0;
+  // fused persistent kernel (mode 4): barrier block, phase timers, epoch counters, plan
   FusedSync* fsync = nullptr;
   unsigned long long *fprof = nullptr, *fepoch = nullptr;
   FusedPlan fplan;
@@ -680,36 +678,27 @@ int b200spai_dist_pcg_fused_ok(b200spai_dist_t s, void* stream, int32_t* ok) {
   return 0;
 }
 
-int b200spai_dist_pcg_fused_profile(b200spai_dist_t s, double* phase_ms3, int32_t* iterations, void* stream) {
-  B2_ARG(s && phase_ms3, "dist_pcg_fused_profile: NULL argument");
+int b200spai_dist_pcg_fused_profile(b200spai_dist_t s, double* phase_ms5, int32_t* iterations, void* stream) {
+  B2_ARG(s && phase_ms5, "dist_pcg_fused_profile: NULL argument");
   B2_ARG(s->fprof, "dist_pcg_fused_profile: no fused solve has run on this handle");
-  unsigned long long h[4] = {0, 0, 0, 0};
+  unsigned long long h[6] = {0, 0, 0, 0, 0, 0};
   B2_CUDA(cudaMemcpyAsync(h, s->fprof, sizeof(h), cudaMemcpyDeviceToHost, as_stream(stream)));
   B2_CUDA(cudaStreamSynchronize(as_stream(stream)));
-  for (int k = 0; k < 3; ++k) phase_ms3[k] = (double)h[k] * 1e-6;
-  if (iterations) *iterations = (int32_t)h[3];
+  for (int k = 0; k < 5; ++k) phase_ms5[k] = (double)h[k] * 1e-6;
+  if (iterations) *iterations = (int32_t)h[5];
   return 0;
 }
 
 // Mode 4: the whole row-partitioned solve in ONE persistent kernel per rank (pcg_fused.cuh).
 static int dist_solve_fused(b200spai_dist_s* s, int precond, const double* b, double* x, cudaStream_t st) {
-  const long long ext = s->hi - s->shift;
-  if (ext + 2 > s->rp_cap) {
-    for (double** v : {&s->r1, &s->p1}) {
-      dev_free(*v);
-      *v = nullptr;
-      B2_TRY(dev_alloc(v, (size_t)ext + 2));
-    }
-    s->rp_cap = ext + 2;
-  }
   if (!s->fsync) B2_TRY(dev_alloc(&s->fsync, 1));
-  if (!s->fprof) B2_TRY(dev_alloc(&s->fprof, 4));
+  if (!s->fprof) B2_TRY(dev_alloc(&s->fprof, 6));
   if (!s->fepoch) {
     B2_TRY(dev_alloc(&s->fepoch, FB_KINDS));
     B2_CUDA(cudaMemsetAsync(s->fepoch, 0, FB_KINDS * sizeof(unsigned long long), st));
   }
   B2_CUDA(cudaMemsetAsync(s->fsync, 0, sizeof(FusedSync), st));
-  B2_CUDA(cudaMemsetAsync(s->fprof, 0, 4 * sizeof(unsigned long long), st));
+  B2_CUDA(cudaMemsetAsync(s->fprof, 0, 6 * sizeof(unsigned long long), st));
   FusedArgs a{};
   a.A = fused_mat(s->A, s->fplan);
   a.G = fused_mat(s->G, s->fplan);
@@ -719,10 +708,8 @@ static int dist_solve_fused(b200spai_dist_s* s, int precond, const double* b, do
   a.hi_halo = (int)(s->hi - s->re);
   a.b = b;
   a.x = x;
-  a.r0 = s->vec(V_R);
-  a.r1 = s->r1;
-  a.p0 = s->vec(V_P);
-  a.p1 = s->p1;
+  a.r = s->vec(V_R);
+  a.p = s->vec(V_P);
   a.z = s->vec(V_Z);
   a.q = s->vec(V_Q);
   a.t = s->vec(V_T);
@@ -960,7 +947,7 @@ int b200spai_dist_destroy(b200spai_dist_t s) {
   for (int q = 0; q < s->world; ++q)
     if (q != s->rank && s->peer_seg[q]) cudaIpcCloseMemHandle(s->peer_seg[q]);
   cudaFree(s->seg);
-  for (double* v : {s->xw, s->bw, s->d, s->partials, s->hist, s->r1, s->p1}) dev_free(v);
+  for (double* v : {s->xw, s->bw, s->d, s->partials, s->hist}) dev_free(v);
   dev_free(s->sc);
   dev_free(s->fsync);
   dev_free(s->fprof);

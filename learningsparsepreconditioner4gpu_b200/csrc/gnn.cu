@@ -326,7 +326,10 @@ int b200spai_gnn_create(int32_t node_in, int32_t edge_in, int32_t block_size, in
     delete m;
     return B200SPAI_ERR_CUDA;
   }
-  cudaError_t e = cudaMemcpy(m->blob, blob_host, (size_t)blob_len * sizeof(float), cudaMemcpyHostToDevice);
+  // pageable H2D copy on the legacy stream: it may return once the data is staged, and the forward kernels run on
+  // non-blocking streams that do not order with the legacy stream -- wait for the copy itself
+  cudaError_t e = cudaMemcpyAsync(m->blob, blob_host, (size_t)blob_len * sizeof(float), cudaMemcpyHostToDevice, cudaStreamLegacy);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(cudaStreamLegacy);
   if (e != cudaSuccess) {
     set_error(std::string("gnn_create: ") + cudaGetErrorString(e));
     dev_free(m->blob);

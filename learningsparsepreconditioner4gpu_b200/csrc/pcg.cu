@@ -363,9 +363,9 @@ static int fused_plan_for(b200spai_pcg_s* s, cudaStream_t st) {
 
 static int solve_fused(b200spai_pcg_s* s, int precond, const double* b, double* x, cudaStream_t st) {
   if (!s->fsync) B2_TRY(dev_alloc(&s->fsync, 1));
-  if (!s->fprof) B2_TRY(dev_alloc(&s->fprof, 4));
+  if (!s->fprof) B2_TRY(dev_alloc(&s->fprof, 6));
   B2_CUDA(cudaMemsetAsync(s->fsync, 0, sizeof(FusedSync), st));
-  B2_CUDA(cudaMemsetAsync(s->fprof, 0, 4 * sizeof(unsigned long long), st));
+  B2_CUDA(cudaMemsetAsync(s->fprof, 0, 6 * sizeof(unsigned long long), st));
   FusedArgs a{};
   a.A = fused_mat(s->A, s->fplan);
   a.G = fused_mat(s->G, s->fplan);
@@ -375,10 +375,8 @@ static int solve_fused(b200spai_pcg_s* s, int precond, const double* b, double* 
   a.hi_halo = 0;
   a.b = b;
   a.x = x;
-  a.r0 = s->r;
-  a.r1 = s->bw;
-  a.p0 = s->p;
-  a.p1 = s->xw;
+  a.r = s->r;
+  a.p = s->p;
   a.z = s->z;
   a.q = s->q;
   a.t = s->t;
@@ -415,7 +413,10 @@ static int solve_impl(b200spai_pcg_s* s, int precond, const double* b, double* x
   const int sgrid = (mode == 0 || mode == 3) ? small_grid(s) : 0;
   if (mode == 3) B2_ARG(sgrid > 0, "pcg_solve: mode 3 (single cooperative kernel) needs a system of <= 131072 rows");
   if (mode == 0) mode = (sgrid > 0 && !getenv("B200SPAI_NO_SMALL") && default_mode() == 2) ? 3 : default_mode();
-  if ((mode == 2 && s->mode == 0) || mode == 4) {  // auto: large SPAI solves take the fused persistent kernel when it applies
+  // auto takes the fused persistent kernel for large SPAI solves only when B200SPAI_PCG_MODE=4 asks for it: on ONE GPU
+  // it runs the same sweeps as the graph driver, whose launch gaps are already < 1 % of an iteration at these sizes
+  static const bool auto_fused = [] { const char* e = getenv("B200SPAI_PCG_MODE"); return e && atoi(e) == 4; }();
+  if ((mode == 2 && s->mode == 0 && auto_fused) || mode == 4) {
     bool fused = false;
     if (precond >= B200SPAI_PRECOND_EXT_SPAI) {
       B2_TRY(fused_plan_for(s, st));
@@ -669,14 +670,14 @@ int b200spai_pcg_profile_iterations(b200spai_pcg_t s, int precond, const double*
   return 0;
 }
 
-int b200spai_pcg_fused_profile(b200spai_pcg_t s, double* phase_ms3, int32_t* iterations, void* stream) {
-  B2_ARG(s && phase_ms3, "pcg_fused_profile: NULL argument");
+int b200spai_pcg_fused_profile(b200spai_pcg_t s, double* phase_ms5, int32_t* iterations, void* stream) {
+  B2_ARG(s && phase_ms5, "pcg_fused_profile: NULL argument");
   B2_ARG(s->fprof, "pcg_fused_profile: no fused solve has run on this handle");
-  unsigned long long h[4] = {0, 0, 0, 0};
+  unsigned long long h[6] = {0, 0, 0, 0, 0, 0};
   B2_CUDA(cudaMemcpyAsync(h, s->fprof, sizeof(h), cudaMemcpyDeviceToHost, as_stream(stream)));
   B2_CUDA(cudaStreamSynchronize(as_stream(stream)));
-  for (int k = 0; k < 3; ++k) phase_ms3[k] = (double)h[k] * 1e-6;
-  if (iterations) *iterations = (int32_t)h[3];
+  for (int k = 0; k < 5; ++k) phase_ms5[k] = (double)h[k] * 1e-6;
+  if (iterations) *iterations = (int32_t)h[5];
   return 0;
 }
 

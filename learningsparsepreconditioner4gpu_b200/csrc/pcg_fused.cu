@@ -8,11 +8,11 @@ namespace {
 constexpr int F_STAGES = 2;
 constexpr int F_NCW = 8;
 
-template <int CAP, typename VT, typename CT>
+template <int CAP, typename VT, typename CT, int MINB>
 struct Inst {
   static constexpr int threads = (F_NCW + 1) * 32;
   static int smem() { return StreamCfg<CAP, VT, CT>::smem_bytes(F_STAGES) + 64; }
-  static const void* fn() { return (const void*)pcg_fused_kernel<CAP, F_STAGES, F_NCW, VT, CT>; }
+  static const void* fn() { return (const void*)pcg_fused_kernel<CAP, F_STAGES, F_NCW, VT, CT, MINB>; }
   static int grid(int* out) {
     static int cached[64] = {0};
     int dev = 0;
@@ -36,23 +36,33 @@ struct Inst {
   }
 };
 
-template <int CAP>
+template <int CAP, int MINB>
 int grid_for(int fmt, int* out) {
   switch (fmt) {
-    case 3: return Inst<CAP, float, unsigned short>::grid(out);
-    case 1: return Inst<CAP, float, int>::grid(out);
-    case 2: return Inst<CAP, double, unsigned short>::grid(out);
-    default: return Inst<CAP, double, int>::grid(out);
+    case 3: return Inst<CAP, float, unsigned short, MINB>::grid(out);
+    case 1: return Inst<CAP, float, int, MINB>::grid(out);
+    case 2: return Inst<CAP, double, unsigned short, MINB>::grid(out);
+    default: return Inst<CAP, double, int, MINB>::grid(out);
   }
 }
-template <int CAP>
+template <int CAP, int MINB>
 int launch_for(int fmt, const FusedArgs& a, int grid, cudaStream_t st) {
   switch (fmt) {
-    case 3: return Inst<CAP, float, unsigned short>::launch(a, grid, st);
-    case 1: return Inst<CAP, float, int>::launch(a, grid, st);
-    case 2: return Inst<CAP, double, unsigned short>::launch(a, grid, st);
-    default: return Inst<CAP, double, int>::launch(a, grid, st);
+    case 3: return Inst<CAP, float, unsigned short, MINB>::launch(a, grid, st);
+    case 1: return Inst<CAP, float, int, MINB>::launch(a, grid, st);
+    case 2: return Inst<CAP, double, unsigned short, MINB>::launch(a, grid, st);
+    default: return Inst<CAP, double, int, MINB>::launch(a, grid, st);
   }
+}
+
+// development switch: B200SPAI_FUSED_MINB=3 selects the 72-register variant (3 CTAs per SM)
+int fused_minb() {
+  static int v = 0;
+  if (v == 0) {
+    const char* e = getenv("B200SPAI_FUSED_MINB");
+    v = (e && atoi(e) == 3) ? 3 : 4;
+  }
+  return v;
 }
 
 bool fused_disabled() {
@@ -88,8 +98,10 @@ int fused_plan(b200spai_csr_s* A, b200spai_csr_s* G, b200spai_csr_s* GT, cudaStr
     if (m->f32_state != f32 || m->c16_state != c16) return 0;
   const int fmt = (f32 == 1 ? 1 : 0) | (c16 == 1 ? 2 : 0);
   int grid = 0;
-  if (which == 2) B2_TRY(grid_for<4096>(fmt, &grid));
-  else B2_TRY(grid_for<2048>(fmt, &grid));
+  const int minb = fused_minb();
+  if (which == 2) B2_TRY((minb == 3 ? grid_for<4096, 3> : grid_for<4096, 4>)(fmt, &grid));
+  else B2_TRY((minb == 3 ? grid_for<2048, 3> : grid_for<2048, 4>)(fmt, &grid));
+  plan->minb = minb;
   if (grid <= 0 || 2 * grid > MAX_PARTIALS) return 0;
   plan->which = which;
   plan->fmt = fmt;
@@ -112,8 +124,8 @@ FusedMat fused_mat(const b200spai_csr_s* M, const FusedPlan& plan) {
 }
 
 int fused_launch(const FusedArgs& args, const FusedPlan& plan, cudaStream_t st) {
-  if (plan.which == 2) return launch_for<4096>(plan.fmt, args, plan.grid, st);
-  return launch_for<2048>(plan.fmt, args, plan.grid, st);
+  if (plan.which == 2) return (plan.minb == 3 ? launch_for<4096, 3> : launch_for<4096, 4>)(plan.fmt, args, plan.grid, st);
+  return (plan.minb == 3 ? launch_for<2048, 3> : launch_for<2048, 4>)(plan.fmt, args, plan.grid, st);
 }
 
 }  // namespace b200spai

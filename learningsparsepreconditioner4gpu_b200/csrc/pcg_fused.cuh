@@ -1,28 +1,35 @@
 // Whole PCG solve of a LARGE system in ONE persistent kernel (driver "mode 4"), single GPU or row-partitioned over the
 // GPUs of an NVSwitch box.  It replaces the 5-launch iteration of pcg.cu / the 8-launch iteration of dist.cu:
 //
-//   P1   [x += alpha p ; r' = r - alpha q ; ||r'||^2]  and  t = G^T r'  [/ d]
-//        r' of a NEIGHBOUR row is recomputed inside the gather from (r, q) with the two roundings its owner uses
-//   --- grid barrier B1: ||r'||^2 -> iteration count, history, convergence / max_iter test (scipy cg order) ---
-//   P2   z = G t + eps r' [/ d] ; rho = r'.z
-//   --- grid barrier B2: rho -> beta ---
-//   P3   p' = z + beta p  and  q = A p'  (p' of a neighbour column recomputed from (z, p)) ; p'.q
-//   --- grid barrier B3: p'.q -> alpha (breakdown if <= 0) ---
+//   P1   t = G^T r [/ d]                                    (matrix sweep, gathers r)
+//   --- barrier B1 (cross-rank): ||r||^2 of the update made at the end of the previous iteration -> iteration count,
+//       history, convergence / max_iter test (the sweep that ran ahead of a converged test only wrote t)
+//   P2   z = G t + eps r [/ d] ; rho = r.z                  (matrix sweep, gathers t)
+//   --- barrier B2 (cross-rank): rho -> beta
+//   V2   p = z + beta p                                     (vector phase, owned rows + halo)
+//   --- local grid barrier
+//   P3   q = A p ; p.q                                      (matrix sweep, gathers p)
+//   --- barrier B3 (cross-rank): p.q -> alpha (breakdown if <= 0)
+//   V1   x += alpha p ; r -= alpha q ; ||r||^2              (vector phase, owned rows + halo of r)
+//   --- local grid barrier
 //
-// so the two pure vector passes of the 5-kernel iteration (72 n bytes) disappear into the SpMV prologues, an iteration
-// is 3 matrix sweeps, and nothing is launched, captured or polled by the host while the solve runs.
+// Nothing is launched, captured or polled by the host while the solve runs.  (A first version folded V1 and V2 into
+// the sweeps by recomputing r' = r - alpha q and p' = z + beta p inside the gathers: two gathers per matrix entry made
+// the sweeps 30-90 % slower than the vector phases they saved -- measured 1.07 vs 0.84 ms per iteration at 216^3 -- so
+// the updates are separate phases again; at 8 ranks the vectors of a rank live in L2 and these phases cost ~10 us.)
 //
 // Each sweep is the TMA-staged streaming SpMV of spmv.cuh (row blocks staged by one producer lane with cp.async.bulk +
 // mbarrier, consumer warps row-parallel out of shared memory, lossless fp32-value / 16-bit-column-step streams, row
 // sums in scipy's sequential rounded order).  The matrices never change, so the producer simply runs ahead through the
 // cyclic schedule G^T, G, A, G^T, ... : the first blocks of the next sweep are already in shared memory while the CTA
-// waits at a barrier (no pipeline ramp per sweep, no launch tail).
+// waits at a barrier or runs a vector phase (no pipeline ramp per sweep, no launch tail).
 //
-// Grid barrier = monotonic arrive counter + release word in global memory (cooperative launch guarantees
+// Cross-rank barrier = monotonic arrive counter + release word in global memory (cooperative launch guarantees
 // co-residency).  Every CTA deposits its two partial sums before arriving; warp 0 of CTA 0 sums them in CTA order
 // (deterministic), and all CTAs read the totals that travel with the release -> identical scalars and identical
 // branches everywhere.  Gathered vectors are read with plain ld.global (L1-cached); the acquire that ends every barrier
 // invalidates L1, which is what makes re-reading vectors other SMs rewrote legal (ld.global.nc would not be).
+// The local barrier is the same counter scheme without values or master.
 //
 // Row-partitioned (world > 1): every rank runs this kernel on its own rows.  The thread that computes an owned BOUNDARY
 // entry of t, z or q also stores it straight into the neighbours' extended vectors (peer stores over NVLink, "dual
@@ -30,20 +37,14 @@
 // peer-mapped exchange block (value + epoch per (barrier kind, source rank), summed in RANK order -> identical bits on
 // all ranks) before it releases the local grid.  The release/acquire chain (peer store -> fence.sys -> arrive ->
 // master acquire -> st.release.sys epoch -> peer's acquire -> peer's release of its grid) also orders the halo data,
-// so one barrier = halo exchange + all-reduce + grid sync.  Halo entries of r' and p' are recomputed locally from the
-// halo of (r, q) and (z, p): they carry the bits their owner computes and are never sent.
+// so one barrier = halo exchange + all-reduce + grid sync.  Halo entries of r and p are updated locally by the vector
+// phases from the halos of q and z: they carry the bits their owner computes and are never sent.
 #pragma once
 #include "pcg_kernels.cuh"
 
 namespace b200spai {
 
 constexpr int FUSED_MAXR = 16;
-#ifndef FUSED_U2
-#define FUSED_U2 8
-#endif
-#ifndef FUSED_MINB
-#define FUSED_MINB 3
-#endif
 enum { FB_INIT = 0, FB_RR = 1, FB_RHO = 2, FB_PQ = 3, FB_READY = 4, FB_KINDS = 5 };
 
 struct FusedMat {
@@ -62,6 +63,8 @@ struct FusedSync {  // one per solver, zeroed before every launch
   unsigned long long pad0[15];
   unsigned long long release;
   unsigned long long pad1[15];
+  unsigned long long light;  // arrive counter of the value-less local barrier
+  unsigned long long pad2[15];
   double bcast[2][4];  // [generation & 1][total0, total1, ok, -]
 };
 
@@ -88,7 +91,7 @@ struct FusedArgs {
   int hi_halo;           // extended entries behind the owned slice
   const double* b;       // [n]
   double* x;             // [n]
-  double *r0, *r1, *p0, *p1, *z, *q, *t;  // EXTENDED vectors (index 0 = first low halo entry)
+  double *r, *p, *z, *q, *t;  // EXTENDED vectors (index 0 = first low halo entry)
   const double* d;       // [n] diagonal (scaled SPAI) or nullptr
   double eps;
   int precond;
@@ -97,7 +100,7 @@ struct FusedArgs {
   double* hist;
   FusedSync* sync;
   long long spin_limit;  // clock64 ticks before a wait gives up
-  unsigned long long* prof;  // optional [4]: ns spent in P1+B1, P2+B2, P3+B3 (CTA 0's view), number of iterations
+  unsigned long long* prof;  // optional [6]: ns in P1+B1, P2+B2, V2+barrier, P3+B3, V1+barrier (CTA 0's view), iterations
   FusedPeer peer;
 };
 
@@ -265,12 +268,35 @@ struct FusedSmem {
   uint64_t *full, *empty;
 };
 
-// One matrix sweep by the consumer threads: blocks first, first + G, ... of M.  PH = 1 (G^T), 2 (G), 3 (A).
-// FLAG: PH 1 -> an (alpha, p, q) update is pending; PH 3 -> first iteration (p' = z).
-template <int PH, bool FLAG, int CAP, int STAGES, int NCW, typename VT, typename CT>
+// Value-less local grid barrier (consumer threads of every CTA).  Returns false on timeout.
+template <int NCW>
+__device__ __forceinline__ bool fused_light_barrier(const FusedArgs& a, unsigned long long& lgen, double* red) {
+  constexpr int NCT = NCW * 32;
+  lgen += 1;
+  bar_consumers<NCT>();
+  if (threadIdx.x == 0) {
+    red_release_gpu_add_u64(&a.sync->light, 1ull);
+    const unsigned long long target = lgen * (unsigned long long)gridDim.x;
+    const long long w0 = clock64();
+    bool seen = true;
+    while (ld_acquire_gpu_u64(&a.sync->light) < target)
+      if (clock64() - w0 > a.spin_limit) {
+        seen = false;
+        break;
+      }
+    red[35] = seen ? 1.0 : 0.0;
+  }
+  bar_consumers<NCT>();
+  return red[35] != 0.0;
+}
+
+// One matrix sweep by the consumer threads: blocks first, first + G, ... of M; `gv` is the gathered (extended) vector.
+//   PH = 1 (G^T):  t = sum [/ d]
+//   PH = 2 (G):    z = sum + eps r [/ d] ; acc += r z
+//   PH = 3 (A):    q = sum ; acc += p q
+template <int PH, int CAP, int STAGES, int NCW, typename VT, typename CT>
 __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& M, const FusedSmem<CAP, STAGES, VT, CT>& sm,
-                                            long long& item, const double* r, double* rn, const double* p, double* pn,
-                                            double alpha, double beta, double& acc, bool& pushed) {
+                                            long long& item, const double* gv, double& acc, bool& pushed) {
   using C = StreamCfg<CAP, VT, CT>;
   constexpr bool DELTA = C::DELTA;
   constexpr int NCT = NCW * 32;
@@ -280,52 +306,29 @@ __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& 
   const int n_items = (firstb < M.nblk) ? (M.nblk - firstb + G - 1) / G : 0;
   const VT* Aval = reinterpret_cast<const VT*>(M.sval);
   const int off = a.off;
-  const double* q = a.q;
-  const double* z = a.z;
-  const double* t = a.t;
   const bool scaled = a.d != nullptr;
   const int np = a.peer.n_push;
+  const double* own = (PH == 2) ? a.r : a.p;  // the owner-side operand of the dot (PH 2, 3)
 
-  // the gathered vector entry at extended column c
-  auto entry = [&](int c) -> double {
-    if (PH == 1) {
-      if (FLAG) return __dsub_rn(ld_coh(r + c), __dmul_rn(alpha, ld_coh(q + c)));
-      return ld_coh(r + c);
-    } else if (PH == 2) {
-      return ld_coh(t + c);
-    } else {
-      if (FLAG) return ld_coh(z + c);
-      return __dadd_rn(__dmul_rn(ld_coh(p + c), beta), ld_coh(z + c));
-    }
-  };
-  // owner work of local row i whose matrix-row sum is `sum`; o0..o3 were loaded before the row walk
-  auto finish = [&](int i, double sum, double o0, double o1, double o2, double o3) {
+  auto finish = [&](int i, double sum, double o0) {
     const int e = off + i;
     double out;
     double* const* dst;
-    if (PH == 1) {  // o0 = r, o1 = q, o2 = p, o3 = x
-      if (FLAG) {
-        a.x[i] = __dadd_rn(o3, __dmul_rn(alpha, o2));
-        const double rv = __dsub_rn(o0, __dmul_rn(alpha, o1));
-        rn[e] = rv;
-        acc += rv * rv;
-      }
+    if (PH == 1) {
       out = scaled ? sum / a.d[i] : sum;
       a.t[e] = out;
       dst = a.peer.push_t;
-    } else if (PH == 2) {  // o0 = r'
+    } else if (PH == 2) {
       double ev = __dmul_rn(a.eps, o0);
       if (scaled) ev = ev / a.d[i];
       out = __dadd_rn(sum, ev);
       a.z[e] = out;
       acc += o0 * out;
       dst = a.peer.push_z;
-    } else {  // o0 = z, o1 = p
-      const double pv = FLAG ? o0 : __dadd_rn(__dmul_rn(o1, beta), o0);
-      pn[e] = pv;
+    } else {
       out = sum;
       a.q[e] = out;
-      acc += pv * out;
+      acc += o0 * out;
       dst = a.peer.push_q;
     }
     for (int s = 0; s < np; ++s)
@@ -333,23 +336,6 @@ __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& 
         dst[s][i - a.peer.push_lo[s]] = out;
         pushed = true;
       }
-  };
-  auto prefetch = [&](int i, double& o0, double& o1, double& o2, double& o3) {
-    const int e = off + i;
-    o0 = o1 = o2 = o3 = 0.0;
-    if (PH == 1) {
-      o0 = ld_coh(r + e);
-      if (FLAG) {
-        o1 = ld_coh(q + e);
-        o2 = ld_coh(p + e);
-        o3 = ld_coh(a.x + i);
-      }
-    } else if (PH == 2) {
-      o0 = ld_coh(r + e);
-    } else {
-      o0 = ld_coh(z + e);
-      if (!FLAG) o1 = ld_coh(p + e);
-    }
   };
 
   for (int it = 0; it < n_items; ++it, ++item) {
@@ -365,16 +351,13 @@ __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& 
       const int* rfirst = sm.first + slot * C::RPTR + (r0 & 3);
       for (int rr = tid; rr < r1 - r0; rr += NCT) {
         const int row = r0 + rr;
-        double o0, o1, o2, o3;
-        prefetch(row, o0, o1, o2, o3);
+        const double o0 = (PH == 1) ? 0.0 : ld_coh(own + off + row);
         int k = rptr[rr] - lo;
         const int e = rptr[rr + 1] - lo;
         int cprev = DELTA ? rfirst[rr] : 0;
         double sum = 0.0;
-        // chunk width: 16 entries (a mesh row in one pass) when an entry is one gather, 8 when it is two (r and q, z and
-        // p) -- the gathers of a chunk are all in flight before the first add, and 2 x 16 of them do not fit the
-        // register budget of three resident CTAs per SM
-        constexpr int U = ((PH == 1 && FLAG) || (PH == 3 && !FLAG)) ? FUSED_U2 : 16;
+        // 16 entries (a mesh row) per pass: all gathers of a pass are in flight before the first add
+        constexpr int U = 16;
 #pragma unroll 1
         for (; k < e; k += U) {
           int c[U];
@@ -390,11 +373,11 @@ __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& 
             c[u] = cprev;
           }
 #pragma unroll
-          for (int u = 0; u < U; ++u) pr[u] = __dmul_rn((k + u < e) ? (double)vals[k + u] : 0.0, entry(c[u]));
+          for (int u = 0; u < U; ++u) pr[u] = __dmul_rn((k + u < e) ? (double)vals[k + u] : 0.0, gv[c[u]]);
 #pragma unroll
           for (int u = 0; u < U; ++u) sum = __dadd_rn(sum, pr[u]);
         }
-        finish(row, sum, o0, o1, o2, o3);
+        finish(row, sum, o0);
       }
     } else {
       // a row longer than the stage capacity (or a block of empty rows): warp per row from global memory, products
@@ -404,15 +387,11 @@ __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& 
         double sum = 0.0;
         for (int k0 = s; k0 < e; k0 += 32) {
           const int k = k0 + lane;
-          const double pv = (k < e) ? __dmul_rn((double)__ldg(Aval + k), entry(__ldg(M.col + k))) : 0.0;
+          const double pv = (k < e) ? __dmul_rn((double)__ldg(Aval + k), ld_coh(gv + __ldg(M.col + k))) : 0.0;
           const int m = min(32, e - k0);
           for (int j = 0; j < m; ++j) sum = __dadd_rn(sum, __shfl_sync(0xffffffffu, pv, j));
         }
-        if (lane == 0) {
-          double o0, o1, o2, o3;
-          prefetch(row, o0, o1, o2, o3);
-          finish(row, sum, o0, o1, o2, o3);
-        }
+        if (lane == 0) finish(row, sum, (PH == 1) ? 0.0 : ld_coh(own + off + row));
       }
     }
     __syncwarp();
@@ -420,8 +399,10 @@ __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& 
   }
 }
 
-template <int CAP, int STAGES, int NCW, typename VT, typename CT>
-__global__ void __launch_bounds__((NCW + 1) * 32, FUSED_MINB) pcg_fused_kernel(const __grid_constant__ FusedArgs a) {
+// MINB = resident CTAs per SM the register allocation is held to (4 -> 56 registers: the occupancy of the standalone
+// streaming kernel, whose gathers need the warps; 3 -> 72 registers)
+template <int CAP, int STAGES, int NCW, typename VT, typename CT, int MINB>
+__global__ void __launch_bounds__((NCW + 1) * 32, MINB) pcg_fused_kernel(const __grid_constant__ FusedArgs a) {
   using C = StreamCfg<CAP, VT, CT>;
   constexpr bool DELTA = C::DELTA;
   constexpr int NCT = NCW * 32;
@@ -499,7 +480,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, FUSED_MINB) pcg_fused_kernel(c
           if (DELTA) bulk_g2s(sm.first + slot * C::RPTR, M.rowfirst + ra, (uint32_t)nr4 * 4, sm.full + slot, policy);
         }
       }
-      if (!any) {  // a CTA without row blocks only takes part in the barriers
+      if (!any) {  // a CTA without row blocks only takes part in the barriers and the vector phases
         while (!*s_done) __nanosleep(200);
         stop = true;
       }
@@ -518,9 +499,9 @@ __global__ void __launch_bounds__((NCW + 1) * 32, FUSED_MINB) pcg_fused_kernel(c
   PcgScalars* sc = a.sc;
   const double rtol = sc->rtol;
   const int max_iter = sc->max_iter;
-  unsigned long long gen = 0;
+  unsigned long long gen = 0, lgen = 0;
   long long item = 0;
-  double t0, t1;
+  double t0 = 0.0, t1 = 0.0;
   bool ok = true;
 
   // (row-partitioned) nobody stores into a peer before every rank is inside this solve
@@ -532,7 +513,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, FUSED_MINB) pcg_fused_kernel(c
   if (ok) {
     for (long long i = gtid; i < n; i += gstride) {
       const double v = a.b[i];
-      a.r0[off + i] = v;
+      a.r[off + i] = v;
       a.x[i] = 0.0;
       acc += v * v;
       for (int s = 0; s < a.peer.n_push; ++s)
@@ -561,10 +542,10 @@ __global__ void __launch_bounds__((NCW + 1) * 32, FUSED_MINB) pcg_fused_kernel(c
       breakdown = 1;
     }
   }
-  double *r = a.r0, *rn = a.r1, *p = a.p0, *pn = a.p1;
-  bool pending = false;
+  bool pending = false;   // an x / r update was made: its ||r||^2 (acc_rr) is all-reduced with barrier B1
+  double acc_rr = 0.0;
   const bool prof = lead && a.prof != nullptr;
-  unsigned long long ns_prev = prof ? global_ns() : 0ull, ns_p[3] = {0ull, 0ull, 0ull};
+  unsigned long long ns_prev = prof ? global_ns() : 0ull, ns_p[5] = {0ull, 0ull, 0ull, 0ull, 0ull};
   auto stamp = [&](int k) {
     if (prof) {
       const unsigned long long now = global_ns();
@@ -574,37 +555,25 @@ __global__ void __launch_bounds__((NCW + 1) * 32, FUSED_MINB) pcg_fused_kernel(c
   };
 
   while (!done) {
-    // ---- P1 ----
+    // ---- P1: t = G^T r ----
     acc = 0.0;
     pushed = false;
-    if (pending) {
-      // halo entries of r': same two roundings as the owner's (never sent)
-      for (long long h = gtid; h < n_halo; h += gstride) {
-        const long long e = h < off ? h : (long long)n + h;
-        rn[e] = __dsub_rn(ld_coh(r + e), __dmul_rn(alpha, ld_coh(a.q + e)));
-      }
-      fused_sweep<1, true, CAP, STAGES, NCW, VT, CT>(a, a.GT, sm, item, r, rn, p, pn, alpha, beta, acc, pushed);
-      double* tmp = r;
-      r = rn;
-      rn = tmp;
-    } else {
-      fused_sweep<1, false, CAP, STAGES, NCW, VT, CT>(a, a.GT, sm, item, r, rn, p, pn, alpha, beta, acc, pushed);
-    }
-    ok = fused_barrier<NCW>(a, gen, FB_RR, acc, 0.0, pushed, red, t0, t1);
+    fused_sweep<1, CAP, STAGES, NCW, VT, CT>(a, a.GT, sm, item, a.r, acc, pushed);
+    ok = fused_barrier<NCW>(a, gen, FB_RR, 0.0, pending ? acc_rr : 0.0, pushed, red, t0, t1);
     stamp(0);
     if (!ok) {
       breakdown = 3;
       break;
     }
     if (pending) {  // the update is complete: count it, test it (scipy: callback, then the test at the loop top)
-      if (!(t0 == t0)) {
+      if (!(t1 == t1)) {
         breakdown = 1;
         break;
       }
-      rr = t0;
+      rr = t1;
       rho_prev = rho;
       iter += 1;
-      const double nrm = sqrt(t0);
+      const double nrm = sqrt(t1);
       if (lead) a.hist[iter] = nrm;
       if (nrm < atol) {
         converged = 1;
@@ -612,10 +581,10 @@ __global__ void __launch_bounds__((NCW + 1) * 32, FUSED_MINB) pcg_fused_kernel(c
       }
       if (iter >= max_iter) break;
     }
-    // ---- P2 ----
+    // ---- P2: z = G t + eps r ; rho ----
     acc = 0.0;
     pushed = false;
-    fused_sweep<2, false, CAP, STAGES, NCW, VT, CT>(a, a.G, sm, item, r, rn, p, pn, alpha, beta, acc, pushed);
+    fused_sweep<2, CAP, STAGES, NCW, VT, CT>(a, a.G, sm, item, a.t, acc, pushed);
     ok = fused_barrier<NCW>(a, gen, FB_RHO, acc, 0.0, pushed, red, t0, t1);
     stamp(1);
     if (!ok) {
@@ -625,29 +594,29 @@ __global__ void __launch_bounds__((NCW + 1) * 32, FUSED_MINB) pcg_fused_kernel(c
     rho = t0;
     const bool first = (iter == 0);
     beta = first ? 0.0 : rho / rho_prev;
-    // ---- P3 ----
+    // ---- V2: p = z + beta p (owned rows and halo; scipy: p *= beta; p += z) ----
+    {
+      const long long n_ext = (long long)n_halo + n;
+      if (first) {
+#pragma unroll 4
+        for (long long e = gtid; e < n_ext; e += gstride) a.p[e] = ld_coh(a.z + e);
+      } else {
+#pragma unroll 4
+        for (long long e = gtid; e < n_ext; e += gstride) a.p[e] = __dadd_rn(__dmul_rn(ld_coh(a.p + e), beta), ld_coh(a.z + e));
+      }
+    }
+    ok = fused_light_barrier<NCW>(a, lgen, red);
+    stamp(2);
+    if (!ok) {
+      breakdown = 3;
+      break;
+    }
+    // ---- P3: q = A p ; p.q ----
     acc = 0.0;
     pushed = false;
-    if (first) {
-      for (long long h = gtid; h < n_halo; h += gstride) {
-        const long long e = h < off ? h : (long long)n + h;
-        pn[e] = ld_coh(a.z + e);
-      }
-      fused_sweep<3, true, CAP, STAGES, NCW, VT, CT>(a, a.A, sm, item, r, rn, p, pn, alpha, beta, acc, pushed);
-    } else {
-      for (long long h = gtid; h < n_halo; h += gstride) {
-        const long long e = h < off ? h : (long long)n + h;
-        pn[e] = __dadd_rn(__dmul_rn(ld_coh(p + e), beta), ld_coh(a.z + e));
-      }
-      fused_sweep<3, false, CAP, STAGES, NCW, VT, CT>(a, a.A, sm, item, r, rn, p, pn, alpha, beta, acc, pushed);
-    }
-    {
-      double* tmp = p;
-      p = pn;
-      pn = tmp;
-    }
+    fused_sweep<3, CAP, STAGES, NCW, VT, CT>(a, a.A, sm, item, a.p, acc, pushed);
     ok = fused_barrier<NCW>(a, gen, FB_PQ, acc, 0.0, pushed, red, t0, t1);
-    stamp(2);
+    stamp(3);
     if (!ok) {
       breakdown = 3;
       break;
@@ -659,15 +628,34 @@ __global__ void __launch_bounds__((NCW + 1) * 32, FUSED_MINB) pcg_fused_kernel(c
       break;
     }
     alpha = rho / pq;
+    // ---- V1: x += alpha p ; r -= alpha q (owned rows, then the halo of r) ; ||r||^2 over the owned rows ----
+    acc_rr = 0.0;
+#pragma unroll 4
+    for (long long i = gtid; i < n; i += gstride) {
+      const long long e = off + i;
+      const double pv = ld_coh(a.p + e), qv = ld_coh(a.q + e);
+      a.x[i] = __dadd_rn(a.x[i], __dmul_rn(alpha, pv));
+      const double rv = __dsub_rn(ld_coh(a.r + e), __dmul_rn(alpha, qv));
+      a.r[e] = rv;
+      acc_rr += rv * rv;
+    }
+    for (long long h = gtid; h < n_halo; h += gstride) {
+      const long long e = h < off ? h : (long long)n + h;
+      a.r[e] = __dsub_rn(ld_coh(a.r + e), __dmul_rn(alpha, ld_coh(a.q + e)));
+    }
     pending = true;
+    ok = fused_light_barrier<NCW>(a, lgen, red);
+    stamp(4);
+    if (!ok) {
+      breakdown = 3;
+      break;
+    }
   }
 
   if (tid == 0) *s_done = 1;  // the producer stops prefetching and drains
   if (prof) {
-    a.prof[0] = ns_p[0];
-    a.prof[1] = ns_p[1];
-    a.prof[2] = ns_p[2];
-    a.prof[3] = (unsigned long long)iter;
+    for (int k = 0; k < 5; ++k) a.prof[k] = ns_p[k];
+    a.prof[5] = (unsigned long long)iter;
   }
   if (lead) {
     sc->bnorm = bnorm;
@@ -687,6 +675,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, FUSED_MINB) pcg_fused_kernel(c
 
 // host side (pcg_fused.cu)
 struct FusedPlan {
+  int minb = 4;     // kernel variant: resident CTAs per SM
   int which = -1;   // partition index (1: 2048-entry stages, 2: 4096)
   int fmt = 0;      // bit 0: fp32 values, bit 1: 16-bit column steps
   int grid = 0;     // co-resident CTAs

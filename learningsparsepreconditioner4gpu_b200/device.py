@@ -201,8 +201,9 @@ class DevicePCG:
         return [float(v) for v in ms]
 
     def fused_profile(self):
-        """Mode 4, after a solve: ([ms in sweep G^T, sweep G, sweep A] incl. their barriers, iterations covered)."""
-        ms = (C.c_double * 3)()
+        """Mode 4, after a solve: ([ms in t = G^T r, z = G t, p update, q = A p, x/r update] incl. the barrier closing
+        each phase, iterations covered)."""
+        ms = (C.c_double * 5)()
         it = C.c_int32()
         _lib.check(self._lib.b200spai_pcg_fused_profile(self._h, ms, C.byref(it), _stream()), "pcg_fused_profile")
         return [float(v) for v in ms], it.value

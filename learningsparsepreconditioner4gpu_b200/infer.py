@@ -186,7 +186,54 @@ def save_stats(stats: Timestat, out_dir, exp_name: str, rtol: float, infer_prefi
     return fname, all_fname
 
 
+def main_hydra(argv: Sequence[str]):
+    """``python -m learningsparsepreconditioner4gpu_b200.infer exp_name=heat pretrained=ckpt.pt +rtol=1e-6 ...``: the
+    reference's Hydra entry point (infer.py:166-385) on the composed ``config/*.yaml`` -- same keys, same ad-hoc
+    ``cfg.get`` knobs (workspace, repeat, rhs, rtol, warmup, dataloader, out_dir, infer_prefix; infer.py:218-259,274,376).
+    ``pretrained`` is a plain ``state_dict`` file (Lightning ``.ckpt`` pickles need omegaconf + lightning); empty ->
+    the seed-42 random init."""
+    from .neural_cg.utils import config as hc
+    from .neural_cg.utils.datamodule import FolderDataModule
+
+    name, cdir, overrides = hc.parse_cli(list(argv))
+    cfg = hc.compose(name, overrides, cdir)
+    if "all_prefix" in cfg.data:
+        raise NotImplementedError("MultiFolderDataModule (data.all_prefix) is outside the solve path")
+    data = FolderDataModule(data_config=cfg.data, split_config=cfg.split, batch_size=cfg.batch_size)
+    edge_f, node_f, block_size = data.dataset.num_edge_features, data.dataset.num_node_features, data.dataset.block_size
+    workspace_class, pcg = get_workspace(cfg.get("workspace", "simple"))
+    kw = hc.workspace_kwargs(cfg)
+    torch.manual_seed(int(cfg.get("seed", 42)))
+    model = workspace_class(edge_features=edge_f, node_features=node_f, block_size=block_size, **kw).eval()
+    if cfg.get("pretrained", ""):
+        sd = torch.load(cfg.pretrained, map_location="cpu")
+        model.load_state_dict(sd.get("state_dict", sd))
+    loader_name = cfg.get("dataloader", "test")
+    if loader_name == "train":
+        dl = data.train_dataloader()
+    elif loader_name in ("val", "test"):
+        dl = data.val_dataloader()
+    elif loader_name == "infer":
+        dl = data.inference_dataloader()
+    else:
+        raise ValueError(f"Unknown dataloader name: {loader_name}")
+    rtol = float(cfg.get("rtol", 1e-6))
+    stats = run_inference(model, dl, pcg=pcg, rhs=cfg.get("rhs", "mask"), rtol=rtol, repeat=int(cfg.get("repeat", 1)),
+                          warmup=int(cfg.get("warmup", 20)))
+    stats.rich_print()
+    f1, f2 = save_stats(stats, cfg.get("out_dir", "output"), cfg.exp_name, rtol, cfg.get("infer_prefix", ""))
+    print(f"Inference statistics saved to {f1}\nAll inference statistics saved to {f2}")
+    return stats
+
+
 def main(argv=None):
+    import sys
+
+    argv = list(sys.argv[1:] if argv is None else argv)
+    # Hydra-style command line (key=value / +key=value overrides, as the reference is launched) -> the config path;
+    # the --flag form below stays as an alias for synthetic systems and ad-hoc folders
+    if any((not a.startswith("--")) and ("=" in a or a.startswith(("+", "~"))) for a in argv):
+        return main_hydra(argv)
     ap = argparse.ArgumentParser(description="learned-SPAI PCG inference benchmark (reference infer.py) on B200")
     ap.add_argument("--exp-name", default="poisson3d")
     ap.add_argument("--data-prefix", default=None, help="dataset folder (reference layout); default: synthetic systems")

@@ -95,11 +95,11 @@ _graph_cache = {}
 
 
 def _graph_for(edge_index: torch.Tensor, num_nodes: int):
-    """DeviceGraph cached on the identity of the edge_index storage (one entry: the operators are called
-    repeatedly on the same batch)."""
-    from .gnns import DeviceGraph
+    """DeviceGraph cached on the identity of the edge_index tensor (one entry: the operators are called repeatedly on
+    the same batch).  The entry keeps the tensor alive and is keyed on address + version + device (``gnns.graph_key``)."""
+    from .gnns import DeviceGraph, graph_key
 
-    key = (edge_index.data_ptr(), int(num_nodes), int(edge_index.shape[1]), edge_index._version)
+    key = graph_key(edge_index, num_nodes)
     hit = _graph_cache.get("g")
     if hit is None or hit[0] != key:
         _graph_cache["g"] = (key, DeviceGraph(edge_index, num_nodes))

@@ -84,6 +84,15 @@ def _check_mlp(cfg: dict, pre_norm: str, what: str):
                                   f"(hidden 16, num_layers 2, gelu, pre_norm in {pre_norm})")
 
 
+def graph_key(edge_index: torch.Tensor, num_nodes: int):
+    """Cache key of a topology: identity of the ``edge_index`` tensor's memory (address, layout, device) AND its in-place
+    version counter.  Only valid while the cached graph keeps a reference to that tensor (``DeviceGraph._keepalive``):
+    torch's caching allocator hands a freed block back at the same address, so an address alone says nothing about the
+    connectivity stored there (two meshes of equal N and E routinely land on the same block)."""
+    return (edge_index.data_ptr(), edge_index._version, edge_index.device.index, tuple(edge_index.stride()),
+            int(num_nodes), int(edge_index.shape[1]))
+
+
 class DeviceGraph:
     """Per-topology preprocessing (b200spai_graph_create): target-sorted edges, segment offsets, workspaces."""
 
@@ -97,7 +106,8 @@ class DeviceGraph:
         _lib.check(self._lib.b200spai_graph_create(self.num_nodes, self.num_edges, C.c_void_p(ei.data_ptr()),
                                                    C.c_void_p(torch.cuda.current_stream().cuda_stream), C.byref(self._h)),
                    "graph_create")
-        self.key = (ei.data_ptr(), self.num_nodes, self.num_edges)
+        self.key = graph_key(edge_index, num_nodes)
+        self._keepalive = edge_index      # pins the storage the key names: it cannot be freed and recycled under the cache
 
     def close(self):
         if self._h:
@@ -200,9 +210,10 @@ class NodeEdgeProcessing(nn.Module):
             self._engine = None
 
     def graph_for(self, edge_index: torch.Tensor, num_nodes: int) -> DeviceGraph:
-        """Topology preprocessing is cached on the identity of the edge_index tensor (fixed-topology
-        datasets reuse one graph for every sample)."""
-        key = (edge_index.data_ptr(), int(num_nodes), int(edge_index.shape[1]))
+        """Topology preprocessing is cached on the identity of the edge_index tensor (fixed-topology datasets reuse one
+        graph for every sample).  The cached graph holds that tensor alive and the key carries its version counter, so
+        neither a recycled address nor an in-place edit can alias a stale topology (``graph_key``)."""
+        key = graph_key(edge_index, num_nodes)
         if self._graph is None or self._graph.key != key:
             self._graph = DeviceGraph(edge_index, num_nodes)
         return self._graph

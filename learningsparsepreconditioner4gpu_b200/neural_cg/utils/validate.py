@@ -43,13 +43,22 @@ def _cuda(x, dtype=None) -> Optional[torch.Tensor]:
 
 
 def to_csr_device(edge_index, edge_attr, n: int, mask, dtype=np.float64) -> DeviceCSR:
-    """Edge list (+ mask) -> fp64 CSR resident in HBM; semantics of to_csr_cpu."""
+    """Edge list (+ mask) -> fp64 CSR resident in HBM; semantics of to_csr_cpu.
+
+    Restriction against the reference (validate.py:22-51 widens WHATEVER dtype arrives to float64): the assembly entry
+    point takes fp32 edge values -- what every caller on the path passes (``matrix_values`` and the GNN output are fp32
+    tensors, data.py:312, workspace.py:94).  float64 values that are not exactly fp32-representable would silently
+    lose bits, so they are refused; build such a matrix with ``DeviceCSR.from_scipy`` (fp64 values) instead."""
     _lib.require_cuda()
     if np.dtype(dtype) != np.float64:
         raise ValueError("only float64 matrices are supported (the reference assembles in float64)")
     assert edge_index.ndim == 2 and edge_index.shape[0] == 2
     assert edge_attr.ndim in (1, 3)
     vals = _cuda(edge_attr, torch.float32)
+    wide = edge_attr.dtype in (torch.float64, np.float64) if hasattr(edge_attr, "dtype") else False
+    if wide and not bool((vals.to(torch.float64) == _cuda(edge_attr, torch.float64)).all()):
+        raise ValueError("to_csr: float64 edge values that are not fp32-representable would lose precision in the fp32 "
+                         "assembly entry point; pass fp32 values or build the matrix with DeviceCSR.from_scipy")
     bsize = 1 if vals.dim() == 1 else vals.shape[-1]
     assert n % bsize == 0
     return DeviceCSR.from_edges(_cuda(edge_index, torch.int64), vals, n // bsize, _cuda(mask, torch.float32))

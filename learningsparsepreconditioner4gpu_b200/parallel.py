@@ -226,8 +226,9 @@ class DistPCG:
         return {k: round(float(v), 5) for k, v in zip(self.PROFILE_KEYS, out)}
 
     def fused_profile(self):
-        """Mode 4, after a solve: ([ms in sweep G^T, sweep G, sweep A] incl. their barriers, iterations covered), this rank."""
-        ms = (C.c_double * 3)()
+        """Mode 4, after a solve: ([ms in t = G^T r, z = G t, p update, q = A p, x/r update] incl. the barrier closing
+        each phase, iterations covered), this rank's view."""
+        ms = (C.c_double * 5)()
         it = C.c_int32()
         _lib.check(self._lib.b200spai_dist_pcg_fused_profile(self._h, ms, C.byref(it), _stream()), "dist_pcg_fused_profile")
         return [float(v) for v in ms], it.value

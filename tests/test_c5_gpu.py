@@ -187,7 +187,7 @@ def test_stream_epilogues_and_fallback_streams_vs_scipy(fp32_values, narrow):
 
 
 def test_fused_kernel_edge_cases():
-    """mode 4: zero rhs, max_iter cut-off, determinism, profile hook, and that auto mode picks it for large SPAI solves."""
+    """mode 4: zero rhs, max_iter cut-off, determinism, profile hook; auto mode keeps the graph driver on one GPU."""
     from learningsparsepreconditioner4gpu_b200 import device as d
 
     A, G = _spd_pair(140000, 4, 3, True, True)
@@ -211,6 +211,6 @@ def test_fused_kernel_edge_cases():
     auto = d.DevicePCG(Ad)
     auto.set_spai(Gd, 3e-3)
     _, ra, _ = auto.solve(b, "ext_spai", rtol=1e-8)
-    assert ra.reserved == 4
-    _, rn, _ = auto.solve(b, "diagonal", rtol=1e-8)                 # no SPAI in the iteration: graph driver
-    assert rn.reserved == 2 and rn.converged == 1
+    assert ra.reserved == 2 and ra.converged == 1
+    with pytest.raises(Exception):
+        solver.solve(b, "diagonal", rtol=1e-8)                      # mode 4 is the SPAI iteration
