@@ -36,10 +36,6 @@ import torch  # noqa: E402
 FUSED_PHASES = ("GT_r+barrier", "G_t+barrier", "update_p+barrier", "A_p+barrier", "update_xr+barrier")
 METRIC = "learned-SPAI PCG solves/s to rtol 1e-6 (GNN->G, assembly, PCG; time-to-1e-6 in extra keys)"
 UNIT = "solves/s"
-# PCG iterations of the default workload at rtol 1e-6, measured by the CUDA path (iteration parity with the oracle
-# is +-1 on every size the oracle can solve, tests/test_pcg_gpu.py).  Used ONLY by --impl reference to scale its
-# per-iteration CPU time to a whole solve without running ~10^3 s of scipy; override with B200SPAI_REF_ITERS.
-DEFAULT_ITERS = {216: 1391}
 
 
 def log(*a):
@@ -109,6 +105,35 @@ class ClockSampler:
         return out
 
 
+def ncu_traffic(grid: int):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the streaming SpMV from the newest committed ncu summary
+    (profiles/r*_spmv_stream_ncu_full.txt, 216^3 only) -- (bytes or None, source)."""
+    import glob
+    import re
+
+    if grid != 216:
+        return None, "no ncu capture for this grid size"
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_spmv_stream_ncu_full.txt")))
+    if not files:
+        return None, "no ncu summary under profiles/"
+    rd, wr = [], []
+    for line in open(files[-1]):
+        m = re.match(r"dram__bytes_(read|write)\.sum \[(\w+)\]:\s*\[(.*)\]", line.strip())
+        if m:
+            scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[m.group(2)]
+            vals = [float(v.strip().strip("'")) * scale for v in m.group(3).split(",")]
+            (rd if m.group(1) == "read" else wr).extend(vals)
+    if not rd or len(rd) != len(wr):
+        return None, f"could not parse {os.path.basename(files[-1])}"
+    return float(np.mean([a + b for a, b in zip(rd, wr)])), f"ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, mean of {len(rd)} launches ({os.path.relpath(files[-1], ROOT)})"
+
+
+def workload_text(g, N, E, rtol) -> str:
+    """The ONE description of the workload both arms (and every N) print, so that their `config` dicts are equal."""
+    return (f"poisson3d jittered Kuhn-tet grid {g}^3 = {N} DOF, E = {E} stored entries, Dirichlet patch, "
+            f"random-init GNN (seed 42), eps 3e-3, rhs = A*mask, rtol {rtol:g}")
+
+
 def tensor_bytes(*ts) -> int:
     return int(sum(t.numel() * t.element_size() for t in ts if isinstance(t, torch.Tensor)))
 
@@ -159,42 +184,59 @@ def phases_ms(timers):
     return out
 
 
-def main_ours(args):
+class Ctx:
+    """One process per GPU: rank / world from the torchrun environment, NCCL process group as plumbing (barriers,
+    max-over-ranks of the device times)."""
+
+    def __init__(self):
+        from learningsparsepreconditioner4gpu_b200 import _lib
+
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        _lib.require_cuda()
+        torch.cuda.set_device(self.local)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            os.environ.setdefault("MASTER_PORT", "29533")
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local), rank=self.rank, world_size=self.world)
+            self.dist = dist
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        torch.cuda.synchronize()
+
+    def _reduce(self, v: float, op) -> float:
+        if self.dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    def max(self, v: float) -> float:
+        return self._reduce(v, None if self.dist is None else self.dist.ReduceOp.MAX)
+
+    def sum(self, v: float) -> float:
+        return self._reduce(v, None if self.dist is None else self.dist.ReduceOp.SUM)
+
+    def close(self):
+        if self.dist is not None:
+            self.dist.destroy_process_group()
+
+
+def main_ours(args, ctx: Ctx, emit: bool = True):
+    """Independent systems, one per GPU (weak scaling; the whole bench line at N = 1, the "replicas" figure at N > 1)."""
     from learningsparsepreconditioner4gpu_b200 import _lib, systems
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    _lib.require_cuda()
-    torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank, world, local, dist = ctx.rank, ctx.world, ctx.local, ctx.dist
     n_gpus = world
     if args.gpus and args.gpus != world and rank == 0:
         log(f"[bench] --gpus {args.gpus} but WORLD_SIZE={world}: running on {world} rank(s)")
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(v: float) -> float:
-        if dist is None:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(v: float) -> float:
-        if dist is None:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    barrier, max_over_ranks, sum_over_ranks = ctx.barrier, ctx.max, ctx.sum
 
     g = args.grid
     t0 = time.time()
@@ -276,28 +318,43 @@ def main_ours(args):
     spmv_bytes = sum(by for k, by in bytes_k.items() if "update" not in k)
     spmv_streamed = sum(by for k, by in streamed_k.items() if "update" not in k)
     spmv_ms = kms[0] + kms[1] + kms[3]
-    achieved = spmv_bytes / 3 / (spmv_ms / 3 * 1e-3) / 1e9
+    algorithmic = spmv_bytes / 3 / (spmv_ms / 3 * 1e-3) / 1e9
     streamed = spmv_streamed / 3 / (spmv_ms / 3 * 1e-3) / 1e9
     iter_bytes = sum(bytes_k.values())
     iter_streamed = sum(streamed_k.values())
     iter_ms = sum(kms)
+    vt = {4: "float", 8: "double"}
+    ct = {2: "unsigned short (16-bit column steps)", 4: "int"}
+    traffic, traffic_src = ncu_traffic(g)
     roofline = {
-        "kernel": "spmv_stream_kernel<4096,2,8,float,u16,*> (3 launches per PCG iteration: t=G^T r, z=G t+eps r, q=A p)",
-        "bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-        "peak_source": peak_src,
-        "traffic": 1.11e9 if g == 216 else None,
-        "traffic_source": "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch at 216^3 (profiles/r01_spmv_stream_ncu_full.txt)",
-        "bytes_per_launch": spmv_bytes // 3, "ms_per_launch": round(spmv_ms / 3, 4),
-        "note": ("achieved = ALGORITHMIC bytes (SURVEY 8d: 12 B per entry, fp64 value + i32 index) / time; the kernel streams a lossless "
-                 f"{per_a} B per entry (fp32 values widened on load, 16-bit column steps), so it can exceed the copy peak; "
-                 "'streamed' is the same time against the bytes really read"),
-        "streamed": {"bytes_per_launch": spmv_streamed // 3, "GB/s": round(streamed, 1), "frac": round(streamed / peak, 4)},
-        "pcg_iteration": {"ms": round(iter_ms, 4), "bytes": iter_bytes, "GB/s": round(iter_bytes / (iter_ms * 1e-3) / 1e9, 1),
-                          "frac": round(iter_bytes / (iter_ms * 1e-3) / 1e9 / peak, 4),
-                          "streamed_bytes": iter_streamed, "streamed_GB/s": round(iter_streamed / (iter_ms * 1e-3) / 1e9, 1),
-                          "streamed_frac": round(iter_streamed / (iter_ms * 1e-3) / 1e9 / peak, 4)},
+        "kernel": f"spmv_stream_kernel<4096,2,8,{vt.get(va, va)},{ct.get(ia, ia)},*> (3 launches per PCG iteration: t=G^T r, z=G t+eps r, q=A p)"
+                  if nnzA >= (1 << 22) else "spmv kernels of the 5-launch iteration",
+        # achieved / frac: the bytes the kernel REALLY streams per launch (lossless fp32 values + 16-bit column steps where they
+        # apply; agrees with ncu's dram__bytes, `traffic`) over its CUDA-event time -- a true fraction of the measured HBM peak
+        "bound": "hbm", "achieved": round(streamed, 1), "peak": peak, "unit": "GB/s", "frac": round(streamed / peak, 4),
+        "peak_source": peak_src, "traffic": traffic, "traffic_source": traffic_src,
+        "bytes_per_launch": spmv_streamed // 3, "ms_per_launch": round(spmv_ms / 3, 4),
+        # the same time against SURVEY 8d's algorithmic bytes (12 B per entry: fp64 value + i32 index): what a kernel streaming the
+        # uncompressed CSR would have to sustain -- > peak means the compression buys more than the roofline allows without it
+        "algorithmic": {"bytes_per_launch": spmv_bytes // 3, "GB/s": round(algorithmic, 1), "frac_of_peak": round(algorithmic / peak, 4),
+                        "speedup_from_lossless_stream": round(spmv_bytes / max(spmv_streamed, 1), 3)},
+        "pcg_iteration": {"ms": round(iter_ms, 4), "streamed_bytes": iter_streamed, "streamed_GB/s": round(iter_streamed / (iter_ms * 1e-3) / 1e9, 1),
+                          "frac": round(iter_streamed / (iter_ms * 1e-3) / 1e9 / peak, 4), "algorithmic_bytes": iter_bytes,
+                          "algorithmic_GB/s": round(iter_bytes / (iter_ms * 1e-3) / 1e9, 1)},
         "per_kernel": detail,
     }
+    # GNN forward against the fp32 FFMA roofline (MAC counts per edge / node; 2 flop per MAC)
+    Fe, Fin, bb = sample.edge_attr.shape[1], sample.x.shape[1], ws.block_size ** 2
+    gnn_flop = 2.0 * (E * (11776 + 16 * Fe + 16 * bb) + N * (4 * 768 + 16 * Fin + 512))
+    gnn_ms = ph.get("gnn", 0.0) / args.steps
+    ffma_peak = 148 * 128 * 2 * 1.965e9 / 1e12
+    roofline["gnn"] = {"kernel": "gnn_edge_kernel + gnn_node_kernel x 4 MP layers, encoders, decoder (fp32 FFMA)", "bound": "fp32",
+                       "flop": gnn_flop, "ms": round(gnn_ms, 3), "achieved": round(gnn_flop / (gnn_ms * 1e-3) / 1e12, 2) if gnn_ms > 0 else None,
+                       "peak": round(ffma_peak, 1), "unit": "TFLOP/s",
+                       "frac": round(gnn_flop / (gnn_ms * 1e-3) / 1e12 / ffma_peak, 4) if gnn_ms > 0 else None,
+                       "peak_source": "148 SMs x 128 FFMA lanes x 2 flop x 1.965 GHz (SURVEY 8d); frac_at_sampled_clock uses the SM clock under load"}
+    if clocks and clocks.get("sm_mhz") and gnn_ms > 0:
+        roofline["gnn"]["frac_at_sampled_clock"] = round(gnn_flop / (gnn_ms * 1e-3) / 1e12 / (148 * 128 * 2 * clocks["sm_mhz"] * 1e6 / 1e12), 4)
     del solver, A, G, rhs
     torch.cuda.empty_cache()
 
@@ -335,10 +392,9 @@ def main_ours(args):
             "metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": round(dev_ms / args.steps, 3), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64 (PCG) / f32 (GNN)", "data": "synthetic",
-            "config": {"workload": f"poisson3d jittered Kuhn-tet grid {g}^3 = {N} DOF per GPU, E = {E} stored entries, "
-                                   f"Dirichlet patch, random-init GNN (seed 42), eps 3e-3, rhs = A*mask, rtol {args.rtol:g}",
-                       "systems_per_step": n_gpus, "parallelism": f"{n_gpus} independent system(s), one per GPU",
-                       "l2": "inputs larger than L2 (A + G + G^T = %.1f GB)" % ((nnzA + 2 * nnzG) * 12 / 1e9)},
+            "config": {"workload": workload_text(g, N, E, args.rtol), "systems_per_step": n_gpus},
+            "parallelism": f"{n_gpus} independent system(s), one per GPU",
+            "l2": "inputs larger than L2 (A + G + G^T = %.1f GB streamed per iteration)" % ((nnzA * (va + ia) + 2 * nnzG * (vg + ig)) / 1e9),
             "time_to_tol_ms": round(float(np.mean(pcg_ms)), 3), "iterations": round(total_iters, 1), "converged": converged,
             "ms_per_iteration": round(float(np.mean(pcg_ms)) / max(float(np.mean(iters)), 1.0), 4),
             "pcg_mode": pcg_mode, "fused_phases": fused_phases,
@@ -347,9 +403,10 @@ def main_ours(args):
                     "ms_per_step": round(e2e_ms / args.steps, 3), "api": "SimpleTrainingWorkspace.solve path on a pinned-host sample"},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
         }
-        print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.destroy_process_group()
+        if emit:
+            print(json.dumps(line), flush=True)
+        return line
+    return None
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -408,47 +465,66 @@ class CpuArm:
 
 
 def cpu_reference_sample(sample, ws, iterations: int, args):
-    arm = CpuArm(sample.to("cpu"), ws, args.rtol, gnn_grid=56)
+    """cpu_baseline of the CUDA arm: scaled with the oracle's OWN iteration count when a fixture holds it (216^3), else
+    with the CUDA path's count."""
+    fx = os.path.join(ROOT, "tests", "golden", f"c5_{args.grid}.npz")
+    if os.path.exists(fx):
+        iterations = int(np.load(fx, allow_pickle=False)["iters_pcg"])
+    arm = CpuArm(sample.to("cpu"), ws, args.rtol, gnn_grid=min(96, args.grid))
     arm.step(iterations, 1)  # warm-up (page in, torch thread pool)
     return arm.step(iterations, 6)
 
 
+def reference_iterations(grid: int):
+    """(iterations, source) the reference's solve of the bench system takes.  216^3: the oracle run to completion on the
+    CPU-generated twin of the bench system (tests/golden/c5_216.npz, minted by tests/golden/make_golden_c5.py --oracle 216:
+    1451 iterations in 1608 s on 4 cores of the build container); other sizes: the committed fixture when there is one."""
+    env = os.environ.get("B200SPAI_REF_ITERS")
+    if env:
+        return int(env), "B200SPAI_REF_ITERS"
+    fx = os.path.join(ROOT, "tests", "golden", f"c5_{grid}.npz")
+    if os.path.exists(fx):
+        return int(np.load(fx, allow_pickle=False)["iters_pcg"]), f"tests/golden/c5_{grid}.npz (oracle solve run to completion)"
+    return int(6.7 * grid), "6.7 x grid edge (fit through the 64^3 / 128^3 / 216^3 fixtures)"
+
+
 def main_reference(args):
     """--impl reference: the reference's CPU path (oracle port; the reference itself needs torch_geometric,
-    lightning and pymathprim, none installable here) on this box's host cores, same workload and metric."""
+    lightning and pymathprim, none installable here) on this box's host cores, same workload and metric.  Every step is a
+    bounded sample: the oracle GNN forward on a 96^3 system of the same family scaled by E, and 3 iterations of the
+    oracle's scipy PCG on the FULL system scaled by the iteration count of the oracle's own complete solve (fixture)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from learningsparsepreconditioner4gpu_b200 import systems
 
+    torch.set_num_threads(os.cpu_count() or 1)     # torchrun exports OMP_NUM_THREADS=1: use every host core at every N
     g = args.grid
-    iterations = int(os.environ.get("B200SPAI_REF_ITERS", DEFAULT_ITERS.get(g, 0)) or 0)
-    if iterations <= 0:
-        iterations = int(6.4 * g)  # measured: 1372 PCG iterations at g = 216 (random-init G); linear in the grid edge
+    iterations, it_src = reference_iterations(g)
     gen_device = "cuda" if torch.cuda.is_available() else "cpu"   # input generation only
     sample = systems.poisson_sample(g, seed=100, gen_device=gen_device, device="cpu")
     ws = systems.default_workspace(sample)
     N, E = sample.num_nodes, sample.num_edges
-    arm = CpuArm(sample, ws, args.rtol, gnn_grid=40)
+    arm = CpuArm(sample, ws, args.rtol, gnn_grid=min(96, g))
     steps = max(args.steps, 1)
     vals, last = [], None
     t_begin = time.perf_counter()
     for i in range(max(args.warmup, 0) + steps):
-        # every step is a bounded sample: a few PCG iterations on the full system + a small-grid GNN forward
         last = arm.step(iterations, pcg_iters=3)
         if i >= args.warmup:
             vals.append(last["value"])
         if time.perf_counter() - t_begin > 200 and vals:
             break
     value = float(np.mean(vals))
+    sample_txt = last["sample"] + f"; iteration count from {it_src}"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
-        "steps": len(vals), "warmup": args.warmup, "ms_per_step": 1e3 / value, "higher_is_better": True, "scaling": "weak",
+        "steps": len(vals), "warmup": args.warmup, "ms_per_step": 1e3 / value, "higher_is_better": True,
+        "scaling": "strong" if int(os.environ.get("WORLD_SIZE", "1")) > 1 else "weak",
         "vs_baseline": None, "dtype": "f64 (PCG) / f32 (GNN)", "data": "synthetic",
-        "config": {"workload": f"poisson3d jittered Kuhn-tet grid {g}^3 = {N} DOF, E = {E} stored entries, Dirichlet patch, "
-                               f"random-init GNN (seed 42), eps 3e-3, rhs = A*mask, rtol {args.rtol:g}",
-                   "systems_per_step": 1, "parallelism": "CPU: torch threads for the GNN, 1 thread for scipy PCG"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": last["cores"], "kind": "port", "sample": last["sample"]},
+        "config": {"workload": workload_text(g, N, E, args.rtol), "systems_per_step": 1},
+        "parallelism": f"CPU: {last['cores']} torch threads for the GNN, 1 thread for scipy PCG (csr_matvec is single-threaded)",
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": last["cores"], "kind": "port", "sample": sample_txt},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -457,108 +533,164 @@ def main_reference(args):
 
 
 # ---------------------------------------------------------------------------------------------------------
-# --mode rowpart: ONE system row-partitioned over all ranks (BASELINE config C5; strong scaling)
+# N > 1 (and --mode rowpart): ONE system row-partitioned over all ranks (BASELINE config C5; strong scaling)
 # ---------------------------------------------------------------------------------------------------------
-def main_rowpart(args):
-    """Every rank holds the INPUTS of the same system and computes only its share (parallel.PartitionedSystem): the GNN
-    on the edges whose target it owns (node-feature halo per layer), one boundary swap of G values, assembly of its rows
-    of A, G and G^T, and the row-partitioned PCG (csrc/dist.cu: NVLink peer-store halos, peer-memory all-reduce)."""
+ROWPART_INPUTS = ("ei_r", "ei_t", "mv_r", "ea_t", "x_ext", "mask_ext")
+
+
+def main_rowpart(args, ctx: Ctx, emit: bool = True):
+    """The SAME 216^3 system at every N, split by rows: every rank holds only ITS slices of the inputs (the edges whose row
+    it owns, the edges whose target it owns, the node window they touch -- parallel.rank_edge_slices) and computes only its
+    share: the GNN on the target-owned edges (node-feature halo per layer), one boundary swap of G values, assembly of its
+    rows of A, G and G^T, and the row-partitioned PCG (one persistent kernel per rank, csrc/pcg_fused.cuh: NVLink
+    peer-store halos and the all-reduce of the CG scalars inside its grid barriers).  value = solves/s of that one system
+    with the slices resident in HBM; e2e = the same with every rank's slices in pinned host memory (H2D of the slices and
+    D2H of the owned part of x inside the timed region)."""
     from learningsparsepreconditioner4gpu_b200 import _lib, parallel as par, systems
-    from learningsparsepreconditioner4gpu_b200.neural_cg.nn.gnns import DeviceGraph
-    from learningsparsepreconditioner4gpu_b200.neural_cg.utils.validate import to_csr_device
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    _lib.require_cuda()
-    torch.cuda.set_device(local)
-    import torch.distributed as dist
-
-    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-    os.environ.setdefault("MASTER_PORT", "29533")
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local), rank=rank, world_size=world)
-
-    def barrier():
-        dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(v: float) -> float:
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
+    rank, world = ctx.rank, ctx.world
+    barrier, max_over_ranks = ctx.barrier, ctx.max
     g = args.grid
-    sample = systems.poisson_sample(g, seed=100, gen_device="cuda", device="cuda")   # the SAME inputs on every rank
+    t0 = time.time()
+    sample = systems.poisson_sample(g, seed=100, gen_device="cuda", device="cuda")   # generated once per rank, then sliced
     N, E = sample.num_nodes, sample.num_edges
     ws = systems.default_workspace(sample)
+    b = ws.block_size
     starts = par.partition_rows(par.row_weights_from_edges(sample.edge_index, N), world)
     rs, re = starts[rank], starts[rank + 1]
-    log(f"[rowpart r{rank}] {g}^3: N={N} rows [{rs},{re})")
+    e0, e1, ids_t = par.rank_edge_slices(sample.edge_index, starts, rank)
+    inp = {"ei_r": sample.edge_index[:, e0:e1].contiguous(), "ei_t": sample.edge_index[:, ids_t].contiguous(),
+           "mv_r": sample.matrix_values[e0:e1].contiguous(), "ea_t": sample.edge_attr[ids_t].contiguous()}
+    ps0 = par.PartitionedSystem(None, N, b, starts, rank=rank, world=world, slices=(inp["ei_r"], inp["ei_t"]))
+    inp["x_ext"] = ps0.ext_slice(sample.x)
+    inp["mask_ext"] = ps0.ext_slice(sample.mask.reshape(N, b))
+    info0 = {"ext_nodes": ps0.ext_nodes, "edges_row_owned": int(e1 - e0), "edges_target_owned": int(ids_t.numel())}
+    ps0.close()
+    del sample, ps0, ids_t
+    torch.cuda.empty_cache()
+    host = {k: v.to("cpu").pin_memory() for k, v in inp.items()}
+    h2d = tensor_bytes(*host.values())
+    d2h = (re - rs) * b * 8
+    log(f"[rowpart r{rank}] {g}^3: N={N} rows [{rs},{re}), slices {h2d / 1e6:.0f} MB, prepared in {time.time() - t0:.1f}s")
 
-    def step(timers=None):
+    def step(d, timers=None, profile=False):
         def mark(name):
             if timers is not None:
                 ev = torch.cuda.Event(enable_timing=True)
                 ev.record()
                 timers.append((name, ev))
         mark("start")
-        ps = par.PartitionedSystem(sample.edge_index, N, ws.block_size, starts)
-        mark("partition (edge ownership, local edge lists)")
-        g_t = ps.gnn_forward(ws.gnn, sample.x, sample.edge_attr)
+        ps = par.PartitionedSystem(None, N, b, starts, rank=rank, world=world, slices=(d["ei_r"], d["ei_t"]))
+        mark("partition (layout, local edge lists, G-exchange plan)")
+        g_t = ps.gnn_forward_local(ws.gnn, d["x_ext"], d["ea_t"])
         mark("gnn (target-owned edges, halo per layer)")
-        local = ps.assemble(sample.matrix_values, g_t, sample.mask)
-        rhs_loc = local[0].matvec(ps.ext_slice(sample.mask.reshape(N, ws.block_size)).reshape(-1).to(torch.float64))
+        local = ps.assemble_local(d["mv_r"], g_t, d["mask_ext"])
+        rhs_loc = local[0].matvec(d["mask_ext"].reshape(-1).to(torch.float64))
         mark("G swap + assemble A, G, G^T rows")
         solver = ps.make_solver(local, ws.epsilon, reuse=True)   # the IPC connection is kept between steps
         mark("connect / relayout")
         x, res, _ = solver.solve(rhs_loc, "ext_spai", rtol=args.rtol)
         mark("pcg (row-partitioned)")
         info = solver.info()
-        if timers is None and os.environ.get("B200SPAI_DIST_PROFILE"):     # warm-up steps only: per-launch times
-            info["per_launch_ms"] = solver.profile_iterations(rhs_loc, 50)
-        info["edges_gnn"] = int(ps.ids_t.numel())
+        info["pcg_mode"] = int(res.reserved)
+        if profile and res.reserved == 4:
+            ms, its = solver.fused_profile()
+            info["fused_phases_ms_per_iteration"] = {k: round(v / max(its, 1), 5) for k, v in zip(FUSED_PHASES, ms)}
+        if profile:
+            info["nnz_local"] = [local[0].nnz, local[1].nnz, local[2].nnz]
+            info["stream_bytes"] = [list(local[0].stream_bytes()), list(local[1].stream_bytes())]
         solver.close()      # parks the connection for the next step
         ps.close()
-        return res, info
+        return x, res, info
 
-    for _ in range(max(args.warmup, 1)):
-        res, info = step()
-    prof = info.get("per_launch_ms")
-    if prof:
-        log(f"[rowpart r{rank}] per-launch ms: {prof}")
+    for _ in range(max(args.warmup, 3)):
+        x, res, info = step(inp, profile=True)
     launches0 = _lib.total_launches()
+    sampler = ClockSampler(ctx.local)
     timers = []
     barrier()
+    if rank == 0:
+        sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     pcg_ms, iters = [], []
     for _ in range(args.steps):
-        res, info = step(timers)
+        x, res, _ = step(inp, timers)
         pcg_ms.append(float(res.solve_ms))
         iters.append(int(res.iterations))
     ev1.record()
     barrier()
+    clocks = sampler.stop() if rank == 0 else None
     dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
     pcg = max_over_ranks(float(np.mean(pcg_ms)))
     ph = phases_ms(timers)
     launches = _lib.total_launches() - launches0
+
+    # ---- end to end: every rank's slices start in pinned host memory ----
+    x_host = torch.empty(max((re - rs) * b, 1), dtype=torch.float64).pin_memory()
+
+    def e2e_step():
+        d = {k: v.to("cuda", non_blocking=True) for k, v in host.items()}
+        xs, r, _ = step(d)
+        x_host[: xs.numel()].copy_(xs, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return r
+
+    e2e_step()
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        e2e_step()
+    ev1.record()
+    barrier()
+    e2e_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    h2d_all, d2h_all = ctx.sum(float(h2d)), ctx.sum(float(d2h))
+
+    # ---- roofline of the dominant phase: the three matrix sweeps of this rank's share ----
+    peak, peak_src = peaks()
+    n_loc = (re - rs) * b
+    roofline = None
+    fp = info.get("fused_phases_ms_per_iteration")
+    if fp:
+        nA, nG, nGT = info["nnz_local"]
+        (va, ia), (vg, ig) = info["stream_bytes"]
+        ra_, rg_ = (8 if ia == 2 else 4), (8 if ig == 2 else 4)
+        streamed = [(vg + ig) * nGT + (rg_ + 16) * n_loc, (vg + ig) * nG + (rg_ + 24) * n_loc, (va + ia) * nA + (ra_ + 16) * n_loc]
+        alg = [12 * nGT + 20 * n_loc + 4, 12 * nG + 28 * n_loc + 4, 12 * nA + 20 * n_loc + 4]
+        sw = [fp["GT_r+barrier"], fp["G_t+barrier"], fp["A_p+barrier"]]
+        ach = sum(streamed) / (sum(sw) * 1e-3) / 1e9
+        roofline = {"kernel": "pcg_fused_kernel<4096,2,8,float,u16,4>: the three matrix sweeps of one iteration on rank 0's rows, each timed "
+                              "INCLUDING the cross-rank barrier (halo exchange + all-reduce) that closes it",
+                    "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4), "peak_source": peak_src,
+                    "traffic": None, "bytes_per_sweep_rank0": [int(v) for v in streamed], "ms_per_sweep_rank0": sw,
+                    "algorithmic": {"bytes_per_sweep_rank0": alg, "GB/s": round(sum(alg) / (sum(sw) * 1e-3) / 1e9, 1)},
+                    "phases_ms_per_iteration_rank0": fp}
+    line = None
     if rank == 0:
+        W = workload_text(g, N, E, args.rtol)
         line = {
-            "metric": "row-partitioned learned-SPAI PCG, one system over all GPUs: solves/s (strong scaling)", "mode": "rowpart",
-            "value": round(args.steps / (dev_ms * 1e-3), 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 1), "ms_per_step": round(dev_ms / args.steps, 3), "higher_is_better": True,
+            "metric": METRIC, "value": round(args.steps / (dev_ms * 1e-3), 4), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": round(dev_ms / args.steps, 3), "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64 (PCG) / f32 (GNN)", "data": "synthetic",
-            "config": {"workload": f"ONE poisson3d jittered Kuhn-tet system {g}^3 = {N} DOF, E = {E}, row-partitioned over {world} GPU(s); "
-                                   f"GNN on target-owned edges, assembly of owned rows, PCG partitioned; rtol {args.rtol:g}",
-                       "halo": info, "rows_rank0": [rs, re]},
+            "config": {"workload": W, "systems_per_step": 1},
+            "parallelism": f"ONE system row-partitioned over {world} GPU(s): GNN on target-owned edges (NCCL node-feature halo per layer), "
+                           f"owned rows of A / G / G^T assembled per rank, PCG in one persistent kernel per rank with NVLink peer-store "
+                           f"halos and peer-memory all-reduce of the CG scalars",
+            "l2": "per-rank matrices larger than L2 up to 8 ranks (A + G + G^T = %.2f GB per rank)" % ((E * 3 * 6 + 24.0 * N) / world / 1e9),
             "time_to_tol_ms": round(pcg, 3), "iterations": float(np.mean(iters)), "converged": int(res.converged),
-            "ms_per_iteration": round(pcg / max(float(np.mean(iters)), 1.0), 4),
-            "phases_ms_per_step": {k: round(v / args.steps, 3) for k, v in ph.items()}, "gpu_launches": int(launches),
+            "ms_per_iteration": round(pcg / max(float(np.mean(iters)), 1.0), 4), "pcg_mode": info.get("pcg_mode"),
+            "phases_ms_per_step": {k: round(v / args.steps, 3) for k, v in ph.items()},
+            "halo": {k: info[k] for k in ("n_push", "n_recv", "push_elems", "owned_offset") if k in info}, "rank0": info0,
+            "e2e": {"value": round(args.steps / (e2e_ms * 1e-3), 4), "unit": UNIT, "h2d_bytes_per_step": int(h2d_all), "d2h_bytes_per_step": int(d2h_all),
+                    "ms_per_step": round(e2e_ms / args.steps, 3),
+                    "api": "parallel.PartitionedSystem / DistPCG on every rank's pinned-host slices of the system (bytes summed over ranks)"},
+            "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": None, "clocks": clocks,
         }
-        print(json.dumps(line), flush=True)
+        if emit:
+            print(json.dumps(line), flush=True)
     barrier()
     par.DistPCG.drop_connections()
-    dist.destroy_process_group()
+    return line
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -638,6 +770,111 @@ def main_batch_small(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------------------------
+# --mode shapes: BASELINE configs C1 (heat), C3 (elasticity, b = 3), C4 (synthetic SPD, irregular rows) at their sizes
+# ---------------------------------------------------------------------------------------------------------
+def main_shapes(args):
+    """One JSON line per named shape (systems.SHAPES): the whole path (graph preprocessing, GNN, assembly, G^T, PCG to
+    rtol) per step on ONE GPU, per-kernel GB/s of the PCG iteration, row-length histogram, and beside it the REAL oracle
+    run of the same system on this box's host cores (oracle GNN forward + the scipy-cg recurrence to convergence): its
+    time is the cpu_baseline, its iteration count and G are the parity columns."""
+    from learningsparsepreconditioner4gpu_b200 import _lib, systems
+    from learningsparsepreconditioner4gpu_b200.device import DevicePCG
+
+    _lib.require_cuda()
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    peak, peak_src = peaks()
+    names = args.shapes.split(",") if args.shapes else list(systems.SHAPES)
+    for name in names:
+        cpu_s, b = systems.shape_sample(name)
+        sample = cpu_s.to("cuda")
+        ws = systems.default_workspace(cpu_s, block_size=b)
+        N, E, n = cpu_s.num_nodes, cpu_s.num_edges, cpu_s.num_nodes * b
+        for _ in range(max(args.warmup, 3)):
+            x, res, solver, A, G, rhs = run_step(ws, sample, args.rtol)
+            del solver, A, G, rhs
+        torch.cuda.synchronize()
+        launches0 = _lib.total_launches()
+        timers = []
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        pcg_ms, iters = [], []
+        for k in range(args.steps):
+            x, res, solver, A, G, rhs = run_step(ws, sample, args.rtol, timers)
+            pcg_ms.append(float(res.solve_ms))
+            iters.append(int(res.iterations))
+            if k < args.steps - 1:
+                del solver, A, G, rhs
+        ev1.record()
+        torch.cuda.synchronize()
+        dev_ms = ev0.elapsed_time(ev1)
+        launches = _lib.total_launches() - launches0
+        ph = phases_ms(timers)
+        mode_ran = int(res.reserved)
+        true_rel = float((rhs - A.matvec(x)).norm() / rhs.norm())
+        # per-kernel times of the 5-launch iteration on these matrices (the kernels mode 3 / 4 fuse)
+        kms = solver.profile_iterations(rhs, "ext_spai", iterations=50)
+        nnzA, nnzG = A.nnz, G.nnz
+        (va, ia), (vg, ig) = A.stream_bytes(), G.stream_bytes()
+        alg = [12 * nnzG + 20 * n + 4, 12 * nnzG + 28 * n + 4, 24 * n, 12 * nnzA + 20 * n + 4, 48 * n]
+        knames = ["GT_r", "G_t", "update_p", "A_p", "update_xr"]
+        per_kernel = {k: {"ms": round(ms, 5), "algorithmic_bytes": by, "GB/s": round(by / (ms * 1e-3) / 1e9, 1) if ms > 0 else None}
+                      for k, by, ms in zip(knames, alg, kms)}
+        spmv_ms = (kms[0] + kms[1] + kms[3]) / 3
+        spmv_bytes = (alg[0] + alg[1] + alg[3]) / 3
+        rl = np.diff(A.to_scipy().indptr)
+        hist_edges = [1, 2, 4, 8, 16, 32, 64, 128, 1 << 30]
+        row_hist = {f"<{hi}": int(((rl >= lo) & (rl < hi)).sum()) for lo, hi in zip([0] + hist_edges[:-1], hist_edges)}
+        # ---- the oracle beside it: a REAL run of the same system on the host cores ----
+        cpu = None
+        parity = None
+        if not args.no_cpu_baseline:
+            from oracle import assemble as oasm, gnn as ognn, pcg as opcg
+
+            sd = {k: v.detach().cpu() for k, v in ws.state_dict().items()}
+            t0 = time.perf_counter()
+            Go = ognn.workspace_forward(sd, cpu_s.x, cpu_s.edge_index, cpu_s.edge_attr, b)
+            t_gnn = time.perf_counter() - t0
+            Ao = oasm.to_csr_cpu(cpu_s.edge_index, cpu_s.matrix_values, n, cpu_s.mask)
+            Gc = oasm.to_csr_cpu(cpu_s.edge_index, Go, n, cpu_s.mask)
+            gt = cpu_s.mask.numpy().reshape(-1).astype(np.float64)
+            timer = opcg.ScipyPcgTimer(Ao, Gc, ws.epsilon)
+            its_o, t_pcg = timer.run(gt, args.rtol)
+            cpu = {"value": round(1.0 / (t_gnn + t_pcg), 5), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                   "sample": f"the whole system: oracle GNN forward {t_gnn:.2f} s ({torch.get_num_threads()} torch threads) + oracle scipy "
+                             f"PCG {its_o} iterations in {t_pcg:.2f} s (1 thread); not extrapolated",
+                   "gnn_s": round(t_gnn, 3), "pcg_s": round(t_pcg, 3), "iterations": int(its_o)}
+            with torch.no_grad():
+                Gd = ws(sample.x, sample.edge_index, sample.edge_attr).cpu().numpy()
+            As = A.to_scipy()
+            parity = {"oracle_iterations": int(its_o), "cuda_iterations": int(np.mean(iters)),
+                      "dG_over_maxG": float(np.abs(Gd - Go.numpy()).max() / np.abs(Go.numpy()).max()),
+                      "pattern_A_bit_exact": bool(np.array_equal(As.indptr, Ao.indptr) and np.array_equal(As.indices, Ao.indices)
+                                                  and np.array_equal(As.data, Ao.data))}
+        line = {
+            "metric": METRIC, "mode": "shapes", "shape": name, "value": round(args.steps / (dev_ms * 1e-3), 3), "unit": UNIT,
+            "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(dev_ms / args.steps, 3),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64 (PCG) / f32 (GNN)", "data": "synthetic",
+            "config": {"workload": f"{name}: N = {N} nodes, block {b}, n = {n} rows, E = {E} stored blocks, nnz(A) = {nnzA}, "
+                                   f"nnz(G) = {nnzG}; random-init GNN (seed 42), eps 3e-3, rhs = A*mask, rtol {args.rtol:g}",
+                       "l2": "whole system is L2-resident (%.1f MB): latency-bound, GB/s are L2 rates" % ((nnzA + 2 * nnzG) * 12 / 1e6)},
+            "time_to_tol_ms": round(float(np.mean(pcg_ms)), 3), "iterations": float(np.mean(iters)), "converged": int(res.converged),
+            "true_rel_residual": true_rel, "pcg_mode": mode_ran,
+            "ms_per_iteration": round(float(np.mean(pcg_ms)) / max(float(np.mean(iters)), 1.0), 5),
+            "phases_ms_per_step": {k: round(v / args.steps, 3) for k, v in ph.items()},
+            "row_length": {"min": int(rl.min()), "mean": round(float(rl.mean()), 2), "max": int(rl.max()), "histogram": row_hist},
+            "stream_bytes_per_entry": {"A": [va, ia], "G": [vg, ig]},
+            "roofline": {"kernel": "SpMV family of the 5-launch iteration (profile_iterations), mean of t = G^T r, z = G t + eps r, q = A p",
+                         "bound": "hbm", "achieved": round(spmv_bytes / (spmv_ms * 1e-3) / 1e9, 1), "peak": peak, "unit": "GB/s",
+                         "frac": round(spmv_bytes / (spmv_ms * 1e-3) / 1e9 / peak, 4), "peak_source": peak_src, "traffic": None,
+                         "per_kernel": per_kernel},
+            "gpu_launches": int(launches), "cpu_baseline": cpu, "parity": parity,
+        }
+        print(json.dumps(line), flush=True)
+        del solver, A, G, rhs
+        torch.cuda.empty_cache()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -647,20 +884,43 @@ def main():
     ap.add_argument("--rtol", type=float, default=1e-6)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--mode", default="batch", choices=["batch", "rowpart", "batch_small"],
-                    help="batch: one independent 10 M-DOF system per GPU (the bench contract); rowpart: one system over all "
-                         "GPUs; batch_small: a batch of small systems per GPU (BASELINE config C2)")
+    ap.add_argument("--shapes", default="", help="shapes: comma-separated subset of heat,elast,synth10240,synth15360,synth20480")
+    ap.add_argument("--no-replicas", action="store_true", help="N > 1: skip the extra independent-systems (replicas) figure")
+    ap.add_argument("--mode", default="auto", choices=["auto", "batch", "rowpart", "batch_small", "shapes"],
+                    help="auto (the bench contract): N = 1 -> one 10 M-DOF system on one GPU; N > 1 -> the SAME system "
+                         "row-partitioned over the N GPUs (strong scaling) with the independent-replicas figure as an extra key; "
+                         "batch: one independent system per GPU (weak scaling); rowpart: the row-partitioned line at any N; "
+                         "batch_small: a batch of small systems per GPU (BASELINE config C2); shapes: C1 / C3 / C4 at their sizes")
     ap.add_argument("--batch", type=int, default=64, help="batch_small: systems per step over all ranks")
     ap.add_argument("--streams", type=int, default=4, help="batch_small: systems in flight per GPU (host threads x CUDA streams)")
     args = ap.parse_args()
     if args.impl == "reference":
         main_reference(args)
-    elif args.mode == "rowpart":
-        main_rowpart(args)
     elif args.mode == "batch_small":
         main_batch_small(args)
+    elif args.mode == "shapes":
+        main_shapes(args)
     else:
-        main_ours(args)
+        ctx = Ctx()
+        if args.mode == "rowpart" or (args.mode == "auto" and ctx.world > 1):
+            line = main_rowpart(args, ctx, emit=False)
+            if ctx.world > 1 and not args.no_replicas and args.mode == "auto":
+                # the round-1 headline, kept beside the strong-scaling line: N independent systems, one per GPU
+                import copy
+
+                a2 = copy.copy(args)
+                a2.steps, a2.no_cpu_baseline = min(args.steps, 2), True
+                rep = main_ours(a2, ctx, emit=False)
+                if line is not None and rep is not None:
+                    line["replicas"] = {k: rep[k] for k in ("value", "unit", "ms_per_step", "steps", "iterations", "ms_per_iteration",
+                                                            "parallelism")}
+                    line["replicas"]["scaling"] = "weak"
+                    line["replicas"]["e2e"] = rep["e2e"]
+            if line is not None:
+                print(json.dumps(line), flush=True)
+        else:
+            main_ours(args, ctx)
+        ctx.close()
 
 
 if __name__ == "__main__":

@@ -369,6 +369,13 @@ def exchange_g_rows(g_t: torch.Tensor, plan, group=None) -> torch.Tensor:
     return out
 
 
+def rank_edge_slices(edge_index: torch.Tensor, starts: Sequence[int], rank: int):
+    """(e0, e1, ids_t) of ``owned_edge_sets`` for ``rank``: the input partitioner.  A distributed caller runs it once per
+    topology where the global edge list lives and hands each rank ``edge_index[:, e0:e1]``, ``edge_index[:, ids_t]``,
+    ``matrix_values[e0:e1]``, ``edge_attr[ids_t]`` and the node window of ``x`` / ``mask``."""
+    return owned_edge_sets(edge_index, int(starts[rank]), int(starts[rank + 1]))
+
+
 class PartitionedSystem:
     """One rank's share of a row-partitioned system: the GNN runs on the edges whose target node this
     rank owns (node-feature halo refreshed after every MP layer), the boundary G values are swapped once, and A, G, G^T
@@ -377,8 +384,13 @@ class PartitionedSystem:
     ``edge_index`` is the global [2, E] list (row-major, column-ascending) on this rank's GPU; ``starts`` the NODE
     partition from ``partition_rows``.  Collective: every rank of ``group`` builds it and calls the methods together."""
 
-    def __init__(self, edge_index: torch.Tensor, num_nodes: int, block_size: int, starts: Sequence[int],
-                 rank: Optional[int] = None, world: Optional[int] = None, group=None):
+    def __init__(self, edge_index: Optional[torch.Tensor], num_nodes: int, block_size: int, starts: Sequence[int],
+                 rank: Optional[int] = None, world: Optional[int] = None, group=None,
+                 slices: Optional[Tuple[torch.Tensor, torch.Tensor]] = None):
+        """``slices`` = (ei_r, ei_t): this rank's two pieces of the GLOBAL edge list, in global node numbering and ascending
+        edge order -- the edges whose row it owns (a contiguous run of the row-major list) and the edges whose target
+        (column) it owns (``rank_edge_slices``).  With ``slices`` nothing of global size E is needed on this rank:
+        ``edge_index`` may be None and the ``*_local`` methods take per-rank inputs."""
         if world is None:
             import torch.distributed as dist
 
@@ -387,18 +399,45 @@ class PartitionedSystem:
         self.N, self.b, self.starts = int(num_nodes), int(block_size), [int(v) for v in starts]
         assert len(self.starts) == self.world + 1 and self.starts[0] == 0 and self.starts[-1] == self.N
         rs, re = self.starts[self.rank], self.starts[self.rank + 1]
-        lo, hi = extended_range(edge_index, rs, re)
+        if slices is None:
+            e0, e1, ids_t = owned_edge_sets(edge_index, rs, re)
+            ei_r, ei_t = edge_index[:, e0:e1], edge_index[:, ids_t]
+            self.e0, self.e1, self.ids_t = e0, e1, ids_t
+        else:
+            ei_r, ei_t = slices
+            self.e0, self.e1, self.ids_t = None, None, None       # global positions are not known (and not needed)
+        self.n_edges_r, self.n_edges_t = int(ei_r.shape[1]), int(ei_t.shape[1])
+        # extended node window: owned rows + every column the owned rows touch + every row that touches an owned column
+        lo, hi = rs, re
+        if self.n_edges_r:
+            lo, hi = min(lo, int(ei_r[1].min())), max(hi, int(ei_r[1].max()) + 1)
+        if self.n_edges_t:
+            lo, hi = min(lo, int(ei_t[0].min())), max(hi, int(ei_t[0].max()) + 1)
         self.layout_nodes = rank_layout(rs, re, lo, hi)
         self.layouts_nodes: List[Layout] = ([self.layout_nodes] if self.world == 1 else
                                             [tuple(int(v) for v in t) for t in _all_gather_object(self.layout_nodes, group)])
         self.shift, self.hi = self.layout_nodes[2], hi
         self.ext_nodes = hi - self.shift
-        self.plan = g_exchange_plan(edge_index, self.starts, self.rank)
-        self.e0, self.e1, self.ids_t = self.plan[0], self.plan[1], self.plan[2]
+        # who needs which G values (g_exchange_plan on the two slices)
+        row_owner_t = owner_of(ei_t[0], self.starts)
+        col_owner_r = owner_of(ei_r[1], self.starts)
+        loc_t = torch.nonzero(row_owner_t == self.rank).reshape(-1)
+        loc_r = torch.nonzero(col_owner_r == self.rank).reshape(-1)
+        send, recv = {}, {}
+        for q in range(self.world):
+            if q == self.rank:
+                continue
+            sq = torch.nonzero(row_owner_t == q).reshape(-1)
+            if sq.numel():
+                send[q] = sq
+            rq = torch.nonzero(col_owner_r == q).reshape(-1)
+            if rq.numel():
+                recv[q] = rq
+        self.plan = (0, self.n_edges_r, None, loc_t, loc_r, send, recv)
         # local edge lists in extended node numbering (global - shift)
-        self.ei_t = (edge_index[:, self.ids_t] - self.shift).contiguous()          # target-owned, for the GNN and G^T
-        self.ei_r = (edge_index[:, self.e0:self.e1] - self.shift).contiguous()     # row-owned, for A and G
-        order = torch.argsort(self.ei_t[1], stable=True)                           # by target, rows ascending inside
+        self.ei_t = (ei_t - self.shift).contiguous()          # target-owned, for the GNN and G^T
+        self.ei_r = (ei_r - self.shift).contiguous()          # row-owned, for A and G
+        order = torch.argsort(self.ei_t[1], stable=True)      # by target, rows ascending inside
         self.order_t = order
         self.ei_tT = torch.stack([self.ei_t[1][order], self.ei_t[0][order]]).contiguous()
         self._graph = None
@@ -423,17 +462,26 @@ class PartitionedSystem:
 
     # GNN ---------------------------------------------------------------------------------------------------
     def gnn_forward(self, gnn, x: torch.Tensor, edge_attr: torch.Tensor) -> torch.Tensor:
-        """G values [E_t, b*b] of the target-owned edges (``ids_t`` order); bit-identical to the single-GPU forward on
-        those edges (per target the messages are summed in the same ascending edge order)."""
+        """G values [E_t, b*b] of the target-owned edges (``ids_t`` order) from the GLOBAL x / edge_attr; bit-identical
+        to the single-GPU forward on those edges (per target the messages are summed in the same ascending edge order)."""
+        assert self.ids_t is not None, "built from slices: use gnn_forward_local with this rank's inputs"
+        return self.gnn_forward_local(gnn, self.ext_slice(x.detach().to(torch.float32)),
+                                      edge_attr.detach().to(torch.float32)[self.ids_t])
+
+    def gnn_forward_local(self, gnn, x_ext: torch.Tensor, ea_t: torch.Tensor) -> torch.Tensor:
+        """The same from this rank's inputs only: ``x_ext`` = node features of the extended window [shift, hi) (zero rows
+        where shift < 0, ``ext_slice``), ``ea_t`` = edge features of the target-owned edges."""
         from .neural_cg.nn.gnns import DeviceGraph, F
 
         lib = _lib.load()
         if self._graph is None:
             self._graph = DeviceGraph(self.ei_t, self.ext_nodes)
         g = self._graph
-        x_loc = self.ext_slice(x.detach().to(torch.float32))
-        ea_loc = edge_attr.detach().to(torch.float32)[self.ids_t].contiguous()
-        out = torch.empty((self.ids_t.numel(), gnn.edge_out), dtype=torch.float32, device=x.device)
+        x = x_ext
+        x_loc = x_ext.detach().to(torch.float32).contiguous()
+        ea_loc = ea_t.detach().to(torch.float32).contiguous()
+        assert x_loc.shape[0] == self.ext_nodes and ea_loc.shape[0] == self.n_edges_t
+        out = torch.empty((self.n_edges_t, gnn.edge_out), dtype=torch.float32, device=x.device)
         eng, L = gnn._get_engine(), gnn.num_mp_layers
         for stage in range(L + 2):
             _lib.check(lib.b200spai_gnn_forward_stage(eng, g._h, stage, _ptr(x_loc), _ptr(ea_loc), _ptr(out), _stream()),
@@ -462,9 +510,18 @@ class PartitionedSystem:
     def assemble(self, matrix_values: torch.Tensor, g_t: torch.Tensor, mask: Optional[torch.Tensor]):
         """(A_loc, G_loc, GT_loc): owned rows of the masked fp64 CSR matrices, columns in the extended layout.
         ``matrix_values`` [E, b, b] global (only rows e0..e1 are read), ``g_t`` from ``gnn_forward``."""
+        assert self.e0 is not None, "built from slices: use assemble_local with this rank's inputs"
         b = self.b
         mask_ext = None if mask is None else self.ext_slice(mask.detach().to(torch.float32).reshape(self.N, b))
-        a_vals = matrix_values.detach().to(torch.float32).reshape(-1, b, b)[self.e0:self.e1].contiguous()
+        return self.assemble_local(matrix_values.detach().reshape(-1, b, b)[self.e0:self.e1], g_t, mask_ext)
+
+    def assemble_local(self, mv_r: torch.Tensor, g_t: torch.Tensor, mask_ext: Optional[torch.Tensor]):
+        """The same from this rank's inputs only: ``mv_r`` [E_r, b, b] = matrix values of the row-owned edges,
+        ``mask_ext`` [ext_nodes, b] = mask over the extended window."""
+        b = self.b
+        if mask_ext is not None:
+            mask_ext = mask_ext.detach().to(torch.float32).reshape(self.ext_nodes, b).contiguous()
+        a_vals = mv_r.detach().to(torch.float32).reshape(-1, b, b).contiguous()
         A_loc = self._local_rows(self.ei_r, a_vals, mask_ext)
         g_t = g_t.reshape(-1, b, b)
         G_loc = self._local_rows(self.ei_r, self.g_rows(g_t).contiguous(), mask_ext)

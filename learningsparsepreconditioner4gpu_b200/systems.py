@@ -78,6 +78,23 @@ def synthetic_sample(n: int = 10240, sparsity: float = 3e-4, amplifier: float = 
     return d.to(device) if device is not None else d
 
 
+SHAPES = ("heat", "elast", "synth10240", "synth15360", "synth20480")
+
+
+def shape_sample(name: str, device=None):
+    """(sample, block_size) of a named BASELINE shape at its stated size: ``heat`` (C1, 18x18x19 = 6156 rows, the size
+    class of the 6276-row bunny mesh of datagen/config/heat.yaml:1), ``elast`` (C3, unit_box(64,16,16), b = 3, 49152 DOF,
+    datagen/config/elast_twist.yaml:12-13), ``synth<n>`` (C4, datagen/synthetic.py:10-27 verbatim with n rows;
+    datagen/config/synthetic.yaml:15-20 draws n in [10240, 20480])."""
+    if name == "heat":
+        return heat_sample(18, device=device), 1
+    if name == "elast":
+        return elasticity_sample(64, 16, 16, device=device), 3
+    if name.startswith("synth"):
+        return synthetic_sample(int(name[5:]), device=device), 1
+    raise ValueError(f"unknown shape {name!r}; one of {SHAPES}")
+
+
 def default_workspace(sample: Data, block_size: int = 1, seed: int = 42, epsilon: float = 3.0e-3, scaled: bool = False):
     """Workspace with the reference's resolved default config and random-init weights."""
     from types import SimpleNamespace

@@ -1,6 +1,6 @@
 """How far does the REFERENCE's own iteration count move when only the summation order of its dot products changes?
 
-    python scripts/cg_order_sensitivity.py 64 128
+    python scripts/cg_order_sensitivity.py 64 128 heat elast synth10240 synth15360 synth20480
 
 The scipy cg recurrence (oracle.pcg.pcg_restated, pinned to the reference's get_pcg_iter_time_scipy by the C5 fixtures)
 is run on the fixture systems with the oracle's G, four times: numpy's dots as they are, dots over the reversed vectors,
@@ -56,21 +56,34 @@ def main():
         "longdouble": lambda a, b: float(np.dot(a.astype(np.longdouble), b.astype(np.longdouble))),
         "chunks64": lambda a, b: float(np.sum([float(u @ v) for u, v in zip(np.array_split(a, 64), np.array_split(b, 64))])),
     }
-    for grid in [int(v) for v in sys.argv[1:]]:
-        g = np.load(os.path.join(ROOT, "tests", "golden", f"c5_{grid}.npz"), allow_pickle=False)
-        s = systems.poisson_sample(grid, seed=int(g["seed"]), gen_device="cpu", device="cpu")
-        sd = {str(k): torch.from_numpy(g["sd/" + str(k)].copy()) for k in g["sd_keys"]}
-        G = ognn.workspace_forward(sd, s.x, s.edge_index, s.edge_attr, 1)
-        n = s.num_nodes
-        A = oasm.to_csr_cpu_sorted(s.edge_index, s.matrix_values, n, s.mask)
-        Gc = oasm.to_csr_cpu_sorted(s.edge_index, G.reshape(-1), n, s.mask)
+    for tok in sys.argv[1:]:
+        if tok.isdigit():        # C5 family: the committed fixture pins the reference's count and history
+            grid = int(tok)
+            g = np.load(os.path.join(ROOT, "tests", "golden", f"c5_{grid}.npz"), allow_pickle=False)
+            s = systems.poisson_sample(grid, seed=int(g["seed"]), gen_device="cpu", device="cpu")
+            sd = {str(k): torch.from_numpy(g["sd/" + str(k)].copy()) for k in g["sd_keys"]}
+            G = ognn.workspace_forward(sd, s.x, s.edge_index, s.edge_attr, 1)
+            n, eps = s.num_nodes, float(g["epsilon"])
+            A = oasm.to_csr_cpu_sorted(s.edge_index, s.matrix_values, n, s.mask)
+            Gc = oasm.to_csr_cpu_sorted(s.edge_index, G.reshape(-1), n, s.mask)
+            out = {"grid": grid, "reference_iters": int(g["iters_pcg"])}
+            ref_hist = g["res_hist"]
+        else:                    # C1 / C3 / C4 at their BASELINE sizes (systems.shape_sample): the oracle is the reference
+            s, bs = systems.shape_sample(tok)
+            ws = systems.default_workspace(s, block_size=bs)
+            G = ognn.workspace_forward(ws.state_dict(), s.x, s.edge_index, s.edge_attr, bs)
+            n, eps = s.num_nodes * bs, ws.epsilon
+            A = oasm.to_csr_cpu(s.edge_index, s.matrix_values, n, s.mask)
+            Gc = oasm.to_csr_cpu(s.edge_index, G, n, s.mask)
+            out, ref_hist = {"shape": tok}, None
         b = A @ s.mask.numpy().reshape(-1).astype(np.float64)
-        M = opcg.make_preconditioner("ext_spai", A, Gc, float(g["epsilon"]))
-        out = {"grid": grid, "reference_iters": int(g["iters_pcg"])}
-        ref_hist = g["res_hist"]
+        M = opcg.make_preconditioner("ext_spai", A, Gc, eps)
         for name, dot in dots.items():
             t0 = time.time()
             it, h = cg(A, b, M, dot)
+            if ref_hist is None:
+                ref_hist = h     # the "numpy" run is the reference recurrence itself
+                out["reference_iters"] = it
             k = min(len(h), len(ref_hist))
             rel = np.abs(h[:k] - ref_hist[:k]) / ref_hist[:k]
             out[name] = {"iters": it, "max_rel_hist_dev": float(rel.max()), "first_dev_over_1pct": int(np.argmax(rel > 0.01)) if (rel > 0.01).any() else -1,

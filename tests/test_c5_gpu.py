@@ -12,10 +12,12 @@ is driven by the CUDA-graph WHILE loop (mode 2) or by the fused persistent kerne
   * scipy directly, for the operator z = G (G^T r) [/ d] + eps r [/ d] and for the fallback streams (fp64 values, int32
     columns).
 
-Bars (stated where asserted): G within 1e-5 of max|G|; iteration count within +-1 of the reference's on the REFERENCE's
-G (oracle-recomputed) and on the CUDA G; history entries 0..5 to 1e-12 on identical G; whole history inside the reference
-history's +-2-iteration envelope widened by 25 % (see tests/test_pcg_gpu.py for why later entries cannot agree to
-digits); solution samples to 1e-4 of max|x|."""
+Bars (stated where asserted): G within 1e-5 of max|G|; history entries 0..5 to 1e-12 on identical G; solution samples to
+1e-4 of max|x|; iteration count on the REFERENCE's G (oracle-recomputed) and on the CUDA G within IT_TOL of the
+reference's: +-1 at 64^3 (234 iterations); at 128^3 (522 iterations) the reference's own count is only defined up to
+-3 .. +7 -- that is how far its recurrence moves when nothing but the summation order of its dot products changes
+(scripts/cg_order_sensitivity.py -> profiles/r02_cg_order_sensitivity.jsonl: 529 / 519 / 520 against 522, histories apart
+by > 1 % from iteration 23) -- so the stated tolerance there is +-7 and the measured delta is printed (-2 .. 0)."""
 import os
 
 import numpy as np
@@ -29,6 +31,7 @@ from test_pcg_gpu import history_within_envelope
 pytestmark = pytest.mark.gpu
 
 MODES = (2, 4)  # graph WHILE driver, fused persistent kernel
+IT_TOL = {64: 1, 128: 7}
 
 
 def _close(a, b, rel):
@@ -67,10 +70,12 @@ def _solve_and_check(g, A, G, b, eps, mode, same_G):
     dit = res.iterations - ref_it
     print(f"[c5 grid={int(g['grid'])} mode={mode} {'reference G' if same_G else 'CUDA G'}] iterations {res.iterations} "
           f"vs reference {ref_it} (delta {dit:+d})")
-    assert abs(dit) <= 1, (res.iterations, ref_it)
+    assert abs(dit) <= IT_TOL[int(g["grid"])], (res.iterations, ref_it)
     h = hist.cpu().numpy()
     assert np.allclose(h[:6], ref_hist[:6], rtol=1e-12 if same_G else 1e-4)
-    assert history_within_envelope(h, ref_hist, shift=2, slack=0.25) == []
+    if ref_it <= 250:      # beyond that two correctly rounded runs are > 10 % apart entry by entry (see the module docstring)
+        assert history_within_envelope(h, ref_hist, shift=2, slack=0.25) == []
+    assert h[-1] < 1e-6 * h[0] <= h[-2]
     xs = x.cpu().numpy()
     assert np.allclose(xs[g["x_sample_ids"]], g["x_samples"], rtol=0, atol=1e-4 * float(g["xsol_max_abs"]))
     r = b - A.matvec(x)
@@ -109,8 +114,6 @@ def test_c5_golden_gnn_and_pcg_on_the_timed_path(grid):
     # ---- PCG on the CUDA G, both large-system drivers ----
     for mode in MODES:
         _solve_and_check(g, A, G, b, eps, mode, same_G=False)
-    if grid > 64:
-        return
     # ---- PCG on the REFERENCE's G: the oracle forward recomputed on the host cores, pinned by the fixture's samples ----
     from oracle import gnn as ognn
 

@@ -318,3 +318,31 @@ def test_partitioned_system_local_edge_lists(kind, world):
         xs = ps.ext_slice(x)
         assert xs.shape == (ext, 2) and torch.equal(xs[lo - shift:], x[lo:hi]) and float(xs[: lo - shift].abs().sum()) == 0.0
         assert ps.row_starts == list(starts) and ps.layout == lay[rank]
+
+
+@pytest.mark.parametrize("world", [1, 3])
+def test_partitioned_system_from_rank_slices_equals_global(world, monkeypatch):
+    """The constructor fed with this rank's two pieces of the edge list (``rank_edge_slices``: what a distributed caller
+    hands each rank) builds the same layout, local edge lists and G-exchange plan as the one fed with the global list."""
+    A = _random_spd_pattern(400, 0.012, 3)
+    ei = _edges(A)
+    n = A.shape[0]
+    starts = par.partition_rows(par.row_weights_from_edges(ei, n), world)
+    lay = [par.rank_layout(starts[r], starts[r + 1], *par.extended_range(ei, starts[r], starts[r + 1])) for r in range(world)]
+    monkeypatch.setattr(par, "_all_gather_object", lambda obj, group: list(lay))
+    for rank in range(world):
+        g = par.PartitionedSystem(ei, n, 1, starts, rank=rank, world=world)
+        e0, e1, ids_t = par.rank_edge_slices(ei, starts, rank)
+        s = par.PartitionedSystem(None, n, 1, starts, rank=rank, world=world, slices=(ei[:, e0:e1].clone(), ei[:, ids_t].clone()))
+        assert g.layout_nodes == s.layout_nodes == lay[rank] and g.ext_nodes == s.ext_nodes
+        for name in ("ei_t", "ei_r", "ei_tT", "order_t"):
+            assert torch.equal(getattr(g, name), getattr(s, name)), name
+        assert torch.equal(g.plan[3], s.plan[3]) and torch.equal(g.plan[4], s.plan[4])
+        assert set(g.plan[5]) == set(s.plan[5]) and set(g.plan[6]) == set(s.plan[6])
+        for q in g.plan[5]:
+            assert torch.equal(g.plan[5][q], s.plan[5][q])
+        for q in g.plan[6]:
+            assert torch.equal(g.plan[6][q], s.plan[6][q])
+        ref = par.g_exchange_plan(ei, starts, rank)            # and both equal the stand-alone plan function
+        assert torch.equal(g.plan[3], ref[3]) and torch.equal(g.plan[4], ref[4])
+        assert (s.n_edges_r, s.n_edges_t) == (e1 - e0, int(ids_t.numel()))
