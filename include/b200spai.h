@@ -92,6 +92,21 @@ int b200spai_csr_diagonal(b200spai_csr_t a, double* diag_dev, void* stream);
  * ---------------------------------------------------------------------------------------------- */
 int b200spai_edges_to_csr(int64_t num_nodes, int64_t num_edges, int32_t block_size, const int64_t* edge_index_dev,
                           const float* values_dev, const float* mask_dev, void* stream, b200spai_csr_t* out);
+/* Fixed topology (the reference's default, config/data.yaml `is_fixed_topology: True`: every sample of a dataset shares
+ * one edge_index and one mask; only the values change).  _plan = b200spai_edges_to_csr that also records, per stored
+ * entry, which edge value it holds, and the list of entries dropped because their value was exactly 0.
+ * b200spai_csr_refresh_from_edges then re-fills the SAME matrix (pattern, row blocks, compressed streams all kept) from a
+ * new [E,b,b] value array in one gather pass.  ok = 0 when an exact zero appeared or disappeared among the values -- the
+ * reference's pattern would differ (validate.py:37-51 drops exact zeros), the matrix content is then undefined and the
+ * caller rebuilds it.  Masks with entries other than 0 / 1 get no plan (b200spai_csr_has_plan -> kind 0).
+ * kind: 0 = none, 1 = from edges, 2 = transpose of a planned matrix. */
+int b200spai_edges_to_csr_plan(int64_t num_nodes, int64_t num_edges, int32_t block_size, const int64_t* edge_index_dev,
+                               const float* values_dev, const float* mask_dev, void* stream, b200spai_csr_t* out);
+int b200spai_csr_has_plan(b200spai_csr_t a, int32_t* kind);
+int b200spai_csr_refresh_from_edges(b200spai_csr_t a, const float* values_dev, int64_t num_values, void* stream, int32_t* ok);
+/* B = A^T keeping the permutation, and the value-only refresh of B after A's values changed. */
+int b200spai_csr_transpose_plan(b200spai_csr_t a, void* stream, b200spai_csr_t* out);
+int b200spai_csr_refresh_transposed(b200spai_csr_t t, b200spai_csr_t a, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * PCG.  Replaces pymathprim.linalg.PreconditionedConjugateGradient as the reference calls it
@@ -122,6 +137,9 @@ int b200spai_pcg_create(b200spai_csr_t a, b200spai_pcg_t* out);
 /* Attach G (the `ext_spai=(spai, epsilon)` argument, validate.py:117).  G^T is built on the device.
  * The solver keeps references to g (must outlive it) and owns G^T. */
 int b200spai_pcg_set_spai(b200spai_pcg_t s, b200spai_csr_t g, double epsilon, void* stream);
+/* The values of A and / or G were refreshed in place (b200spai_csr_refresh_from_edges): re-gathers G^T and drops the
+ * cached diagonal.  Patterns, captured graphs and workspaces are kept. */
+int b200spai_pcg_refresh(b200spai_pcg_t s, void* stream);
 /* mode: 0 = auto (3 for systems of <= 131072 rows, else 2; B200SPAI_PCG_MODE=1 forces 1, B200SPAI_PCG_MODE=4 makes
  * the auto choice for large SPAI solves 4 when it applies), 1 = stream-enqueued kernels with a device-side done flag
  * polled every few iterations, 2 = one CUDA graph with a device-driven WHILE node (no host involvement at all),

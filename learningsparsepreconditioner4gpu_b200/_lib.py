@@ -45,6 +45,12 @@ SIGNATURES = {
     "b200spai_pcg_profile_iterations": [c_vp, C.c_int, c_vp, c_vp, c_i32, C.POINTER(C.c_float), c_vp],
     "b200spai_pcg_launch_count": [c_vp, C.POINTER(c_i64)],
     "b200spai_pcg_fused_profile": [c_vp, C.POINTER(c_f64), C.POINTER(c_i32), c_vp],
+    "b200spai_pcg_refresh": [c_vp, c_vp],
+    "b200spai_edges_to_csr_plan": [c_i64, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp, C.POINTER(c_vp)],
+    "b200spai_csr_has_plan": [c_vp, C.POINTER(c_i32)],
+    "b200spai_csr_refresh_from_edges": [c_vp, c_vp, c_i64, c_vp, C.POINTER(c_i32)],
+    "b200spai_csr_transpose_plan": [c_vp, c_vp, C.POINTER(c_vp)],
+    "b200spai_csr_refresh_transposed": [c_vp, c_vp, c_vp],
     "b200spai_pcg_destroy": [c_vp],
     "b200spai_graph_create": [c_i64, c_i64, c_vp, c_vp, C.POINTER(c_vp)],
     "b200spai_graph_destroy": [c_vp],

@@ -161,6 +161,8 @@ void csr_free(b200spai_csr_s* a) {
   dev_free(a->val32);
   dev_free(a->col16);
   dev_free(a->rowfirst);
+  dev_free(a->src);
+  dev_free(a->zero_list);
   dev_free(a->blk[0]);
   dev_free(a->blk[1]);
   dev_free(a->blk[2]);
@@ -478,7 +480,18 @@ __global__ void gather_transposed_kernel(const int* __restrict__ perm, const int
   valT[i] = val[src];
 }
 
-static int csr_transpose_impl(b200spai_csr_s* A, cudaStream_t stream, b200spai_csr_s** out) {
+// value-only refresh of a matrix whose entries are a permutation of another value array (transpose plan)
+__global__ void refresh_permuted_kernel(const int* __restrict__ src, const double* __restrict__ val, long long nnz,
+                                        double* __restrict__ out, float* __restrict__ out32) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nnz; i += stride) {
+    const double v = val[src[i]];
+    out[i] = v;
+    if (out32) out32[i] = (float)v;
+  }
+}
+
+static int csr_transpose_impl(b200spai_csr_s* A, cudaStream_t stream, b200spai_csr_s** out, bool keep_plan = false) {
   b200spai_csr_s* T = nullptr;
   B2_TRY(csr_alloc(A->n_cols, A->n_rows, A->nnz, &T));
   const long long nnz = A->nnz;
@@ -514,7 +527,12 @@ static int csr_transpose_impl(b200spai_csr_s* A, cudaStream_t stream, b200spai_c
     dev_free(rowidx);
     dev_free(iota);
     dev_free(keys_out);
-    dev_free(perm);
+    if (keep_plan) {
+      T->src = perm;
+      T->src_kind = 2;
+    } else {
+      dev_free(perm);
+    }
   }
   *out = T;
   return 0;
@@ -638,6 +656,25 @@ int b200spai_csr_create_dev(int32_t n_rows, int32_t n_cols, int64_t nnz, const i
 int b200spai_csr_transpose(b200spai_csr_t a, void* stream, b200spai_csr_t* out) {
   B2_ARG(a && out, "csr_transpose: NULL handle");
   return csr_transpose_impl(a, as_stream(stream), out);
+}
+
+int b200spai_csr_transpose_plan(b200spai_csr_t a, void* stream, b200spai_csr_t* out) {
+  B2_ARG(a && out, "csr_transpose_plan: NULL handle");
+  return csr_transpose_impl(a, as_stream(stream), out, true);
+}
+
+int b200spai_csr_refresh_transposed(b200spai_csr_t t, b200spai_csr_t a, void* stream) {
+  B2_ARG(t && a, "csr_refresh_transposed: NULL handle");
+  B2_ARG(t->nnz == 0 || (t->src_kind == 2 && t->src), "csr_refresh_transposed: t was not built by b200spai_csr_transpose_plan");
+  B2_ARG(t->nnz == a->nnz && t->n_rows == a->n_cols && t->n_cols == a->n_rows, "csr_refresh_transposed: t is not the transpose of a");
+  if (t->nnz == 0) return 0;
+  long long g = (t->nnz + 1023) / 1024;
+  const long long cap = (long long)sm_count() * 16;
+  refresh_permuted_kernel<<<(unsigned)(g > cap ? cap : g), 256, 0, as_stream(stream)>>>(t->src, a->val, t->nnz, t->val,
+                                                                                       t->f32_state == 1 ? t->val32 : nullptr);
+  B2_LAUNCH_CHECK();
+  count_launches(1);
+  return 0;
 }
 
 int b200spai_csr_shape(b200spai_csr_t a, int32_t* n_rows, int32_t* n_cols, int64_t* nnz) {

@@ -23,6 +23,16 @@ struct b200spai_csr_s {
   int nblk[4] = {0, 0, 0, 0};
   int max_row_len = -1;
   double mean_row_len = 0.0;
+  // Fixed-topology value refresh (b200spai_edges_to_csr_plan / b200spai_csr_transpose_plan): src[k] = where the value of
+  // stored entry k comes from -- src_kind 1: index into the flattened [E,b,b] edge values (-1: the unit diagonal a
+  // masked DOF receives); src_kind 2: position in the parent matrix's value array (this matrix is its transpose).
+  // zero_list: edge-value indices that were dropped because the VALUE was exactly 0 (not because of the mask): the
+  // cached pattern stays valid only while they remain 0.
+  int* src = nullptr;
+  int src_kind = 0;
+  int* zero_list = nullptr;
+  long long n_zero = 0;
+  long long n_src_values = 0;  // src_kind 1: E * b * b
 
   b200spai::CsrView view() const { return b200spai::CsrView{n_rows, rowptr, col, val}; }
 };

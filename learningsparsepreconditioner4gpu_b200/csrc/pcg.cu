@@ -543,7 +543,10 @@ int b200spai_pcg_set_spai(b200spai_pcg_t s, b200spai_csr_t g, double epsilon, vo
     s->exec[i] = nullptr;
     s->graph[i] = nullptr;
   }
-  B2_TRY(b200spai_csr_transpose(g, stream, &s->GT));
+  // G built with a refresh plan (fixed topology): G^T keeps its permutation too, so that b200spai_pcg_refresh can
+  // re-gather its values instead of sorting 150 M keys again
+  if (g->src_kind == 1) B2_TRY(b200spai_csr_transpose_plan(g, stream, &s->GT));
+  else B2_TRY(b200spai_csr_transpose(g, stream, &s->GT));
   s->fplan_valid = false;
   s->G = g;
   s->eps = epsilon;
@@ -552,6 +555,17 @@ int b200spai_pcg_set_spai(b200spai_pcg_t s, b200spai_csr_t g, double epsilon, vo
   B2_CUDA(cudaEventElapsedTime(&s->setup_ms, e0, e1));
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
+  return 0;
+}
+
+int b200spai_pcg_refresh(b200spai_pcg_t s, void* stream) {
+  B2_ARG(s, "pcg_refresh: NULL handle");
+  if (s->G) {
+    B2_ARG(s->GT && (s->GT->nnz == 0 || s->GT->src_kind == 2),
+           "pcg_refresh: G^T has no refresh plan (G must come from b200spai_edges_to_csr_plan before b200spai_pcg_set_spai)");
+    B2_TRY(b200spai_csr_refresh_transposed(s->GT, s->G, stream));
+  }
+  s->have_d = false;  // diag(A) is re-read on the next diagonal / scaled solve
   return 0;
 }
 

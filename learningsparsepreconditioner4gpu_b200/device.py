@@ -70,8 +70,10 @@ class DeviceCSR:
 
     @classmethod
     def from_edges(cls, edge_index: torch.Tensor, values: torch.Tensor, num_nodes: int,
-                   mask: Optional[torch.Tensor] = None) -> "DeviceCSR":
-        """Device to_csr_cpu (validate.py:22-51): values fp32 [E] / [E,1,1] / [E,b,b], mask fp32 [N,b] or None."""
+                   mask: Optional[torch.Tensor] = None, plan: bool = False) -> "DeviceCSR":
+        """Device to_csr_cpu (validate.py:22-51): values fp32 [E] / [E,1,1] / [E,b,b], mask fp32 [N,b] or None.
+        ``plan``: also record where every stored value comes from, so that ``refresh_from_edges`` can re-fill the matrix
+        from the next sample's values of the SAME topology and mask in one gather pass (fixed-topology datasets)."""
         _lib.require_cuda()
         assert edge_index.is_cuda and edge_index.dtype == torch.int64 and edge_index.shape[0] == 2
         b = 1 if values.dim() == 1 else values.shape[-1]
@@ -80,9 +82,25 @@ class DeviceCSR:
         ei = edge_index.contiguous()
         h = C.c_void_p()
         lib = _lib.load()
-        _lib.check(lib.b200spai_edges_to_csr(num_nodes, ei.shape[1], b, _ptr(ei), _ptr(vals), _ptr(m), _stream(), C.byref(h)),
-                   "edges_to_csr")
+        fn = lib.b200spai_edges_to_csr_plan if plan else lib.b200spai_edges_to_csr
+        _lib.check(fn(num_nodes, ei.shape[1], b, _ptr(ei), _ptr(vals), _ptr(m), _stream(), C.byref(h)), "edges_to_csr")
         return cls(h)
+
+    @property
+    def plan_kind(self) -> int:
+        """0 = no refresh plan, 1 = planned from edges, 2 = planned transpose."""
+        k = C.c_int32()
+        _lib.check(self._lib.b200spai_csr_has_plan(self._h, C.byref(k)), "csr_has_plan")
+        return k.value
+
+    def refresh_from_edges(self, values: torch.Tensor) -> bool:
+        """New values on the planned pattern.  False: an exact zero appeared / disappeared, the reference's pattern would
+        change -- the content is undefined, rebuild with ``from_edges``."""
+        vals = values.detach().to(torch.float32).contiguous()
+        ok = C.c_int32()
+        _lib.check(self._lib.b200spai_csr_refresh_from_edges(self._h, _ptr(vals), vals.numel(), _stream(), C.byref(ok)),
+                   "csr_refresh_from_edges")
+        return bool(ok.value)
 
     # ---- queries ---------------------------------------------------------------------------------
     @property
@@ -156,6 +174,10 @@ class DevicePCG:
 
     def set_mode(self, mode: int):
         _lib.check(self._lib.b200spai_pcg_set_mode(self._h, mode), "pcg_set_mode")
+
+    def refresh(self):
+        """A and / or G were refreshed in place (``DeviceCSR.refresh_from_edges``): re-gather G^T, drop the cached diagonal."""
+        _lib.check(self._lib.b200spai_pcg_refresh(self._h, _stream()), "pcg_refresh")
 
     def set_spai(self, G: DeviceCSR, epsilon: float):
         self.G = G  # keep alive

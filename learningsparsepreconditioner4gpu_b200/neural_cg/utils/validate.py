@@ -42,7 +42,7 @@ def _cuda(x, dtype=None) -> Optional[torch.Tensor]:
     return t.to(device="cuda", dtype=dtype) if dtype is not None else t.to(device="cuda")
 
 
-def to_csr_device(edge_index, edge_attr, n: int, mask, dtype=np.float64) -> DeviceCSR:
+def to_csr_device(edge_index, edge_attr, n: int, mask, dtype=np.float64, plan: bool = False) -> DeviceCSR:
     """Edge list (+ mask) -> fp64 CSR resident in HBM; semantics of to_csr_cpu.
 
     Restriction against the reference (validate.py:22-51 widens WHATEVER dtype arrives to float64): the assembly entry
@@ -61,7 +61,7 @@ def to_csr_device(edge_index, edge_attr, n: int, mask, dtype=np.float64) -> Devi
                          "assembly entry point; pass fp32 values or build the matrix with DeviceCSR.from_scipy")
     bsize = 1 if vals.dim() == 1 else vals.shape[-1]
     assert n % bsize == 0
-    return DeviceCSR.from_edges(_cuda(edge_index, torch.int64), vals, n // bsize, _cuda(mask, torch.float32))
+    return DeviceCSR.from_edges(_cuda(edge_index, torch.int64), vals, n // bsize, _cuda(mask, torch.float32), plan=plan)
 
 
 def to_csr_cpu(edge_index, edge_attr, n: int, mask, dtype=np.float64) -> csr_matrix:
