@@ -65,6 +65,12 @@ int b200spai_csr_create_dev(int32_t n_rows, int32_t n_cols, int64_t nnz, const i
  * csr_matrix(spai.T), validate.py:176). */
 int b200spai_csr_transpose(b200spai_csr_t a, void* stream, b200spai_csr_t* out);
 int b200spai_csr_shape(b200spai_csr_t a, int32_t* n_rows, int32_t* n_cols, int64_t* nnz);
+/* Native 3x3 block stream (csrc/bsr.cuh; the reference keeps b x b blocks, neural_cg/data.py:134-156, validate.py:36-45):
+ * matrices assembled from [E,3,3] blocks by b200spai_edges_to_csr (and their transposes / row slices) are also kept as
+ * block rows -- nine fp32 values + one 16-bit block-column step per block, 38 B instead of 54 B -- when that is smaller
+ * than the scalar stream; the streaming SpMV then runs on blocks and returns the bits of the scalar kernels.
+ * block_size = 3 and nblocks > 0 when the block stream is in use, 1 / 0 otherwise (B200SPAI_NO_BSR=1 disables it). */
+int b200spai_csr_bsr_info(b200spai_csr_t a, void* stream, int32_t* block_size, int64_t* nblocks);
 /* Copy back (any pointer may be NULL to skip it). */
 int b200spai_csr_download(b200spai_csr_t a, int32_t* indptr_host, int32_t* indices_host, double* data_host,
                           void* stream);

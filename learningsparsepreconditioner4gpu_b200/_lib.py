@@ -46,6 +46,7 @@ SIGNATURES = {
     "b200spai_pcg_launch_count": [c_vp, C.POINTER(c_i64)],
     "b200spai_pcg_fused_profile": [c_vp, C.POINTER(c_f64), C.POINTER(c_i32), c_vp],
     "b200spai_pcg_refresh": [c_vp, c_vp],
+    "b200spai_csr_bsr_info": [c_vp, c_vp, C.POINTER(c_i32), C.POINTER(c_i64)],
     "b200spai_edges_to_csr_plan": [c_i64, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp, C.POINTER(c_vp)],
     "b200spai_csr_has_plan": [c_vp, C.POINTER(c_i32)],
     "b200spai_csr_refresh_from_edges": [c_vp, c_vp, c_i64, c_vp, C.POINTER(c_i32)],

@@ -236,6 +236,7 @@ static int edges_to_csr_impl(int64_t num_nodes, int64_t num_edges, int32_t block
   }
   dev_free(zc);
   count_launches(plan ? 5 : 4);
+  if (!rc) A->block_hint = b;
   if (!rc) *out = A;
   return rc;
 }
@@ -286,6 +287,7 @@ int b200spai_csr_refresh_from_edges(b200spai_csr_t a, const float* values_dev, i
   dev_free(bad);
   B2_CUDA(e);
   *ok = h ? 0 : 1;  // 0: an exact zero appeared or disappeared -- the pattern changed, rebuild the matrix
+  if (*ok) B2_TRY(csr_values_changed(a, st));
   return 0;
 }
 

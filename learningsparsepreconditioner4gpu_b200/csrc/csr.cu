@@ -163,6 +163,11 @@ void csr_free(b200spai_csr_s* a) {
   dev_free(a->rowfirst);
   dev_free(a->src);
   dev_free(a->zero_list);
+  dev_free(a->browptr);
+  dev_free(a->bval);
+  dev_free(a->bstep);
+  dev_free(a->bfirst);
+  dev_free(a->bblk);
   dev_free(a->blk[0]);
   dev_free(a->blk[1]);
   dev_free(a->blk[2]);
@@ -337,6 +342,157 @@ int csr_ensure_col16(b200spai_csr_s* A, cudaStream_t stream) {
   return 0;
 }
 
+// ---- native 3x3 block stream (bsr.cuh) -------------------------------------------------------------------------
+// One thread per block row walks its three scalar rows (sorted columns) as a 3-way merge over block columns.
+// FILL = false: count the blocks; FILL = true: write the nine values (absent entries stay +0), the 16-bit block-column
+// step and the first block column of the row.
+template <bool FILL>
+__global__ void bsr3_build_kernel(const int* __restrict__ rowptr, const int* __restrict__ col, const double* __restrict__ val,
+                                  int nb_rows, int* __restrict__ counts, const int* __restrict__ browptr,
+                                  float* __restrict__ bval, unsigned short* __restrict__ bstep, int* __restrict__ bfirst,
+                                  int* __restrict__ bad) {
+  const int R = blockIdx.x * blockDim.x + threadIdx.x;
+  if (R >= nb_rows) return;
+  int k[3], e[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    k[i] = rowptr[3 * R + i];
+    e[i] = rowptr[3 * R + i + 1];
+  }
+  int n = 0, prev = 0;
+  long long w = FILL ? browptr[R] : 0;
+  while (true) {
+    int cur = 0x7fffffff;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+      if (k[i] < e[i]) cur = min(cur, col[k[i]] / 3);
+    if (cur == 0x7fffffff) break;
+    if (FILL) {
+      float* out = bval + w * 9;
+#pragma unroll
+      for (int j = 0; j < 9; ++j) out[j] = 0.0f;
+      const int step = (n == 0) ? 0 : cur - prev;
+      if (step < 0 || step > 65535) atomicOr(bad, 1);
+      bstep[w] = (unsigned short)step;
+      if (n == 0) bfirst[R] = cur;
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+      while (k[i] < e[i] && col[k[i]] / 3 == cur) {
+        if (FILL) bval[w * 9 + i * 3 + (col[k[i]] - 3 * cur)] = (float)val[k[i]];
+        ++k[i];
+      }
+    prev = cur;
+    ++n;
+    ++w;
+  }
+  if (!FILL) counts[R] = n;
+  else if (n == 0) bfirst[R] = 0;
+}
+
+static bool bsr_disabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200SPAI_NO_BSR");
+    v = (e && atoi(e) != 0) ? 1 : 0;
+  }
+  return v == 1;
+}
+
+int csr_ensure_bsr3(b200spai_csr_s* A, cudaStream_t stream) {
+  if (A->bsr_state != 0) return 0;
+  A->bsr_state = -1;
+  if (bsr_disabled() || A->block_hint != 3 || A->nnz == 0 || A->n_rows % 3 != 0 || A->n_cols % 3 != 0) return 0;
+  B2_TRY(csr_ensure_f32(A, stream));
+  if (A->f32_state != 1) return 0;  // the block stream carries fp32 values: only when that is lossless
+  const int nb = A->n_rows / 3;
+  const int tb = 128;
+  int* counts = nullptr;
+  B2_TRY(dev_alloc(&counts, (size_t)nb + 1 + PAD));
+  B2_CUDA(cudaMemsetAsync(counts, 0, ((size_t)nb + 1 + PAD) * sizeof(int), stream));
+  bsr3_build_kernel<false><<<(nb + tb - 1) / tb, tb, 0, stream>>>(A->rowptr, A->col, A->val, nb, counts, nullptr, nullptr,
+                                                                 nullptr, nullptr, nullptr);
+  B2_LAUNCH_CHECK();
+  size_t tmp_bytes = 0;
+  B2_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, counts, counts, nb + 1, stream));
+  void* tmp = nullptr;
+  B2_CUDA(pool_malloc(&tmp, tmp_bytes + 16));
+  B2_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, counts, counts, nb + 1, stream));
+  int h_nblocks = 0;
+  B2_CUDA(cudaMemcpyAsync(&h_nblocks, counts + nb, sizeof(int), cudaMemcpyDeviceToHost, stream));
+  B2_CUDA(cudaStreamSynchronize(stream));
+  dev_free(tmp);
+  // 38 bytes per block against 6 bytes per stored scalar entry: keep the block stream only when it is the smaller one
+  if (38LL * h_nblocks >= 6LL * A->nnz) {
+    dev_free(counts);
+    return 0;
+  }
+  int* bad = nullptr;
+  int rc = dev_alloc(&bad, 1);
+  if (!rc) rc = dev_alloc(&A->bval, (size_t)h_nblocks * 9 + 64);
+  if (!rc) rc = dev_alloc(&A->bstep, (size_t)h_nblocks + 64);
+  if (!rc) rc = dev_alloc(&A->bfirst, (size_t)nb + 1 + PAD);
+  if (rc) {
+    dev_free(bad);
+    dev_free(counts);
+    return rc;
+  }
+  A->browptr = counts;
+  A->nb_rows = nb;
+  A->nblocks = h_nblocks;
+  B2_CUDA(cudaMemsetAsync(bad, 0, sizeof(int), stream));
+  B2_CUDA(cudaMemsetAsync(A->bval + (size_t)h_nblocks * 9, 0, 64 * sizeof(float), stream));
+  B2_CUDA(cudaMemsetAsync(A->bstep + h_nblocks, 0, 64 * sizeof(unsigned short), stream));
+  B2_CUDA(cudaMemsetAsync(A->bfirst + nb, 0, (1 + PAD) * sizeof(int), stream));
+  bsr3_build_kernel<true><<<(nb + tb - 1) / tb, tb, 0, stream>>>(A->rowptr, A->col, A->val, nb, nullptr, A->browptr, A->bval,
+                                                                A->bstep, A->bfirst, bad);
+  B2_LAUNCH_CHECK();
+  count_launches(2);
+  int h_bad = 0;
+  B2_CUDA(cudaMemcpyAsync(&h_bad, bad, sizeof(int), cudaMemcpyDeviceToHost, stream));
+  B2_CUDA(cudaStreamSynchronize(stream));
+  dev_free(bad);
+  if (h_bad) return 0;  // a block-column step does not fit 16 bits: stay on the scalar streams (arrays freed with the matrix)
+  B2_TRY(build_row_blocks(A->browptr, nb, h_nblocks, BSR_TARGET, BSR_W, &A->bblk, &A->nbblk, stream));
+  A->bsr_state = 1;
+  return 0;
+}
+
+int csr_values_changed(b200spai_csr_s* A, cudaStream_t stream) {
+  if (A->bsr_state != 1) return 0;
+  const int tb = 128;
+  int* bad = nullptr;
+  B2_TRY(dev_alloc(&bad, 1));
+  B2_CUDA(cudaMemsetAsync(bad, 0, sizeof(int), stream));
+  bsr3_build_kernel<true><<<(A->nb_rows + tb - 1) / tb, tb, 0, stream>>>(A->rowptr, A->col, A->val, A->nb_rows, nullptr, A->browptr,
+                                                                        A->bval, A->bstep, A->bfirst, bad);
+  B2_LAUNCH_CHECK();
+  count_launches(1);
+  dev_free(bad);  // stream-ordered reuse (the pool hands it back to this stream only)
+  return 0;
+}
+
+template <int MODE>
+static int launch_bsr3(b200spai_csr_s* A, const SpmvArgs& args, cudaStream_t stream) {
+  constexpr int STAGES = 2, NCW = 8, threads = (NCW + 1) * 32;
+  const int smem = bsr_smem_bytes(STAGES);
+  auto kern = spmv_bsr3_stream_kernel<STAGES, NCW, MODE>;
+  static int ctas_per_sm = 0;  // per instantiation
+  if (ctas_per_sm == 0) {
+    B2_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int occ = 0;
+    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, smem));
+    ctas_per_sm = occ > 0 ? occ : 1;
+  }
+  int grid = sm_count() * ctas_per_sm;
+  if (grid > A->nbblk) grid = A->nbblk;
+  if (grid < 1) grid = 1;
+  BsrView B{A->nb_rows, A->browptr, A->bval, A->bstep, A->bfirst};
+  kern<<<grid, threads, smem, stream>>>(B, A->bblk, A->nbblk, args);
+  B2_LAUNCH_CHECK();
+  return 0;
+}
+
 // ---- SpMV dispatch -------------------------------------------------------------------------------
 static int stream_cfg_from_env() {
   static int cfg = -1;
@@ -435,6 +591,10 @@ static int launch_stream_mode(b200spai_csr_s* A, const SpmvArgs& args, cudaStrea
 template <int MODE>
 static int spmv_launch_mode(b200spai_csr_s* A, const SpmvArgs& args, int kernel, cudaStream_t stream) {
   if (kernel == 0) kernel = spmv_auto_kernel(A);
+  if (kernel == 2 && A->block_hint == 3) {  // assembled from 3x3 blocks: the native block stream when it is the smaller one
+    B2_TRY(csr_ensure_bsr3(A, stream));
+    if (A->bsr_state == 1) return launch_bsr3<MODE>(A, args, stream);
+  }
   if (kernel == 2) return launch_stream_mode<MODE>(A, args, stream);
   return launch_vector_mode<MODE>(A, args, stream);
 }
@@ -494,6 +654,7 @@ __global__ void refresh_permuted_kernel(const int* __restrict__ src, const doubl
 static int csr_transpose_impl(b200spai_csr_s* A, cudaStream_t stream, b200spai_csr_s** out, bool keep_plan = false) {
   b200spai_csr_s* T = nullptr;
   B2_TRY(csr_alloc(A->n_cols, A->n_rows, A->nnz, &T));
+  T->block_hint = A->block_hint;
   const long long nnz = A->nnz;
   const int tb = 256;
   B2_CUDA(cudaMemsetAsync(T->rowptr, 0, ((size_t)A->n_cols + 1) * sizeof(int), stream));
@@ -565,6 +726,14 @@ int b200spai_csr_stream_info(b200spai_csr_t a, int32_t* value_bytes, int32_t* in
   B2_TRY(csr_ensure_col16(a, as_stream(stream)));
   if (value_bytes) *value_bytes = (a->f32_state == 1) ? 4 : 8;
   if (index_bytes) *index_bytes = (a->c16_state == 1) ? 2 : 4;
+  return 0;
+}
+
+int b200spai_csr_bsr_info(b200spai_csr_t a, void* stream, int32_t* block_size, int64_t* nblocks) {
+  B2_ARG(a, "csr_bsr_info: NULL handle");
+  if (a->block_hint == 3) B2_TRY(csr_ensure_bsr3(a, as_stream(stream)));
+  if (block_size) *block_size = (a->bsr_state == 1) ? 3 : 1;
+  if (nblocks) *nblocks = (a->bsr_state == 1) ? a->nblocks : 0;
   return 0;
 }
 
@@ -674,7 +843,7 @@ int b200spai_csr_refresh_transposed(b200spai_csr_t t, b200spai_csr_t a, void* st
                                                                                        t->f32_state == 1 ? t->val32 : nullptr);
   B2_LAUNCH_CHECK();
   count_launches(1);
-  return 0;
+  return csr_values_changed(t, as_stream(stream));
 }
 
 int b200spai_csr_shape(b200spai_csr_t a, int32_t* n_rows, int32_t* n_cols, int64_t* nnz) {

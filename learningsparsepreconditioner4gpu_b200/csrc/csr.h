@@ -1,6 +1,6 @@
 // Device-resident CSR matrix + SpMV dispatch (internal header).
 #pragma once
-#include "spmv.cuh"
+#include "bsr.cuh"
 
 struct b200spai_csr_s {
   int n_rows = 0, n_cols = 0;
@@ -23,6 +23,18 @@ struct b200spai_csr_s {
   int nblk[4] = {0, 0, 0, 0};
   int max_row_len = -1;
   double mean_row_len = 0.0;
+  // Native 3x3 block stream (bsr.cuh), built lazily for matrices assembled from [E,3,3] blocks (block_hint == 3) when it
+  // is smaller than the scalar stream.  bsr_state: 0 = not examined yet, 1 = valid, -1 = does not apply / disabled.
+  int block_hint = 1;
+  int bsr_state = 0;
+  int nb_rows = 0;
+  long long nblocks = 0;
+  int* browptr = nullptr;
+  float* bval = nullptr;
+  unsigned short* bstep = nullptr;
+  int* bfirst = nullptr;
+  int4* bblk = nullptr;
+  int nbblk = 0;
   // Fixed-topology value refresh (b200spai_edges_to_csr_plan / b200spai_csr_transpose_plan): src[k] = where the value of
   // stored entry k comes from -- src_kind 1: index into the flattened [E,b,b] edge values (-1: the unit diagonal a
   // masked DOF receives); src_kind 2: position in the parent matrix's value array (this matrix is its transpose).
@@ -50,6 +62,9 @@ int spmv_launch(b200spai_csr_s* A, const SpmvArgs& args, int mode, int kernel, c
 int csr_ensure_partition(b200spai_csr_s* A, int which, cudaStream_t stream);
 int csr_ensure_f32(b200spai_csr_s* A, cudaStream_t stream);
 int csr_ensure_col16(b200spai_csr_s* A, cudaStream_t stream);
+int csr_ensure_bsr3(b200spai_csr_s* A, cudaStream_t stream);
+// The values of A changed in place (fixed-topology refresh): bring the derived value arrays (block stream) up to date.
+int csr_values_changed(b200spai_csr_s* A, cudaStream_t stream);
 // Contiguous row blocks {r0, rowptr[r0], r1, rowptr[r1]} balanced on rowptr[r] + weight*r (one-off, synchronises).
 int build_row_blocks(const int* rowptr, int n_rows, long long nnz, long long target, int weight, int4** blk_out,
                      int* nblk_out, cudaStream_t stream);

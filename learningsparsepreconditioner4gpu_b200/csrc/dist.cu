@@ -608,6 +608,7 @@ int b200spai_csr_slice_rows(b200spai_csr_t a, int32_t r0, int32_t r1, int64_t sh
   const long long cnt = (long long)h[1] - h[0];
   b200spai_csr_s* L = nullptr;
   B2_TRY(csr_alloc(r1 - r0, n_cols_local, cnt, &L));
+  if (a->block_hint == 3 && r0 % 3 == 0 && (r1 - r0) % 3 == 0 && shift % 3 == 0 && n_cols_local % 3 == 0) L->block_hint = 3;
   int* bad = nullptr;
   B2_TRY(dev_alloc(&bad, 1));
   B2_CUDA(cudaMemsetAsync(bad, 0, sizeof(int), st));

@@ -596,13 +596,22 @@ __global__ void __launch_bounds__((NCW + 1) * 32, MINB) pcg_fused_kernel(const _
     beta = first ? 0.0 : rho / rho_prev;
     // ---- V2: p = z + beta p (owned rows and halo; scipy: p *= beta; p += z) ----
     {
+      // the extended vectors start 16-byte aligned: two entries per access, L2-coherent (.cg) loads and stores
       const long long n_ext = (long long)n_halo + n;
+      const long long n2 = n_ext >> 1;
+      double2* p2 = reinterpret_cast<double2*>(a.p);
+      const double2* z2 = reinterpret_cast<const double2*>(a.z);
       if (first) {
-#pragma unroll 4
-        for (long long e = gtid; e < n_ext; e += gstride) a.p[e] = ld_coh(a.z + e);
+#pragma unroll 2
+        for (long long j = gtid; j < n2; j += gstride) __stcg(p2 + j, __ldcg(z2 + j));
+        if (gtid == 0 && (n_ext & 1)) a.p[n_ext - 1] = __ldcg(a.z + n_ext - 1);
       } else {
-#pragma unroll 4
-        for (long long e = gtid; e < n_ext; e += gstride) a.p[e] = __dadd_rn(__dmul_rn(ld_coh(a.p + e), beta), ld_coh(a.z + e));
+#pragma unroll 2
+        for (long long j = gtid; j < n2; j += gstride) {
+          const double2 pv = __ldcg(p2 + j), zv = __ldcg(z2 + j);
+          __stcg(p2 + j, make_double2(__dadd_rn(__dmul_rn(pv.x, beta), zv.x), __dadd_rn(__dmul_rn(pv.y, beta), zv.y)));
+        }
+        if (gtid == 0 && (n_ext & 1)) a.p[n_ext - 1] = __dadd_rn(__dmul_rn(__ldcg(a.p + n_ext - 1), beta), __ldcg(a.z + n_ext - 1));
       }
     }
     ok = fused_light_barrier<NCW>(a, lgen, red);
@@ -630,18 +639,34 @@ __global__ void __launch_bounds__((NCW + 1) * 32, MINB) pcg_fused_kernel(const _
     alpha = rho / pq;
     // ---- V1: x += alpha p ; r -= alpha q (owned rows, then the halo of r) ; ||r||^2 over the owned rows ----
     acc_rr = 0.0;
-#pragma unroll 4
-    for (long long i = gtid; i < n; i += gstride) {
-      const long long e = off + i;
-      const double pv = ld_coh(a.p + e), qv = ld_coh(a.q + e);
-      a.x[i] = __dadd_rn(a.x[i], __dmul_rn(alpha, pv));
-      const double rv = __dsub_rn(ld_coh(a.r + e), __dmul_rn(alpha, qv));
-      a.r[e] = rv;
-      acc_rr += rv * rv;
+    {
+      // the owned slice starts at an even extended index (16-byte aligned); x is the caller's array and may not be
+      const bool x16 = (reinterpret_cast<unsigned long long>(a.x) & 15ull) == 0ull;
+      const long long n2 = x16 ? (long long)(n >> 1) : 0;
+      const double2* p2 = reinterpret_cast<const double2*>(a.p + off);
+      const double2* q2 = reinterpret_cast<const double2*>(a.q + off);
+      double2* r2 = reinterpret_cast<double2*>(a.r + off);
+      double2* x2 = reinterpret_cast<double2*>(a.x);
+#pragma unroll 2
+      for (long long j = gtid; j < n2; j += gstride) {
+        const double2 pv = __ldcg(p2 + j), qv = __ldcg(q2 + j), rv = __ldcg(r2 + j), xv = __ldcg(x2 + j);
+        __stcg(x2 + j, make_double2(__dadd_rn(xv.x, __dmul_rn(alpha, pv.x)), __dadd_rn(xv.y, __dmul_rn(alpha, pv.y))));
+        const double r0 = __dsub_rn(rv.x, __dmul_rn(alpha, qv.x)), r1 = __dsub_rn(rv.y, __dmul_rn(alpha, qv.y));
+        __stcg(r2 + j, make_double2(r0, r1));
+        acc_rr += r0 * r0;
+        acc_rr += r1 * r1;
+      }
+      for (long long i = 2 * n2 + gtid; i < n; i += gstride) {  // the odd last entry, or everything when x is unaligned
+        const long long e = off + i;
+        a.x[i] = __dadd_rn(__ldcg(a.x + i), __dmul_rn(alpha, __ldcg(a.p + e)));
+        const double rv = __dsub_rn(__ldcg(a.r + e), __dmul_rn(alpha, __ldcg(a.q + e)));
+        a.r[e] = rv;
+        acc_rr += rv * rv;
+      }
     }
     for (long long h = gtid; h < n_halo; h += gstride) {
       const long long e = h < off ? h : (long long)n + h;
-      a.r[e] = __dsub_rn(ld_coh(a.r + e), __dmul_rn(alpha, ld_coh(a.q + e)));
+      a.r[e] = __dsub_rn(__ldcg(a.r + e), __dmul_rn(alpha, __ldcg(a.q + e)));
     }
     pending = true;
     ok = fused_light_barrier<NCW>(a, lgen, red);

@@ -121,6 +121,13 @@ class DeviceCSR:
         _lib.check(self._lib.b200spai_csr_stream_info(self._h, C.byref(v), C.byref(i), _stream()), "csr_stream_info")
         return v.value, i.value
 
+    def bsr_info(self):
+        """(block size, stored blocks) of the native block stream the streaming SpMV uses: (3, nblocks) for matrices
+        assembled from 3x3 blocks when that stream is the smaller one, else (1, 0)."""
+        b, nb = C.c_int32(), C.c_int64()
+        _lib.check(self._lib.b200spai_csr_bsr_info(self._h, _stream(), C.byref(b), C.byref(nb)), "csr_bsr_info")
+        return b.value, nb.value
+
     def to_scipy(self):
         from scipy.sparse import csr_matrix
 
