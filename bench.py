@@ -596,6 +596,8 @@ def main_rowpart(args, ctx: Ctx, emit: bool = True):
         if profile and res.reserved == 4:
             ms, its = solver.fused_profile()
             info["fused_phases_ms_per_iteration"] = {k: round(v / max(its, 1), 5) for k, v in zip(FUSED_PHASES, ms)}
+            if world > 1:
+                info["cross_rank_barrier"] = solver.fused_barrier_profile()
         if profile:
             info["nnz_local"] = [local[0].nnz, local[1].nnz, local[2].nnz]
             info["stream_bytes"] = [list(local[0].stream_bytes()), list(local[1].stream_bytes())]
@@ -664,7 +666,7 @@ def main_rowpart(args, ctx: Ctx, emit: bool = True):
                     "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4), "peak_source": peak_src,
                     "traffic": None, "bytes_per_sweep_rank0": [int(v) for v in streamed], "ms_per_sweep_rank0": sw,
                     "algorithmic": {"bytes_per_sweep_rank0": alg, "GB/s": round(sum(alg) / (sum(sw) * 1e-3) / 1e9, 1)},
-                    "phases_ms_per_iteration_rank0": fp}
+                    "phases_ms_per_iteration_rank0": fp, "cross_rank_barrier_rank0": info.get("cross_rank_barrier")}
     line = None
     if rank == 0:
         W = workload_text(g, N, E, args.rtol)

@@ -258,6 +258,10 @@ int b200spai_dist_pcg_set_mode(b200spai_dist_t d, int mode);
 int b200spai_dist_pcg_fused_ok(b200spai_dist_t d, void* stream, int32_t* ok);
 /* Mode 4, after a solve: as b200spai_pcg_fused_profile (this rank's view). */
 int b200spai_dist_pcg_fused_profile(b200spai_dist_t d, double* phase_ms5, int32_t* iterations, void* stream);
+/* Mode 4, world > 1, after a solve: mean microseconds per cross-rank barrier that CTA 0 of this rank spent {waiting for the
+ * last CTA of its own grid after its own arrival, from there until the last peer's contribution had arrived}, and the
+ * number of barriers averaged over. */
+int b200spai_dist_pcg_fused_barrier_profile(b200spai_dist_t d, double* wait_us2, int64_t* barriers, void* stream);
 /* b / x: the owned rows only.  max_iter must be given (> 0).  resid_hist_dev: NULL or max_iter+1 doubles. */
 int b200spai_dist_pcg_solve(b200spai_dist_t d, int precond, const double* b_local_dev, double* x_local_dev, double rtol,
                             int32_t max_iter, double* resid_hist_dev, void* stream, b200spai_pcg_result* result);

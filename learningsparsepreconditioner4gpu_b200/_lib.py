@@ -75,6 +75,7 @@ SIGNATURES = {
     "b200spai_dist_pcg_set_mode": [c_vp, C.c_int],
     "b200spai_dist_pcg_fused_ok": [c_vp, c_vp, C.POINTER(c_i32)],
     "b200spai_dist_pcg_fused_profile": [c_vp, C.POINTER(c_f64), C.POINTER(c_i32), c_vp],
+    "b200spai_dist_pcg_fused_barrier_profile": [c_vp, C.POINTER(c_f64), C.POINTER(c_i64), c_vp],
     "b200spai_dist_pcg_solve": [c_vp, C.c_int, c_vp, c_vp, c_f64, c_i32, c_vp, c_vp, C.POINTER(PcgResult)],
     "b200spai_dist_pcg_profile_iterations": [c_vp, C.c_int, c_vp, c_vp, c_i32, C.POINTER(C.c_float), c_vp],
     "b200spai_dist_destroy": [c_vp],

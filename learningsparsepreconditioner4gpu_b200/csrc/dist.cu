@@ -273,6 +273,7 @@ struct b200spai_dist_s {
   unsigned long long *fprof = nullptr, *fepoch = nullptr;
   FusedPlan fplan;
   bool fplan_valid = false;
+  int4* fblk[3] = {nullptr, nullptr, nullptr};  // row blocks of A, G, G^T with the boundary blocks first (mode 4)
   double* vec(int v) const { return reinterpret_cast<double*>(seg + SEG_VEC_OFFSET) + (size_t)v * (size_t)ext_cap; }
 };
 
@@ -660,10 +661,45 @@ int b200spai_dist_pcg_set_mode(b200spai_dist_t s, int mode) {
   return 0;
 }
 
+// The row blocks whose rows a neighbour needs go FIRST in every CTA's sweep: their peer stores are long complete when the
+// sweep ends, so the system-scope fence before the barrier finds nothing in flight (in row order the high boundary would
+// be written last, right before the barrier).
+static int dist_boundary_first(b200spai_dist_s* s, const b200spai_csr_s* M, int which, int4** out, cudaStream_t st) {
+  const int nb = M->nblk[which];
+  dev_free(*out);
+  *out = nullptr;
+  if (nb <= 0) return 0;
+  std::vector<int4> h((size_t)nb), r;
+  B2_CUDA(cudaMemcpyAsync(h.data(), M->blk[which], (size_t)nb * sizeof(int4), cudaMemcpyDeviceToHost, st));
+  B2_CUDA(cudaStreamSynchronize(st));
+  r.reserve((size_t)nb);
+  const DistCtx& c = s->ctx;
+  auto boundary = [&](const int4& b) {
+    for (int k = 0; k < c.n_push; ++k) {
+      const long long lo = c.push_src_off[k] - s->off, hi = lo + c.push_len[k];
+      if (b.x < hi && b.z > lo) return true;
+    }
+    return false;
+  };
+  for (const int4& b : h)
+    if (boundary(b)) r.push_back(b);
+  for (const int4& b : h)
+    if (!boundary(b)) r.push_back(b);
+  B2_TRY(dev_alloc(out, (size_t)nb));
+  B2_CUDA(cudaMemcpyAsync(*out, r.data(), (size_t)nb * sizeof(int4), cudaMemcpyHostToDevice, st));
+  B2_CUDA(cudaStreamSynchronize(st));  // r is a host temporary
+  return 0;
+}
+
 static int dist_fused_plan(b200spai_dist_s* s, cudaStream_t st) {
   if (!s->fplan_valid) {
     s->fplan = FusedPlan{};
     if (s->A && s->G && s->GT && s->n > 0) B2_TRY(fused_plan(s->A, s->G, s->GT, st, &s->fplan));
+    if (s->fplan.which >= 0 && s->world > 1 && !getenv("B200SPAI_DIST_ROW_ORDER")) {
+      B2_TRY(dist_boundary_first(s, s->A, s->fplan.which, &s->fblk[0], st));
+      B2_TRY(dist_boundary_first(s, s->G, s->fplan.which, &s->fblk[1], st));
+      B2_TRY(dist_boundary_first(s, s->GT, s->fplan.which, &s->fblk[2], st));
+    }
     s->fplan_valid = true;
   }
   return 0;
@@ -690,20 +726,36 @@ int b200spai_dist_pcg_fused_profile(b200spai_dist_t s, double* phase_ms5, int32_
   return 0;
 }
 
+int b200spai_dist_pcg_fused_barrier_profile(b200spai_dist_t s, double* wait_us2, int64_t* barriers, void* stream) {
+  B2_ARG(s && wait_us2 && barriers, "dist_pcg_fused_barrier_profile: NULL argument");
+  B2_ARG(s->fprof, "dist_pcg_fused_barrier_profile: no fused solve has run on this handle");
+  unsigned long long h[10] = {0};
+  B2_CUDA(cudaMemcpyAsync(h, s->fprof, sizeof(h), cudaMemcpyDeviceToHost, as_stream(stream)));
+  B2_CUDA(cudaStreamSynchronize(as_stream(stream)));
+  const double nb = h[8] > 0 ? (double)h[8] : 1.0;
+  wait_us2[0] = (double)h[6] * 1e-3 / nb;
+  wait_us2[1] = (double)h[7] * 1e-3 / nb;
+  *barriers = (int64_t)h[8];
+  return 0;
+}
+
 // Mode 4: the whole row-partitioned solve in ONE persistent kernel per rank (pcg_fused.cuh).
 static int dist_solve_fused(b200spai_dist_s* s, int precond, const double* b, double* x, cudaStream_t st) {
   if (!s->fsync) B2_TRY(dev_alloc(&s->fsync, 1));
-  if (!s->fprof) B2_TRY(dev_alloc(&s->fprof, 6));
+  if (!s->fprof) B2_TRY(dev_alloc(&s->fprof, 10));
   if (!s->fepoch) {
     B2_TRY(dev_alloc(&s->fepoch, FB_KINDS));
     B2_CUDA(cudaMemsetAsync(s->fepoch, 0, FB_KINDS * sizeof(unsigned long long), st));
   }
   B2_CUDA(cudaMemsetAsync(s->fsync, 0, sizeof(FusedSync), st));
-  B2_CUDA(cudaMemsetAsync(s->fprof, 0, 6 * sizeof(unsigned long long), st));
+  B2_CUDA(cudaMemsetAsync(s->fprof, 0, 10 * sizeof(unsigned long long), st));
   FusedArgs a{};
   a.A = fused_mat(s->A, s->fplan);
   a.G = fused_mat(s->G, s->fplan);
   a.GT = fused_mat(s->GT, s->fplan);
+  if (s->fblk[0]) a.A.blk = s->fblk[0];
+  if (s->fblk[1]) a.G.blk = s->fblk[1];
+  if (s->fblk[2]) a.GT.blk = s->fblk[2];
   a.n = s->n;
   a.off = s->off;
   a.hi_halo = (int)(s->hi - s->re);
@@ -953,6 +1005,7 @@ int b200spai_dist_destroy(b200spai_dist_t s) {
   dev_free(s->fsync);
   dev_free(s->fprof);
   dev_free(s->fepoch);
+  for (int4* b : s->fblk) dev_free(b);
   dev_free(s->ticket);
   dev_free(s->ticket_halo);
   dev_free(s->epoch);

@@ -363,9 +363,9 @@ static int fused_plan_for(b200spai_pcg_s* s, cudaStream_t st) {
 
 static int solve_fused(b200spai_pcg_s* s, int precond, const double* b, double* x, cudaStream_t st) {
   if (!s->fsync) B2_TRY(dev_alloc(&s->fsync, 1));
-  if (!s->fprof) B2_TRY(dev_alloc(&s->fprof, 6));
+  if (!s->fprof) B2_TRY(dev_alloc(&s->fprof, 10));
   B2_CUDA(cudaMemsetAsync(s->fsync, 0, sizeof(FusedSync), st));
-  B2_CUDA(cudaMemsetAsync(s->fprof, 0, 6 * sizeof(unsigned long long), st));
+  B2_CUDA(cudaMemsetAsync(s->fprof, 0, 10 * sizeof(unsigned long long), st));
   FusedArgs a{};
   a.A = fused_mat(s->A, s->fplan);
   a.G = fused_mat(s->G, s->fplan);

@@ -11,7 +11,7 @@ constexpr int F_NCW = 8;
 template <int CAP, typename VT, typename CT, int MINB>
 struct Inst {
   static constexpr int threads = (F_NCW + 1) * 32;
-  static int smem() { return StreamCfg<CAP, VT, CT>::smem_bytes(F_STAGES) + 64; }
+  static int smem() { return StreamCfg<CAP, VT, CT>::smem_bytes(F_STAGES) + 160; }
   static const void* fn() { return (const void*)pcg_fused_kernel<CAP, F_STAGES, F_NCW, VT, CT, MINB>; }
   static int grid(int* out) {
     static int cached[64] = {0};

@@ -68,9 +68,9 @@ struct FusedSync {  // one per solver, zeroed before every launch
   double bcast[2][4];  // [generation & 1][total0, total1, ok, -]
 };
 
-struct FusedXchg {  // one per rank, inside the peer-mapped segment; never reset (epochs are monotonic across solves)
-  unsigned long long epoch[FB_KINDS][FUSED_MAXR];
-  double val[FB_KINDS][FUSED_MAXR][2];
+struct alignas(16) FusedXchg {  // one per rank, inside the peer-mapped segment; never reset (epochs are monotonic across solves)
+  // [kind][source rank] = two words {low 32 bits of the value << 32 | epoch, high 32 bits of the value | epoch}
+  unsigned long long w[FB_KINDS][FUSED_MAXR][2];
 };
 
 struct FusedPeer {
@@ -100,7 +100,9 @@ struct FusedArgs {
   double* hist;
   FusedSync* sync;
   long long spin_limit;  // clock64 ticks before a wait gives up
-  unsigned long long* prof;  // optional [6]: ns in P1+B1, P2+B2, V2+barrier, P3+B3, V1+barrier (CTA 0's view), iterations
+  // optional [9]: ns in P1+B1, P2+B2, V2+barrier, P3+B3, V1+barrier (CTA 0's view), iterations, then (world > 1) ns CTA 0
+  // waited for the last local CTA, ns from there to the last peer's contribution, cross-rank barriers timed
+  unsigned long long* prof;
   FusedPeer peer;
 };
 
@@ -152,9 +154,49 @@ __device__ __forceinline__ void bar_consumers() {
   asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
 }
 
+// CTA-wide OR over the consumer threads (named barrier 1), doubling as the barrier itself.
+template <int NT>
+__device__ __forceinline__ bool bar_or_consumers(bool pred) {
+  uint32_t r;
+  asm volatile(
+      "{\n"
+      ".reg .pred p, q;\n"
+      "setp.ne.u32 q, %1, 0;\n"
+      "bar.red.or.pred p, 1, %2, q;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(r)
+      : "r"((uint32_t)pred), "n"(NT)
+      : "memory");
+  return r != 0;
+}
+__device__ __forceinline__ void st_relaxed_sys_v2(unsigned long long* p, unsigned long long w0, unsigned long long w1) {
+  asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(w0), "l"(w1) : "memory");
+}
+__device__ __forceinline__ void ld_relaxed_sys_v2(const unsigned long long* p, unsigned long long& w0, unsigned long long& w1) {
+  asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(p) : "memory");
+}
+
+// Shared scratch of the barrier code: red[0..31] warp partials, [32..35] broadcast, then (CTA 0 only) the epoch counters
+// of the cross-rank exchange and the barrier timers, all 8-byte slots.
+constexpr int FRED_EPOCH = 36;              // FB_KINDS slots
+constexpr int FRED_T_LOCAL = 42;            // ns CTA 0 waited for the last local CTA (after its own arrival)
+constexpr int FRED_T_PEER = 43;             // ns between the last local arrival and the last peer's contribution
+constexpr int FRED_N_BAR = 44;              // cross-rank barriers timed
+constexpr int FRED_SLOTS = 46;
+
 // Grid barrier + deterministic reduction of (v0, v1) + (world > 1) all-reduce over the ranks.  Called by every
 // CONSUMER thread of every CTA; returns false when a wait timed out (peer or CTA gone): the solve is then abandoned.
-// `pushed`: this thread stored into a peer's memory since the last barrier.
+// `pushed`: this thread stored into a peer's memory since the last barrier.  Every barrier kind carries ONE value
+// (v1 for FB_RR, v0 otherwise); the other is passed through the local reduction only.
+//
+// Cross-rank exchange (NCCL-LL style): the value travels WITH its flag -- two 8-byte words {low half | epoch, high half |
+// epoch} written by one 16-byte store into slot [kind][source rank] of every rank's exchange block; the receiver polls
+// the slot until both words carry the epoch.  8-byte words are single-copy atomic, so no value can be read with a stale
+// half, and no separate flag store (and no release on the far side of the NVLink round trip) is needed.  Ordering of
+// the HALO data: a CTA whose threads pushed fences at system scope ONCE (thread 0, after the CTA barrier: cumulative over
+// the CTA's stores) before it arrives; CTA 0 acquires the arrivals, fences at system scope and only then sends its
+// words; the receiver fences after the last word arrived and then releases its grid.
 template <int NCW>
 __device__ __forceinline__ bool fused_barrier(const FusedArgs& a, unsigned long long& gen, int kind, double v0, double v1,
                                               bool pushed, double* red, double& t0, double& t1) {
@@ -168,27 +210,36 @@ __device__ __forceinline__ bool fused_barrier(const FusedArgs& a, unsigned long 
     red[warp] = v0;
     red[16 + warp] = v1;
   }
-  if (pushed) __threadfence_system();  // this thread's peer stores are performed before its CTA arrives
-  bar_consumers<NCT>();
+  const bool cta_pushed = bar_or_consumers<NCT>(pushed);
   if (warp == 0) {
     double c0 = (lane < NCW) ? red[lane] : 0.0, c1 = (lane < NCW) ? red[16 + lane] : 0.0;
     c0 = warp_sum(c0);
     c1 = warp_sum(c1);
+    unsigned long long ns_arrive = 0ull;
     if (lane == 0) {
       a.partials[blockIdx.x] = c0;
       a.partials[G + blockIdx.x] = c1;
+      if (cta_pushed) asm volatile("fence.acq_rel.sys;" ::: "memory");  // the CTA's peer stores are performed before it arrives
       red_release_gpu_add_u64(&a.sync->arrive, 1ull);  // release: partials, vector writes and (fenced) peer stores
     }
     if (blockIdx.x == 0) {
       // ---- master: wait for every CTA, sum in CTA order, exchange with the other ranks, release ----
+      unsigned long long* red64 = reinterpret_cast<unsigned long long*>(red);
+      const bool timed = a.prof != nullptr && a.peer.world > 1;
       int ok = 1;
       if (lane == 0) {
+        if (timed) ns_arrive = global_ns();
         const long long w0 = clock64();
         while (ld_acquire_gpu_u64(&a.sync->arrive) < gen * (unsigned long long)G)
           if (clock64() - w0 > a.spin_limit) {
             ok = 0;
             break;
           }
+        if (timed) {
+          const unsigned long long now = global_ns();
+          red64[FRED_T_LOCAL] += now - ns_arrive;
+          ns_arrive = now;
+        }
       }
       __syncwarp();
       double s0 = 0.0, s1 = 0.0;
@@ -201,30 +252,36 @@ __device__ __forceinline__ bool fused_barrier(const FusedArgs& a, unsigned long 
       const FusedPeer& P = a.peer;
       if (P.world > 1) {
         unsigned long long ep = 0;
-        if (lane == 0) ep = ++P.epoch[kind];
+        if (lane == 0) ep = ++red64[FRED_EPOCH + kind];
         ep = __shfl_sync(0xffffffffu, ep, 0);
-        double r0v = 0.0, r1v = 0.0;
+        const unsigned long long e32 = ep & 0xffffffffull;
+        const double sv = (kind == FB_RR) ? s1 : s0;
+        double rv = 0.0;
         if (lane < P.world) {
-          FusedXchg* X = P.xchg[lane];
-          X->val[kind][P.rank][0] = s0;
-          X->val[kind][P.rank][1] = s1;
-          f_st_release_sys(&X->epoch[kind][P.rank], ep);  // cumulative: also publishes the halo stores the arrivals ordered
-          const FusedXchg* M = P.xchg[P.rank];
-          const long long w0 = clock64();
-          while (f_ld_relaxed_sys(&M->epoch[kind][lane]) < ep)
-            if (clock64() - w0 > a.spin_limit) {
+          const unsigned long long bits = (unsigned long long)__double_as_longlong(sv);
+          asm volatile("fence.acq_rel.sys;" ::: "memory");  // after the acquired arrivals, before the words leave
+          st_relaxed_sys_v2(&P.xchg[lane]->w[kind][P.rank][0], ((bits & 0xffffffffull) << 32) | e32, (bits & 0xffffffff00000000ull) | e32);
+          const unsigned long long* mine = &P.xchg[P.rank]->w[kind][lane][0];
+          unsigned long long w0v = 0ull, w1v = 0ull;
+          const long long c0k = clock64();
+          while (true) {
+            ld_relaxed_sys_v2(mine, w0v, w1v);
+            if ((w0v & 0xffffffffull) == e32 && (w1v & 0xffffffffull) == e32) break;
+            if (clock64() - c0k > a.spin_limit) {
               ok = 0;
               break;
             }
+          }
           asm volatile("fence.acq_rel.sys;" ::: "memory");
-          r0v = *reinterpret_cast<const volatile double*>(&M->val[kind][lane][0]);
-          r1v = *reinterpret_cast<const volatile double*>(&M->val[kind][lane][1]);
+          rv = __longlong_as_double((long long)((w1v & 0xffffffff00000000ull) | (w0v >> 32)));
         }
-        s0 = 0.0;
-        s1 = 0.0;
-        for (int r = 0; r < P.world; ++r) {  // rank order: identical bits on every rank
-          s0 += __shfl_sync(0xffffffffu, r0v, r);
-          s1 += __shfl_sync(0xffffffffu, r1v, r);
+        double tot = 0.0;
+        for (int r = 0; r < P.world; ++r) tot += __shfl_sync(0xffffffffu, rv, r);  // rank order: identical bits on every rank
+        if (kind == FB_RR) s1 = tot;
+        else s0 = tot;
+        if (timed && lane == 0) {
+          red64[FRED_T_PEER] += global_ns() - ns_arrive;
+          red64[FRED_N_BAR] += 1ull;
         }
       }
       ok = __all_sync(0xffffffffu, ok);
@@ -418,7 +475,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, MINB) pcg_fused_kernel(const _
   sm.hdr = reinterpret_cast<int4*>(sp);              sp += STAGES * 16;
   sm.full = reinterpret_cast<uint64_t*>(sp);         sp += STAGES * 8;
   sm.empty = reinterpret_cast<uint64_t*>(sp);        sp += STAGES * 8;
-  double* red = reinterpret_cast<double*>(sp);       sp += 36 * 8;
+  double* red = reinterpret_cast<double*>(sp);       sp += FRED_SLOTS * 8;
   volatile int* s_done = reinterpret_cast<volatile int*>(sp);
 
   const int tid = threadIdx.x;
@@ -430,6 +487,9 @@ __global__ void __launch_bounds__((NCW + 1) * 32, MINB) pcg_fused_kernel(const _
     }
     mbar_fence_init();
     *s_done = 0;
+    unsigned long long* red64 = reinterpret_cast<unsigned long long*>(red);
+    for (int k = 0; k < FB_KINDS; ++k) red64[FRED_EPOCH + k] = (blockIdx.x == 0 && a.peer.world > 1) ? a.peer.epoch[k] : 0ull;
+    red64[FRED_T_LOCAL] = red64[FRED_T_PEER] = red64[FRED_N_BAR] = 0ull;
   }
   __syncthreads();
 
@@ -681,6 +741,14 @@ __global__ void __launch_bounds__((NCW + 1) * 32, MINB) pcg_fused_kernel(const _
   if (prof) {
     for (int k = 0; k < 5; ++k) a.prof[k] = ns_p[k];
     a.prof[5] = (unsigned long long)iter;
+    const unsigned long long* red64 = reinterpret_cast<const unsigned long long*>(red);
+    a.prof[6] = red64[FRED_T_LOCAL];
+    a.prof[7] = red64[FRED_T_PEER];
+    a.prof[8] = red64[FRED_N_BAR];
+  }
+  if (lead && a.peer.world > 1) {  // the epoch counters survive the solve (monotonic across solves and relayouts)
+    const unsigned long long* red64 = reinterpret_cast<const unsigned long long*>(red);
+    for (int k = 0; k < FB_KINDS; ++k) a.peer.epoch[k] = red64[FRED_EPOCH + k];
   }
   if (lead) {
     sc->bnorm = bnorm;

@@ -233,6 +233,14 @@ class DistPCG:
         _lib.check(self._lib.b200spai_dist_pcg_fused_profile(self._h, ms, C.byref(it), _stream()), "dist_pcg_fused_profile")
         return [float(v) for v in ms], it.value
 
+    def fused_barrier_profile(self):
+        """Mode 4, world > 1, after a solve: {mean us CTA 0 waited for its own grid, mean us from there to the last peer}
+        per cross-rank barrier, and the number of barriers."""
+        us = (C.c_double * 2)()
+        nb = C.c_int64()
+        _lib.check(self._lib.b200spai_dist_pcg_fused_barrier_profile(self._h, us, C.byref(nb), _stream()), "dist_pcg_fused_barrier_profile")
+        return {"wait_local_grid_us": round(us[0], 3), "wait_peers_us": round(us[1], 3), "barriers": nb.value}
+
     def gather(self, x_local: torch.Tensor) -> torch.Tensor:
         """The full solution vector on every rank (plumbing for checks; NCCL all_gather of ragged pieces)."""
         if self.world == 1:
