@@ -180,7 +180,8 @@ static int ensure_hist(b200spai_pcg_s* s, long long need) {
 
 static int ensure_diag(b200spai_pcg_s* s, cudaStream_t st) {
   if (s->have_d) return 0;
-  B2_TRY(dev_alloc(&s->d, (size_t)s->n));
+  // the buffer is allocated once: captured graphs and the fused plan bake its address, a value refresh only rewrites it
+  if (!s->d) B2_TRY(dev_alloc(&s->d, (size_t)s->n));
   B2_TRY(b200spai_csr_diagonal(s->A, s->d, st));
   s->have_d = true;
   return 0;

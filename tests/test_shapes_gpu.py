@@ -83,7 +83,11 @@ def test_named_shape_at_baseline_size_matches_oracle(name):
         assert abs(res.iterations - its_o) <= tol_it, (res.iterations, its_o)
         true_rel = float((bd - A.matvec(x)).norm() / bd.norm())
         assert true_rel < 2e-6, true_rel
-        assert np.abs(x.cpu().numpy() - xo).max() <= 1e-4 * np.abs(xo).max()
+        # b = A * mask, so the exact solution is known: two solves stopped at the same residual tolerance differ by up to
+        # cond(A) * rtol (synth20480: 1.7e-4 measured, 11 k iterations); the bar is the oracle's own distance from the truth
+        err, err_o = np.abs(x.cpu().numpy() - gt).max(), np.abs(xo - gt).max()
+        print(f"[shape {name} mode {res.reserved}] |x - x*|_inf = {err:.2e} (oracle {err_o:.2e})")
+        assert err <= max(3.0 * err_o, 1e-4 * np.abs(gt).max()), (err, err_o)
     # ---- and end to end on the CUDA G (what workspace.solve runs) ----
     xw, resw, _, _, _ = ws.solve(dev, rtol=1e-6)
     print(f"[shape {name} workspace.solve mode {resw.reserved}] iterations {resw.iterations} vs oracle {its_o} (delta {resw.iterations - its_o:+d})")
