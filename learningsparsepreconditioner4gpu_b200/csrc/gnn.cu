@@ -36,7 +36,7 @@ constexpr int MP_THREADS = 256;
 constexpr int MLP16 = 3 * (F * F + F);        // 816 floats: three 16x16 Linear (+bias)
 constexpr int MLP48 = 48 * F + F + 2 * (F * F + F);  // 1328 floats: 48->16, 16->16, 16->16
 constexpr int LAYER_FLOATS = 2 * MLP48 + MLP16;      // msg, edge, node
-constexpr int GNN_CFG_DEFAULT = 2;
+constexpr int GNN_CFG_DEFAULT = 6;  // rational-erfc GELU + tensor-core per-edge MLPs
 
 }  // namespace b200spai
 
@@ -91,12 +91,13 @@ __global__ void graph_segptr_kernel(const int* __restrict__ dst, long long E, lo
   segptr[i] = (int)lo;
 }
 
-// B200SPAI_GNN_CFG (development switch): bit 1 = rational-erfc GELU (default) instead of erff.
+// B200SPAI_GNN_CFG (development switch): bit 1 (value 2) = rational-erfc GELU instead of erff; bit 2 (value 4) = per-edge
+// MLPs (message-passing edge kernel, decoder) on the tensor cores (3xTF32 mma.sync, gnn_mma.cuh) instead of FFMA.
 static int gnn_cfg() {
   static int cfg = -1;
   if (cfg < 0) {
     const char* e = getenv("B200SPAI_GNN_CFG");
-    cfg = e ? (atoi(e) & 2) : GNN_CFG_DEFAULT;
+    cfg = e ? (atoi(e) & 6) : GNN_CFG_DEFAULT;
   }
   return cfg;
 }
@@ -205,24 +206,27 @@ static int graph_create_impl(long long N, long long E, const long long* edge_ind
 }  // namespace b200spai
 
 #include "gnn_kernels.cuh"
+#include "gnn_mma.cuh"
 
 using namespace b200spai;
 
 namespace {
 
-template <bool FIRST, int G>
+template <bool FIRST, int G, bool MMA>
 int launch_mp(const MpParams& P, cudaStream_t st) {
   static int occ_e = 0, occ_n = 0;
   if (!occ_e) {
-    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_e, gnn_edge_kernel<FIRST, G>, MP_THREADS, 0));
+    if (MMA) B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_e, gnn_edge_mma_kernel<FIRST, G>, MMA_THREADS, 0));
+    else B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_e, gnn_edge_kernel<FIRST, G>, MP_THREADS, 0));
     B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_n, gnn_node_kernel<G>, 256, 0));
     if (occ_e < 1) occ_e = 1;
     if (occ_n < 1) occ_n = 1;
   }
   if (P.E > 0) {
-    long long grid = (P.E + MP_THREADS - 1) / MP_THREADS;
+    long long grid = (P.E + MP_THREADS - 1) / MP_THREADS;  // MMA: 8 warps x 32 edges per CTA pass, the same 256 edges
     if (grid > (long long)sm_count() * occ_e) grid = (long long)sm_count() * occ_e;
-    gnn_edge_kernel<FIRST, G><<<(int)grid, MP_THREADS, 0, st>>>(P);
+    if (MMA) gnn_edge_mma_kernel<FIRST, G><<<(int)grid, MMA_THREADS, 0, st>>>(P);
+    else gnn_edge_kernel<FIRST, G><<<(int)grid, MP_THREADS, 0, st>>>(P);
   }
   long long grid = (P.N + 255) / 256;
   if (grid > (long long)sm_count() * occ_n) grid = (long long)sm_count() * occ_n;
@@ -230,16 +234,18 @@ int launch_mp(const MpParams& P, cudaStream_t st) {
   return 0;
 }
 
-template <int G>
+template <int G, bool MMA>
 int launch_dec(b200spai_gnn_t m, b200spai_graph_t g, const float* x, float* g_out_dev, cudaStream_t st) {
   static int occ = 0;
   if (!occ) {
-    B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gnn_dec_kernel<G>, 256, 0));
+    if (MMA) B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gnn_dec_mma_kernel<G>, MMA_THREADS, 0));
+    else B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gnn_dec_kernel<G>, 256, 0));
     if (occ < 1) occ = 1;
   }
   long long ctas = (g->E + 255) / 256;
   if (ctas > (long long)sm_count() * occ) ctas = (long long)sm_count() * occ;
-  gnn_dec_kernel<G><<<(int)ctas, 256, 0, st>>>(g->src, g->dst, g->perm, g->ef, x, m->w_dec(), g->E, m->bb, g_out_dev);
+  if (MMA) gnn_dec_mma_kernel<G><<<(int)ctas, MMA_THREADS, 0, st>>>(g->src, g->dst, g->perm, g->ef, x, m->w_dec(), g->E, m->bb, g_out_dev);
+  else gnn_dec_kernel<G><<<(int)ctas, 256, 0, st>>>(g->src, g->dst, g->perm, g->ef, x, m->w_dec(), g->E, m->bb, g_out_dev);
   return 0;
 }
 
@@ -276,13 +282,18 @@ int gnn_stage(b200spai_gnn_t m, b200spai_graph_t g, int stage, const float* x_de
     P.edge_attr = edge_attr_dev;
     P.edge_in = m->edge_in;
     int rc;
-    if (l == 0)
-      rc = (cfg & 2) ? launch_mp<true, 1>(P, st) : launch_mp<true, 0>(P, st);
-    else
-      rc = (cfg & 2) ? launch_mp<false, 1>(P, st) : launch_mp<false, 0>(P, st);
+    if (cfg & 4) {
+      if (l == 0) rc = (cfg & 2) ? launch_mp<true, 1, true>(P, st) : launch_mp<true, 0, true>(P, st);
+      else rc = (cfg & 2) ? launch_mp<false, 1, true>(P, st) : launch_mp<false, 0, true>(P, st);
+    } else {
+      if (l == 0) rc = (cfg & 2) ? launch_mp<true, 1, false>(P, st) : launch_mp<true, 0, false>(P, st);
+      else rc = (cfg & 2) ? launch_mp<false, 1, false>(P, st) : launch_mp<false, 0, false>(P, st);
+    }
     if (rc) return rc;
   } else if (E > 0) {
-    int rc = (cfg & 2) ? launch_dec<1>(m, g, xb[m->L & 1], g_out_dev, st) : launch_dec<0>(m, g, xb[m->L & 1], g_out_dev, st);
+    int rc;
+    if (cfg & 4) rc = (cfg & 2) ? launch_dec<1, true>(m, g, xb[m->L & 1], g_out_dev, st) : launch_dec<0, true>(m, g, xb[m->L & 1], g_out_dev, st);
+    else rc = (cfg & 2) ? launch_dec<1, false>(m, g, xb[m->L & 1], g_out_dev, st) : launch_dec<0, false>(m, g, xb[m->L & 1], g_out_dev, st);
     if (rc) return rc;
   }
   B2_LAUNCH_CHECK();

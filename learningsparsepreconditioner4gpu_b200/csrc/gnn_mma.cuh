@@ -36,6 +36,19 @@ __device__ __forceinline__ uint32_t tf32_rna(float x) {
   return r;
 }
 
+// Activations: cvt.rna.tf32.f32 compiles to 4 instructions on sm_100a (FSETP |x| < inf, IADD 0x1000, SEL, LOP3); the
+// activations are finite, so round-to-nearest (ties away) is done by hand in 2: add half a TF32 ulp to the bit pattern,
+// clear the 13 low bits.  The exact remainder a - hi (one FADD) is rounded the same way.  volatile: the splits of the
+// layer-1 inputs must not be hoisted out of the msg/edge loop (they would occupy 96 registers).
+__device__ __forceinline__ void tf32_split(float a, uint32_t& hi, uint32_t& lo) {
+  uint32_t h, l;
+  asm volatile("add.u32 %0, %1, 0x1000;" : "=r"(h) : "r"(__float_as_uint(a)));
+  h &= 0xffffe000u;
+  l = (__float_as_uint(a - __uint_as_float(h)) + 0x1000u) & 0xffffe000u;
+  hi = h;
+  lo = l;
+}
+
 __device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
       : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
@@ -86,8 +99,7 @@ __device__ __forceinline__ void mma_linear(const float4* __restrict__ tw, int la
     for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        hi[mt][i] = tf32_rna(a[mt][c][i]);
-        lo[mt][i] = tf32_rna(a[mt][c][i] - __uint_as_float(hi[mt][i]));
+        tf32_split(a[mt][c][i], hi[mt][i], lo[mt][i]);
       }
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
@@ -159,3 +171,149 @@ __device__ __forceinline__ void mma_put(float (&a)[MT][KC][4], int mt, int B, in
   a[mt][2 * B + 1][h] = f.z;
   a[mt][2 * B + 1][h + 2] = f.w;
 }
+
+// LayerNorm statistics of the rows a lane shares with the 3 other lanes of its quad (each lane holds KC*2 of the 8*KC
+// features of row (mt, h)); normalises in place.
+template <int KC, int MT>
+__device__ __forceinline__ void mma_layernorm(float (&a)[MT][KC][4]) {
+  constexpr float inv = 1.0f / (8 * KC);
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      float s = 0.0f;
+#pragma unroll
+      for (int c = 0; c < KC; ++c) s += a[mt][c][h] + a[mt][c][h + 2];
+      s += __shfl_xor_sync(0xffffffffu, s, 1);
+      s += __shfl_xor_sync(0xffffffffu, s, 2);
+      const float mean = s * inv;
+      float var = 0.0f;
+#pragma unroll
+      for (int c = 0; c < KC; ++c) {
+        const float d0 = a[mt][c][h] - mean, d1 = a[mt][c][h + 2] - mean;
+        var = fmaf(d0, d0, var);
+        var = fmaf(d1, d1, var);
+      }
+      var += __shfl_xor_sync(0xffffffffu, var, 1);
+      var += __shfl_xor_sync(0xffffffffu, var, 2);
+      const float rstd = 1.0f / sqrtf(var * inv + 1e-5f);
+#pragma unroll
+      for (int c = 0; c < KC; ++c) {
+        a[mt][c][h] = (a[mt][c][h] - mean) * rstd;
+        a[mt][c][h + 2] = (a[mt][c][h + 2] - mean) * rstd;
+      }
+    }
+}
+
+constexpr int MMA_THREADS = 256;
+constexpr int MMA_MT = 2;  // row tiles per warp: 32 edges
+
+// ---- message-passing edge kernel on the tensor cores (same contract as gnn_edge_kernel) --------------------------
+template <bool FIRST, int G>
+__global__ void __launch_bounds__(MMA_THREADS, 2) gnn_edge_mma_kernel(const MpParams P) {
+  __shared__ __align__(16) MmaMlpTab<6> s_msg, s_edge;
+  __shared__ __align__(16) MmaMlpTab<2> s_enc;  // edge encoder (layer 0 only)
+  const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  mma_build_tab<6>(P.w_layer, &s_msg, tid, MMA_THREADS);
+  mma_build_tab<6>(P.w_layer + MLP48, &s_edge, tid, MMA_THREADS);
+  if (FIRST) mma_build_tab<2>(P.w_eenc, &s_enc, tid, MMA_THREADS);
+  __syncthreads();
+  const long long ntiles = (P.E + 31) >> 5;
+  const long long wstride = (long long)gridDim.x * (MMA_THREADS / 32);
+  for (long long tile = (long long)blockIdx.x * (MMA_THREADS / 32) + (tid >> 5); tile < ntiles; tile += wstride) {
+    const long long p0 = tile << 5;
+    float v[MMA_MT][6][4];     // [x_i = x[dst], x_j = x[src], e]  (basic_layers.py:216-222) in A-fragment order
+    float4 ev[MMA_MT][2];      // e of the lane's rows (residual)
+    if (FIRST) {               // edge encoder e = MLP(edge_attr) on the fly (gnns.py:84)
+      float a0[MMA_MT][2][4];
+#pragma unroll
+      for (int mt = 0; mt < MMA_MT; ++mt)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const long long p = p0 + 16 * mt + 8 * h + g;
+          const long long eo = p < P.E ? __ldg(P.perm + p) : 0;
+          float f[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) f[i] = (p < P.E && 4 * t + i < P.edge_in) ? __ldg(P.edge_attr + eo * P.edge_in + 4 * t + i) : 0.0f;
+          mma_put<2, MMA_MT>(a0, mt, 0, h, make_float4(f[0], f[1], f[2], f[3]));
+        }
+      mlp3_mma<2, MMA_MT, G>(&s_enc, lane, a0, ev);
+    }
+#pragma unroll
+    for (int mt = 0; mt < MMA_MT; ++mt)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const long long p = p0 + 16 * mt + 8 * h + g;
+        const bool in = p < P.E;
+        const int d = in ? __ldg(P.dst + p) : 0, s = in ? __ldg(P.src + p) : 0;
+        mma_put<6, MMA_MT>(v, mt, 0, h, __ldg(reinterpret_cast<const float4*>(P.xin + (long long)d * F) + t));
+        mma_put<6, MMA_MT>(v, mt, 1, h, __ldg(reinterpret_cast<const float4*>(P.xin + (long long)s * F) + t));
+        // ef is padded to a whole tile; later layers re-read e for the residual (L1/L2 hit) instead of holding it
+        mma_put<6, MMA_MT>(v, mt, 2, h, FIRST ? ev[mt][h] : *ef_chunk(P.ef, p, t));
+      }
+    mma_layernorm<6, MMA_MT>(v);
+#pragma unroll 1
+    for (int m = 0; m < 2; ++m) {  // msg MLP, then edge MLP, through one copy of the code
+      float4 o[MMA_MT][2];
+      mlp3_mma<6, MMA_MT, G>(m == 0 ? &s_msg : &s_edge, lane, v, o);
+#pragma unroll
+      for (int mt = 0; mt < MMA_MT; ++mt)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const long long p = p0 + 16 * mt + 8 * h + g;
+          if (m == 0) {
+            reinterpret_cast<float4*>(P.msg + p * F)[t] = o[mt][h];  // msg is padded to a whole tile
+          } else {
+            const float4 e = FIRST ? ev[mt][h] : *ef_chunk(P.ef, p, t), r = o[mt][h];
+            *ef_chunk(P.ef, p, t) = make_float4(e.x + r.x, e.y + r.y, e.z + r.z, e.w + r.w);
+          }
+        }
+    }
+  }
+}
+
+// ---- decoder on the tensor cores (same contract as gnn_dec_kernel) ------------------------------------------------
+template <int G>
+__global__ void __launch_bounds__(MMA_THREADS, 2) gnn_dec_mma_kernel(const int* __restrict__ src, const int* __restrict__ dst,
+                                                                     const int* __restrict__ perm, float* ef,
+                                                                     const float* __restrict__ x, const float* __restrict__ w,
+                                                                     long long E, int bb, float* __restrict__ gout) {
+  __shared__ __align__(16) MmaMlpTab<6> s_dec;
+  const int tid = threadIdx.x, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  mma_build_tab<6>(w, &s_dec, tid, MMA_THREADS);
+  __syncthreads();
+  const long long ntiles = (E + 31) >> 5;
+  const long long wstride = (long long)gridDim.x * (MMA_THREADS / 32);
+  for (long long tile = (long long)blockIdx.x * (MMA_THREADS / 32) + (tid >> 5); tile < ntiles; tile += wstride) {
+    const long long p0 = tile << 5;
+    float v[MMA_MT][6][4];  // [edge, x[edge_index[0]], x[edge_index[1]]]  (gnns.py:88-90)
+#pragma unroll
+    for (int mt = 0; mt < MMA_MT; ++mt)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const long long p = p0 + 16 * mt + 8 * h + g;
+        const bool in = p < E;
+        const int d = in ? __ldg(dst + p) : 0, s = in ? __ldg(src + p) : 0;
+        mma_put<6, MMA_MT>(v, mt, 0, h, *ef_chunk(ef, p, t));
+        mma_put<6, MMA_MT>(v, mt, 1, h, __ldg(reinterpret_cast<const float4*>(x + (long long)s * F) + t));
+        mma_put<6, MMA_MT>(v, mt, 2, h, __ldg(reinterpret_cast<const float4*>(x + (long long)d * F) + t));
+      }
+    float4 o[MMA_MT][2];
+    mlp3_mma<6, MMA_MT, G>(&s_dec, lane, v, o);
+#pragma unroll
+    for (int mt = 0; mt < MMA_MT; ++mt)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const long long p = p0 + 16 * mt + 8 * h + g;
+        if (p < E && 4 * t < bb) {
+          const long long eo = __ldg(perm + p);
+          const float f[4] = {o[mt][h].x, o[mt][h].y, o[mt][h].z, o[mt][h].w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            if (4 * t + i < bb) gout[eo * bb + 4 * t + i] = f[i];
+        }
+      }
+  }
+}
+
+}  // namespace b200spai

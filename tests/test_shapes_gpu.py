@@ -60,7 +60,10 @@ def test_named_shape_at_baseline_size_matches_oracle(name):
     Gref = to_csr_device(dev.edge_index, Go.cuda(), n, dev.mask)
     assert _same(Gref.to_scipy(), Gco)
     bd = A.matvec(dev.mask.reshape(-1).double())
-    assert np.array_equal(bd.cpu().numpy(), bo)
+    if A.nnz >= (1 << 18):
+        assert np.array_equal(bd.cpu().numpy(), bo)      # streaming kernel: scipy's sequential row sums, bit for bit
+    else:                                                # sub-warp-per-row kernel: tree-summed rows, rounding-level differences
+        assert np.allclose(bd.cpu().numpy(), bo, rtol=1e-13, atol=1e-14 * np.abs(bo).max())
     r = np.random.default_rng(0).standard_normal(n)
     GT = sp.csr_matrix(Gco.T)
     GT.sort_indices()
