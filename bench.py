@@ -648,6 +648,14 @@ def main_rowpart(args, ctx: Ctx, emit: bool = True):
     e2e_ms = max_over_ranks(ev0.elapsed_time(ev1))
     h2d_all, d2h_all = ctx.sum(float(h2d)), ctx.sum(float(d2h))
 
+    # ---- every rank's view of the iteration (who waits for whom): phases, barrier waits, local sizes ----
+    mine = {"rank": rank, "rows": int(re - rs), "nnz_local": info.get("nnz_local"), "phases_ms_per_iteration": info.get("fused_phases_ms_per_iteration"),
+            "cross_rank_barrier": info.get("cross_rank_barrier")}
+    per_rank = [mine]
+    if world > 1:
+        import torch.distributed as dist
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, mine)
     # ---- roofline of the dominant phase: the three matrix sweeps of this rank's share ----
     peak, peak_src = peaks()
     n_loc = (re - rs) * b
@@ -686,7 +694,7 @@ def main_rowpart(args, ctx: Ctx, emit: bool = True):
             "e2e": {"value": round(args.steps / (e2e_ms * 1e-3), 4), "unit": UNIT, "h2d_bytes_per_step": int(h2d_all), "d2h_bytes_per_step": int(d2h_all),
                     "ms_per_step": round(e2e_ms / args.steps, 3),
                     "api": "parallel.PartitionedSystem / DistPCG on every rank's pinned-host slices of the system (bytes summed over ranks)"},
-            "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": None, "clocks": clocks,
+            "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": None, "clocks": clocks, "per_rank": per_rank,
         }
         if emit:
             print(json.dumps(line), flush=True)

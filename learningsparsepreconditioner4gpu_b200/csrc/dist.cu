@@ -274,6 +274,7 @@ struct b200spai_dist_s {
   FusedPlan fplan;
   bool fplan_valid = false;
   int4* fblk[3] = {nullptr, nullptr, nullptr};  // row blocks of A, G, G^T with the boundary blocks first (mode 4)
+  int fnbnd[3] = {0, 0, 0};                     // how many of them are boundary blocks
   double* vec(int v) const { return reinterpret_cast<double*>(seg + SEG_VEC_OFFSET) + (size_t)v * (size_t)ext_cap; }
 };
 
@@ -664,10 +665,11 @@ int b200spai_dist_pcg_set_mode(b200spai_dist_t s, int mode) {
 // The row blocks whose rows a neighbour needs go FIRST in every CTA's sweep: their peer stores are long complete when the
 // sweep ends, so the system-scope fence before the barrier finds nothing in flight (in row order the high boundary would
 // be written last, right before the barrier).
-static int dist_boundary_first(b200spai_dist_s* s, const b200spai_csr_s* M, int which, int4** out, cudaStream_t st) {
+static int dist_boundary_first(b200spai_dist_s* s, const b200spai_csr_s* M, int which, int4** out, int* n_boundary, cudaStream_t st) {
   const int nb = M->nblk[which];
   dev_free(*out);
   *out = nullptr;
+  *n_boundary = 0;
   if (nb <= 0) return 0;
   std::vector<int4> h((size_t)nb), r;
   B2_CUDA(cudaMemcpyAsync(h.data(), M->blk[which], (size_t)nb * sizeof(int4), cudaMemcpyDeviceToHost, st));
@@ -683,6 +685,7 @@ static int dist_boundary_first(b200spai_dist_s* s, const b200spai_csr_s* M, int 
   };
   for (const int4& b : h)
     if (boundary(b)) r.push_back(b);
+  *n_boundary = (int)r.size();
   for (const int4& b : h)
     if (!boundary(b)) r.push_back(b);
   B2_TRY(dev_alloc(out, (size_t)nb));
@@ -695,10 +698,10 @@ static int dist_fused_plan(b200spai_dist_s* s, cudaStream_t st) {
   if (!s->fplan_valid) {
     s->fplan = FusedPlan{};
     if (s->A && s->G && s->GT && s->n > 0) B2_TRY(fused_plan(s->A, s->G, s->GT, st, &s->fplan));
-    if (s->fplan.which >= 0 && s->world > 1 && !getenv("B200SPAI_DIST_ROW_ORDER")) {
-      B2_TRY(dist_boundary_first(s, s->A, s->fplan.which, &s->fblk[0], st));
-      B2_TRY(dist_boundary_first(s, s->G, s->fplan.which, &s->fblk[1], st));
-      B2_TRY(dist_boundary_first(s, s->GT, s->fplan.which, &s->fblk[2], st));
+    if (s->fplan.which >= 0 && s->world > 1) {  // (the neighbour flags of barrier B1 rely on this order)
+      B2_TRY(dist_boundary_first(s, s->A, s->fplan.which, &s->fblk[0], &s->fnbnd[0], st));
+      B2_TRY(dist_boundary_first(s, s->G, s->fplan.which, &s->fblk[1], &s->fnbnd[1], st));
+      B2_TRY(dist_boundary_first(s, s->GT, s->fplan.which, &s->fblk[2], &s->fnbnd[2], st));
     }
     s->fplan_valid = true;
   }
@@ -753,9 +756,9 @@ static int dist_solve_fused(b200spai_dist_s* s, int precond, const double* b, do
   a.A = fused_mat(s->A, s->fplan);
   a.G = fused_mat(s->G, s->fplan);
   a.GT = fused_mat(s->GT, s->fplan);
-  if (s->fblk[0]) a.A.blk = s->fblk[0];
-  if (s->fblk[1]) a.G.blk = s->fblk[1];
-  if (s->fblk[2]) a.GT.blk = s->fblk[2];
+  if (s->fblk[0]) { a.A.blk = s->fblk[0]; a.A.nbnd = s->fnbnd[0]; }
+  if (s->fblk[1]) { a.G.blk = s->fblk[1]; a.G.nbnd = s->fnbnd[1]; }
+  if (s->fblk[2]) { a.GT.blk = s->fblk[2]; a.GT.nbnd = s->fnbnd[2]; }
   a.n = s->n;
   a.off = s->off;
   a.hi_halo = (int)(s->hi - s->re);
@@ -780,8 +783,11 @@ static int dist_solve_fused(b200spai_dist_s* s, int precond, const double* b, do
   P.rank = s->rank;
   P.world = s->world;
   P.n_push = c.n_push;
+  P.n_recv = c.n_recv;
+  for (int k = 0; k < c.n_recv; ++k) P.recv_peer[k] = c.recv_peer[k];
   for (int k = 0; k < c.n_push; ++k) {
     const int q = c.push_peer[k];
+    P.push_peer[k] = q;
     P.push_lo[k] = (int)(c.push_src_off[k] - s->off);
     P.push_hi[k] = P.push_lo[k] + c.push_len[k];
     P.push_r[k] = c.vec[V_R][q] + c.push_dst_off[k];

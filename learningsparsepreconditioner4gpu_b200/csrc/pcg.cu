@@ -396,6 +396,7 @@ static int solve_fused(b200spai_pcg_s* s, int precond, const double* b, double* 
   a.peer.rank = 0;
   a.peer.world = 1;
   a.peer.n_push = 0;
+  a.peer.n_recv = 0;
   B2_TRY(fused_launch(a, s->fplan, st));
   s->launches += 1;
   count_launches(1);

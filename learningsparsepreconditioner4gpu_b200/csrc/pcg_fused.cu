@@ -85,7 +85,11 @@ int fused_plan(b200spai_csr_s* A, b200spai_csr_s* G, b200spai_csr_s* GT, cudaStr
     if (m->n_rows <= 0) return 0;
     nnz_max = std::max(nnz_max, m->nnz);
   }
-  const int which = (nnz_max >= (1LL << 22)) ? 2 : 1;
+  int which = (nnz_max >= (1LL << 22)) ? 2 : 1;
+  if (const char* e = getenv("B200SPAI_FUSED_WHICH")) {  // development switch: 1 = 2048-entry stages, 2 = 4096
+    const int w = atoi(e);
+    if (w == 1 || w == 2) which = w;
+  }
   for (auto* m : ms) {
     B2_TRY(csr_ensure_partition(m, which, st));
     B2_TRY(csr_ensure_f32(m, st));
@@ -120,6 +124,7 @@ FusedMat fused_mat(const b200spai_csr_s* M, const FusedPlan& plan) {
   m.rowfirst = M->rowfirst;
   m.blk = M->blk[plan.which];
   m.nblk = M->nblk[plan.which];
+  m.nbnd = 0;
   return m;
 }
 

@@ -2,10 +2,11 @@
 // GPUs of an NVSwitch box.  It replaces the 5-launch iteration of pcg.cu / the 8-launch iteration of dist.cu:
 //
 //   P1   t = G^T r [/ d]                                    (matrix sweep, gathers r)
-//   --- barrier B1 (cross-rank): ||r||^2 of the update made at the end of the previous iteration -> iteration count,
-//       history, convergence / max_iter test (the sweep that ran ahead of a converged test only wrote t)
+//   --- barrier B1: local grid barrier; row-partitioned: + the neighbours' "boundary rows of t stored" flags (no all-reduce)
 //   P2   z = G t + eps r [/ d] ; rho = r.z                  (matrix sweep, gathers t)
-//   --- barrier B2 (cross-rank): rho -> beta
+//   --- barrier B2 (cross-rank): rho -> beta, and ||r||^2 of the update made at the end of the previous iteration ->
+//       iteration count, history, convergence / max_iter test (the P1/P2 sweeps that ran ahead of a converged test only
+//       wrote t and z)
 //   V2   p = z + beta p                                     (vector phase, owned rows + halo)
 //   --- local grid barrier
 //   P3   q = A p ; p.q                                      (matrix sweep, gathers p)
@@ -45,7 +46,7 @@
 namespace b200spai {
 
 constexpr int FUSED_MAXR = 16;
-enum { FB_INIT = 0, FB_RR = 1, FB_RHO = 2, FB_PQ = 3, FB_READY = 4, FB_KINDS = 5 };
+enum { FB_INIT = 0, FB_RR = 1, FB_RHO = 2, FB_PQ = 3, FB_READY = 4, FB_HALO = 5, FB_KINDS = 6 };
 
 struct FusedMat {
   const int* rowptr;
@@ -56,25 +57,32 @@ struct FusedMat {
   const int* rowfirst;  // first column of each row (u16 stream only)
   const int4* blk;      // row blocks {r0, rowptr[r0], r1, rowptr[r1]}, any order
   int nblk;
+  int nbnd;             // (row-partitioned) the first nbnd blocks hold the rows a neighbour's halo needs
 };
 
 struct FusedSync {  // one per solver, zeroed before every launch
   unsigned long long arrive;
   unsigned long long pad0[15];
-  unsigned long long release;
-  unsigned long long pad1[15];
+  // release of the value barrier, LL style: three 16-byte pairs {low half | gen, high half | gen} of total 0, total 1 and
+  // the ok flag -- the totals travel WITH the release, a waiting CTA needs one L2 round trip, not two
+  unsigned long long rel[6];
+  unsigned long long pad1[10];
   unsigned long long light;  // arrive counter of the value-less local barrier
   unsigned long long pad2[15];
-  double bcast[2][4];  // [generation & 1][total0, total1, ok, -]
+  unsigned long long bdone;  // CTAs that finished (and fenced) the boundary blocks of a t = G^T r sweep
+  unsigned long long pad3[15];
 };
 
 struct alignas(16) FusedXchg {  // one per rank, inside the peer-mapped segment; never reset (epochs are monotonic across solves)
   // [kind][source rank] = two words {low 32 bits of the value << 32 | epoch, high 32 bits of the value | epoch}
   unsigned long long w[FB_KINDS][FUSED_MAXR][2];
+  // [source rank] = epoch of the last t = G^T r sweep whose boundary rows that rank has stored into this rank's halo
+  unsigned long long hflag[FUSED_MAXR];
 };
 
 struct FusedPeer {
-  int rank, world, n_push;
+  int rank, world, n_push, n_recv;
+  int push_peer[FUSED_MAXR], recv_peer[FUSED_MAXR];  // ranks whose halo holds my rows / whose rows my halo holds
   int push_lo[FUSED_MAXR], push_hi[FUSED_MAXR];  // owned local rows [lo, hi) a neighbour's extended range contains
   double* push_r[FUSED_MAXR];                    // address of row push_lo[s] inside the neighbour's extended vector
   double* push_t[FUSED_MAXR];
@@ -197,9 +205,10 @@ constexpr int FRED_SLOTS = 46;
 // the HALO data: a CTA whose threads pushed fences at system scope ONCE (thread 0, after the CTA barrier: cumulative over
 // the CTA's stores) before it arrives; CTA 0 acquires the arrivals, fences at system scope and only then sends its
 // words; the receiver fences after the last word arrived and then releases its grid.
+// `both`: the barrier all-reduces v0 under `kind` AND v1 under FB_RR in the same exchange (lanes 0..15 / 16..31).
 template <int NCW>
 __device__ __forceinline__ bool fused_barrier(const FusedArgs& a, unsigned long long& gen, int kind, double v0, double v1,
-                                              bool pushed, double* red, double& t0, double& t1) {
+                                              bool pushed, double* red, double& t0, double& t1, bool both = false) {
   constexpr int NCT = NCW * 32;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned G = gridDim.x;
@@ -211,57 +220,85 @@ __device__ __forceinline__ bool fused_barrier(const FusedArgs& a, unsigned long 
     red[16 + warp] = v1;
   }
   const bool cta_pushed = bar_or_consumers<NCT>(pushed);
+  const bool master = blockIdx.x == 0;
+  unsigned long long* red64 = reinterpret_cast<unsigned long long*>(red);
+  const bool timed = master && a.prof != nullptr && a.peer.world > 1;
+  unsigned long long ns_arrive = 0ull;
   if (warp == 0) {
     double c0 = (lane < NCW) ? red[lane] : 0.0, c1 = (lane < NCW) ? red[16 + lane] : 0.0;
     c0 = warp_sum(c0);
     c1 = warp_sum(c1);
-    unsigned long long ns_arrive = 0ull;
     if (lane == 0) {
       a.partials[blockIdx.x] = c0;
       a.partials[G + blockIdx.x] = c1;
       if (cta_pushed) asm volatile("fence.acq_rel.sys;" ::: "memory");  // the CTA's peer stores are performed before it arrives
       red_release_gpu_add_u64(&a.sync->arrive, 1ull);  // release: partials, vector writes and (fenced) peer stores
-    }
-    if (blockIdx.x == 0) {
-      // ---- master: wait for every CTA, sum in CTA order, exchange with the other ranks, release ----
-      unsigned long long* red64 = reinterpret_cast<unsigned long long*>(red);
-      const bool timed = a.prof != nullptr && a.peer.world > 1;
-      int ok = 1;
-      if (lane == 0) {
+      if (master) {  // wait for every CTA
         if (timed) ns_arrive = global_ns();
+        int okw = 1;
         const long long w0 = clock64();
         while (ld_acquire_gpu_u64(&a.sync->arrive) < gen * (unsigned long long)G)
           if (clock64() - w0 > a.spin_limit) {
-            ok = 0;
+            okw = 0;
             break;
           }
+        red[35] = okw ? 1.0 : 0.0;
         if (timed) {
           const unsigned long long now = global_ns();
           red64[FRED_T_LOCAL] += now - ns_arrive;
           ns_arrive = now;
         }
       }
-      __syncwarp();
-      double s0 = 0.0, s1 = 0.0;
-      for (unsigned i = lane; i < G; i += 32) {
+    }
+  }
+  if (master) {
+    // ---- master CTA: all consumer threads fetch the per-CTA partials at once (one L2 round trip instead of G / 32 in a
+    // row), fixed order: thread-strided sums, warp tree, warps in index order; then warp 0 exchanges with the other
+    // ranks and releases the grid ----
+    bar_consumers<NCT>();  // thread 0 has acquired every arrival
+    double s0, s1;
+    {
+      const unsigned i0 = tid, i1 = tid + NCT, i2 = tid + 2 * NCT;
+      const double a0 = i0 < G ? __ldcg(a.partials + i0) : 0.0, b0 = i0 < G ? __ldcg(a.partials + G + i0) : 0.0;
+      const double a1 = i1 < G ? __ldcg(a.partials + i1) : 0.0, b1 = i1 < G ? __ldcg(a.partials + G + i1) : 0.0;
+      const double a2 = i2 < G ? __ldcg(a.partials + i2) : 0.0, b2 = i2 < G ? __ldcg(a.partials + G + i2) : 0.0;
+      s0 = (a0 + a1) + a2;
+      s1 = (b0 + b1) + b2;
+      for (unsigned i = tid + 3 * NCT; i < G; i += NCT) {
         s0 += __ldcg(a.partials + i);
         s1 += __ldcg(a.partials + G + i);
       }
+    }
+    s0 = warp_sum(s0);
+    s1 = warp_sum(s1);
+    const int ok_arrive = red[35] != 0.0;
+    if (lane == 0) {
+      red[warp] = s0;
+      red[16 + warp] = s1;
+    }
+    bar_consumers<NCT>();
+    if (warp == 0) {
+      int ok = ok_arrive;
+      s0 = (lane < NCW) ? red[lane] : 0.0;
+      s1 = (lane < NCW) ? red[16 + lane] : 0.0;
       s0 = warp_sum(s0);
       s1 = warp_sum(s1);
       const FusedPeer& P = a.peer;
       if (P.world > 1) {
+        // lanes 0..15 carry `kind`, lanes 16..31 carry FB_RR when `both` (world <= 16)
+        const int half = lane >> 4, pr = lane & 15;
+        const int mykind = half ? FB_RR : kind;
         unsigned long long ep = 0;
-        if (lane == 0) ep = ++red64[FRED_EPOCH + kind];
-        ep = __shfl_sync(0xffffffffu, ep, 0);
+        if (pr == 0 && (half == 0 || both)) ep = ++red64[FRED_EPOCH + mykind];
+        ep = __shfl_sync(0xffffffffu, ep, lane & 16);
         const unsigned long long e32 = ep & 0xffffffffull;
-        const double sv = (kind == FB_RR) ? s1 : s0;
+        const double sv = half ? s1 : ((kind == FB_RR) ? s1 : s0);
         double rv = 0.0;
-        if (lane < P.world) {
+        if (pr < P.world && (half == 0 || both)) {
           const unsigned long long bits = (unsigned long long)__double_as_longlong(sv);
           asm volatile("fence.acq_rel.sys;" ::: "memory");  // after the acquired arrivals, before the words leave
-          st_relaxed_sys_v2(&P.xchg[lane]->w[kind][P.rank][0], ((bits & 0xffffffffull) << 32) | e32, (bits & 0xffffffff00000000ull) | e32);
-          const unsigned long long* mine = &P.xchg[P.rank]->w[kind][lane][0];
+          st_relaxed_sys_v2(&P.xchg[pr]->w[mykind][P.rank][0], ((bits & 0xffffffffull) << 32) | e32, (bits & 0xffffffff00000000ull) | e32);
+          const unsigned long long* mine = &P.xchg[P.rank]->w[mykind][pr][0];
           unsigned long long w0v = 0ull, w1v = 0ull;
           const long long c0k = clock64();
           while (true) {
@@ -275,37 +312,51 @@ __device__ __forceinline__ bool fused_barrier(const FusedArgs& a, unsigned long 
           asm volatile("fence.acq_rel.sys;" ::: "memory");
           rv = __longlong_as_double((long long)((w1v & 0xffffffff00000000ull) | (w0v >> 32)));
         }
-        double tot = 0.0;
-        for (int r = 0; r < P.world; ++r) tot += __shfl_sync(0xffffffffu, rv, r);  // rank order: identical bits on every rank
+        double tot = 0.0, tot2 = 0.0;
+        for (int r = 0; r < P.world; ++r) {  // rank order: identical bits on every rank
+          tot += __shfl_sync(0xffffffffu, rv, r);
+          tot2 += __shfl_sync(0xffffffffu, rv, 16 + r);
+        }
         if (kind == FB_RR) s1 = tot;
         else s0 = tot;
+        if (both) s1 = tot2;
         if (timed && lane == 0) {
           red64[FRED_T_PEER] += global_ns() - ns_arrive;
           red64[FRED_N_BAR] += 1ull;
         }
       }
       ok = __all_sync(0xffffffffu, ok);
-      if (lane == 0) {
-        double* bc = a.sync->bcast[gen & 1];
-        bc[0] = s0;
-        bc[1] = s1;
-        bc[2] = ok ? 1.0 : 0.0;
-        st_release_gpu_u64(&a.sync->release, gen);
+      if (lane < 3) {
+        const unsigned long long g32 = gen & 0xffffffffull;
+        const unsigned long long bits = lane == 0 ? (unsigned long long)__double_as_longlong(s0)
+                                       : lane == 1 ? (unsigned long long)__double_as_longlong(s1) : (ok ? ~0ull : 0ull);
+        asm volatile("fence.acq_rel.gpu;" ::: "memory");  // everything the arrivals released is ordered before the words
+        asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(&a.sync->rel[2 * lane]), "l"(((bits & 0xffffffffull) << 32) | g32),
+                     "l"((bits & 0xffffffff00000000ull) | g32) : "memory");
       }
     }
-    if (lane == 0) {
-      const long long w0 = clock64();
-      bool seen = true;
-      while (ld_acquire_gpu_u64(&a.sync->release) < gen)
-        if (clock64() - w0 > 3 * a.spin_limit) {
+  }
+  if (warp == 0) {
+    // every CTA: lanes 0..2 poll one pair each until both words carry this generation
+    const unsigned long long g32 = gen & 0xffffffffull;
+    unsigned long long w0v = 0ull, w1v = 0ull;
+    bool seen = true;
+    if (lane < 3) {
+      const long long c0k = clock64();
+      while (true) {
+        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0v), "=l"(w1v) : "l"(&a.sync->rel[2 * lane]) : "memory");
+        if ((w0v & 0xffffffffull) == g32 && (w1v & 0xffffffffull) == g32) break;
+        if (clock64() - c0k > 3 * a.spin_limit) {
           seen = false;
           break;
         }
-      const double* bc = a.sync->bcast[gen & 1];
-      red[32] = __ldcg(bc + 0);
-      red[33] = __ldcg(bc + 1);
-      red[34] = seen ? __ldcg(bc + 2) : 0.0;
+      }
+      asm volatile("fence.acq_rel.gpu;" ::: "memory");
     }
+    seen = __all_sync(0xffffffffu, seen);
+    const unsigned long long bits = (w1v & 0xffffffff00000000ull) | (w0v >> 32);
+    if (lane < 2) red[32 + lane] = __longlong_as_double((long long)bits);
+    if (lane == 2) red[34] = (seen && bits != 0ull) ? 1.0 : 0.0;
   }
   bar_consumers<NCT>();
   t0 = red[32];
@@ -326,13 +377,31 @@ struct FusedSmem {
 };
 
 // Value-less local grid barrier (consumer threads of every CTA).  Returns false on timeout.
+// halo_epoch != 0 (row-partitioned, after t = G^T r): CTA 0 first waits until every neighbour whose rows this rank's halo
+// holds has flagged that sweep (FusedXchg::hflag, raised by the neighbour's last boundary CTA -- early in ITS sweep, the
+// boundary blocks go first), fences at system scope and only then arrives: the local release/acquire chain hands the
+// halo data on to every CTA.  This replaces an all-to-all exchange by a (normally already satisfied) neighbour flag.
 template <int NCW>
-__device__ __forceinline__ bool fused_light_barrier(const FusedArgs& a, unsigned long long& lgen, double* red) {
+__device__ __forceinline__ bool fused_light_barrier(const FusedArgs& a, unsigned long long& lgen, double* red,
+                                                    unsigned long long halo_epoch = 0ull) {
   constexpr int NCT = NCW * 32;
   lgen += 1;
   bar_consumers<NCT>();
   if (threadIdx.x == 0) {
-    red_release_gpu_add_u64(&a.sync->light, 1ull);
+    bool halo_ok = true;
+    if (halo_epoch != 0ull && blockIdx.x == 0 && a.peer.n_recv > 0) {
+      const long long w0 = clock64();
+      for (int k = 0; k < a.peer.n_recv && halo_ok; ++k) {
+        const unsigned long long* f = &a.peer.xchg[a.peer.rank]->hflag[a.peer.recv_peer[k]];
+        while (f_ld_relaxed_sys(f) < halo_epoch)
+          if (clock64() - w0 > a.spin_limit) {
+            halo_ok = false;
+            break;
+          }
+      }
+      asm volatile("fence.acq_rel.sys;" ::: "memory");
+    }
+    if (halo_ok) red_release_gpu_add_u64(&a.sync->light, 1ull);
     const unsigned long long target = lgen * (unsigned long long)gridDim.x;
     const long long w0 = clock64();
     bool seen = true;
@@ -351,9 +420,30 @@ __device__ __forceinline__ bool fused_light_barrier(const FusedArgs& a, unsigned
 //   PH = 1 (G^T):  t = sum [/ d]
 //   PH = 2 (G):    z = sum + eps r [/ d] ; acc += r z
 //   PH = 3 (A):    q = sum ; acc += p q
+// Called by every consumer thread of a CTA that owns boundary blocks, right after the last of them in a t = G^T r sweep:
+// the CTA's peer stores are fenced at system scope, then counted; the CTA that completes the count raises this sweep's
+// epoch in hflag[my rank] of every neighbour it pushes to (one 8-byte NVLink store each).
+template <int NCW>
+__device__ __forceinline__ void fused_boundary_done(const FusedArgs& a, const FusedMat& M, unsigned long long halo_epoch,
+                                                    unsigned long long sweep_no) {
+  bar_consumers<NCW * 32>();  // every consumer thread's stores of the boundary blocks are issued
+  if (threadIdx.x == 0) {
+    asm volatile("fence.acq_rel.sys;" ::: "memory");  // cumulative over the CTA (bar.sync): the peer stores are performed
+    const unsigned long long n_bnd_ctas = (unsigned long long)min(M.nbnd, (int)gridDim.x);
+    unsigned long long old;
+    asm volatile("atom.acq_rel.gpu.global.add.u64 %0, [%1], 1;" : "=l"(old) : "l"(&a.sync->bdone) : "memory");
+    if (old + 1ull == sweep_no * n_bnd_ctas) {  // the last boundary CTA of this sweep
+      asm volatile("fence.acq_rel.sys;" ::: "memory");
+      for (int s = 0; s < a.peer.n_push; ++s)
+        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&a.peer.xchg[a.peer.push_peer[s]]->hflag[a.peer.rank]), "l"(halo_epoch) : "memory");
+    }
+  }
+}
+
 template <int PH, int CAP, int STAGES, int NCW, typename VT, typename CT>
 __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& M, const FusedSmem<CAP, STAGES, VT, CT>& sm,
-                                            long long& item, const double* gv, double& acc, bool& pushed) {
+                                            long long& item, const double* gv, double& acc, bool& pushed,
+                                            unsigned long long halo_epoch = 0ull, unsigned long long sweep_no = 0ull) {
   using C = StreamCfg<CAP, VT, CT>;
   constexpr bool DELTA = C::DELTA;
   constexpr int NCT = NCW * 32;
@@ -395,7 +485,10 @@ __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& 
       }
   };
 
+  // (row-partitioned, PH 1) boundary blocks are dealt first: block index firstb + it * G < M.nbnd
+  const int n_bnd_items = (PH == 1 && a.peer.world > 1 && firstb < M.nbnd) ? (M.nbnd - firstb + G - 1) / G : 0;
   for (int it = 0; it < n_items; ++it, ++item) {
+    if (PH == 1 && n_bnd_items > 0 && it == n_bnd_items) fused_boundary_done<NCW>(a, M, halo_epoch, sweep_no);
     const int slot = (int)(item % STAGES);
     mbar_wait(sm.full + slot, (uint32_t)((item / STAGES) & 1));
     const int4 info = sm.hdr[slot];
@@ -454,6 +547,7 @@ __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& 
     __syncwarp();
     if (lane == 0) mbar_arrive(sm.empty + slot);
   }
+  if (PH == 1 && n_bnd_items > 0 && n_items == n_bnd_items) fused_boundary_done<NCW>(a, M, halo_epoch, sweep_no);
 }
 
 // MINB = resident CTAs per SM the register allocation is held to (4 -> 56 registers: the occupancy of the standalone
@@ -614,13 +708,30 @@ __global__ void __launch_bounds__((NCW + 1) * 32, MINB) pcg_fused_kernel(const _
     }
   };
 
+  // Row-partitioned: the hand-over of t between P1 and P2 needs the local grid and the NEIGHBOURS' boundary rows only,
+  // so barrier B1 is a local barrier + neighbour flags, and ||r||^2 of the previous update travels with rho in B2 (the
+  // P2 sweep that runs ahead of a converged test only writes z).
+  const unsigned long long halo_base = (a.peer.world > 1) ? a.peer.epoch[FB_HALO] : 0ull;
+  unsigned long long n_p1 = 0;
+
   while (!done) {
     // ---- P1: t = G^T r ----
     acc = 0.0;
     pushed = false;
-    fused_sweep<1, CAP, STAGES, NCW, VT, CT>(a, a.GT, sm, item, a.r, acc, pushed);
-    ok = fused_barrier<NCW>(a, gen, FB_RR, 0.0, pending ? acc_rr : 0.0, pushed, red, t0, t1);
+    n_p1 += 1;
+    fused_sweep<1, CAP, STAGES, NCW, VT, CT>(a, a.GT, sm, item, a.r, acc, pushed, halo_base + n_p1, n_p1);
+    ok = fused_light_barrier<NCW>(a, lgen, red, (a.peer.world > 1) ? halo_base + n_p1 : 0ull);
     stamp(0);
+    if (!ok) {
+      breakdown = 3;
+      break;
+    }
+    // ---- P2: z = G t + eps r ; rho ----
+    acc = 0.0;
+    pushed = false;
+    fused_sweep<2, CAP, STAGES, NCW, VT, CT>(a, a.G, sm, item, a.t, acc, pushed);
+    ok = fused_barrier<NCW>(a, gen, FB_RHO, acc, pending ? acc_rr : 0.0, pushed, red, t0, t1, true);
+    stamp(1);
     if (!ok) {
       breakdown = 3;
       break;
@@ -640,16 +751,6 @@ __global__ void __launch_bounds__((NCW + 1) * 32, MINB) pcg_fused_kernel(const _
         break;
       }
       if (iter >= max_iter) break;
-    }
-    // ---- P2: z = G t + eps r ; rho ----
-    acc = 0.0;
-    pushed = false;
-    fused_sweep<2, CAP, STAGES, NCW, VT, CT>(a, a.G, sm, item, a.t, acc, pushed);
-    ok = fused_barrier<NCW>(a, gen, FB_RHO, acc, 0.0, pushed, red, t0, t1);
-    stamp(1);
-    if (!ok) {
-      breakdown = 3;
-      break;
     }
     rho = t0;
     const bool first = (iter == 0);
@@ -749,6 +850,7 @@ __global__ void __launch_bounds__((NCW + 1) * 32, MINB) pcg_fused_kernel(const _
   if (lead && a.peer.world > 1) {  // the epoch counters survive the solve (monotonic across solves and relayouts)
     const unsigned long long* red64 = reinterpret_cast<const unsigned long long*>(red);
     for (int k = 0; k < FB_KINDS; ++k) a.peer.epoch[k] = red64[FRED_EPOCH + k];
+    a.peer.epoch[FB_HALO] = halo_base + n_p1;
   }
   if (lead) {
     sc->bnorm = bnorm;
