@@ -30,6 +30,8 @@ struct Inst {
     return 0;
   }
   static int launch(const FusedArgs& a, int grid, cudaStream_t st) {
+    // the LL partial slots must not carry a tag of an earlier launch (generations restart at 1)
+    B2_CUDA(cudaMemsetAsync(a.partials, 0, (size_t)4 * grid * sizeof(unsigned long long), st));
     void* args[] = {(void*)&a};
     B2_CUDA(cudaLaunchCooperativeKernel(fn(), dim3((unsigned)grid), dim3(threads), args, (size_t)smem(), st));
     return 0;
@@ -106,7 +108,7 @@ int fused_plan(b200spai_csr_s* A, b200spai_csr_s* G, b200spai_csr_s* GT, cudaStr
   if (which == 2) B2_TRY((minb == 3 ? grid_for<4096, 3> : grid_for<4096, 4>)(fmt, &grid));
   else B2_TRY((minb == 3 ? grid_for<2048, 3> : grid_for<2048, 4>)(fmt, &grid));
   plan->minb = minb;
-  if (grid <= 0 || 2 * grid > MAX_PARTIALS) return 0;
+  if (grid <= 0 || 4 * grid > MAX_PARTIALS) return 0;
   plan->which = which;
   plan->fmt = fmt;
   plan->grid = grid;

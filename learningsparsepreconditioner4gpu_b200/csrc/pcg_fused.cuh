@@ -46,7 +46,7 @@
 namespace b200spai {
 
 constexpr int FUSED_MAXR = 16;
-enum { FB_INIT = 0, FB_RR = 1, FB_RHO = 2, FB_PQ = 3, FB_READY = 4, FB_HALO = 5, FB_KINDS = 6 };
+enum { FB_INIT = 0, FB_RR = 1, FB_RHO = 2, FB_PQ = 3, FB_READY = 4, FB_HALO = 5 /* +0 t, +1 z, +2 q */, FB_KINDS = 8 };
 
 struct FusedMat {
   const int* rowptr;
@@ -69,15 +69,14 @@ struct FusedSync {  // one per solver, zeroed before every launch
   unsigned long long pad1[10];
   unsigned long long light;  // arrive counter of the value-less local barrier
   unsigned long long pad2[15];
-  unsigned long long bdone;  // CTAs that finished (and fenced) the boundary blocks of a t = G^T r sweep
-  unsigned long long pad3[15];
+  unsigned long long bdone[3][16];  // [t, z, q][0]: CTAs that finished (and fenced) the boundary blocks of such a sweep
 };
 
 struct alignas(16) FusedXchg {  // one per rank, inside the peer-mapped segment; never reset (epochs are monotonic across solves)
   // [kind][source rank] = two words {low 32 bits of the value << 32 | epoch, high 32 bits of the value | epoch}
   unsigned long long w[FB_KINDS][FUSED_MAXR][2];
-  // [source rank] = epoch of the last t = G^T r sweep whose boundary rows that rank has stored into this rank's halo
-  unsigned long long hflag[FUSED_MAXR];
+  // [t, z, q][source rank] = epoch of the last sweep of that kind whose boundary rows that rank has stored into this rank's halo
+  unsigned long long hflag[3][FUSED_MAXR];
 };
 
 struct FusedPeer {
@@ -104,7 +103,7 @@ struct FusedArgs {
   double eps;
   int precond;
   PcgScalars* sc;
-  double* partials;      // [2 * gridDim.x]
+  double* partials;      // [4 * gridDim.x] 8-byte LL words (two tagged pairs per CTA), zeroed before every launch
   double* hist;
   FusedSync* sync;
   long long spin_limit;  // clock64 ticks before a wait gives up
@@ -188,31 +187,78 @@ __device__ __forceinline__ void ld_relaxed_sys_v2(const unsigned long long* p, u
 // Shared scratch of the barrier code: red[0..31] warp partials, [32..35] broadcast, then (CTA 0 only) the epoch counters
 // of the cross-rank exchange and the barrier timers, all 8-byte slots.
 constexpr int FRED_EPOCH = 36;              // FB_KINDS slots
-constexpr int FRED_T_LOCAL = 42;            // ns CTA 0 waited for the last local CTA (after its own arrival)
-constexpr int FRED_T_PEER = 43;             // ns between the last local arrival and the last peer's contribution
-constexpr int FRED_N_BAR = 44;              // cross-rank barriers timed
-constexpr int FRED_SLOTS = 46;
+constexpr int FRED_T_LOCAL = 44;            // ns CTA 0 waited for the last local CTA's partials (after its own arrival)
+constexpr int FRED_T_PEER = 45;             // ns from there to the last peer's contribution
+constexpr int FRED_N_BAR = 46;              // cross-rank barriers timed
+constexpr int FRED_SLOTS = 48;
+static_assert(FRED_EPOCH + FB_KINDS <= FRED_T_LOCAL, "epoch slots overlap the timers");
+
+// 64 bits as two tagged words {low half | tag, high half | tag} (NCCL-LL style): 8-byte words are single-copy atomic, so a
+// reader that finds `tag` in both words holds the value the writer stored with it -- value and flag in one access.
+__device__ __forceinline__ void ll_store_gpu(unsigned long long* slot, unsigned long long bits, unsigned long long tag32) {
+  asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(slot), "l"(((bits & 0xffffffffull) << 32) | tag32),
+               "l"((bits & 0xffffffff00000000ull) | tag32) : "memory");
+}
+__device__ __forceinline__ bool ll_load_gpu(const unsigned long long* slot, unsigned long long tag32, unsigned long long& bits) {
+  unsigned long long w0, w1;
+  asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(slot) : "memory");
+  bits = (w1 & 0xffffffff00000000ull) | (w0 >> 32);
+  return (w0 & 0xffffffffull) == tag32 && (w1 & 0xffffffffull) == tag32;
+}
+
+// (row-partitioned) CTA 0, thread 0: wait until every neighbour whose rows this rank's halo holds has flagged the sweep
+// `halo_epoch` of kind `hk` (0: t, 1: z, 2: q), then fence at system scope.  The flag is raised by the neighbour's last
+// boundary CTA early in ITS sweep (the boundary blocks go first), so this normally returns at once.
+__device__ __forceinline__ bool fused_wait_halo(const FusedArgs& a, int hk, unsigned long long halo_epoch) {
+  bool ok = true;
+  const long long w0 = clock64();
+  for (int k = 0; k < a.peer.n_recv && ok; ++k) {
+    const unsigned long long* f = &a.peer.xchg[a.peer.rank]->hflag[hk][a.peer.recv_peer[k]];
+    while (f_ld_relaxed_sys(f) < halo_epoch)
+      if (clock64() - w0 > a.spin_limit) {
+        ok = false;
+        break;
+      }
+  }
+  asm volatile("fence.acq_rel.sys;" ::: "memory");
+  return ok;
+}
 
 // Grid barrier + deterministic reduction of (v0, v1) + (world > 1) all-reduce over the ranks.  Called by every
 // CONSUMER thread of every CTA; returns false when a wait timed out (peer or CTA gone): the solve is then abandoned.
-// `pushed`: this thread stored into a peer's memory since the last barrier.  Every barrier kind carries ONE value
-// (v1 for FB_RR, v0 otherwise); the other is passed through the local reduction only.
 //
-// Cross-rank exchange (NCCL-LL style): the value travels WITH its flag -- two 8-byte words {low half | epoch, high half |
-// epoch} written by one 16-byte store into slot [kind][source rank] of every rank's exchange block; the receiver polls
-// the slot until both words carry the epoch.  8-byte words are single-copy atomic, so no value can be read with a stale
-// half, and no separate flag store (and no release on the far side of the NVLink round trip) is needed.  Ordering of
-// the HALO data: a CTA whose threads pushed fences at system scope ONCE (thread 0, after the CTA barrier: cumulative over
-// the CTA's stores) before it arrives; CTA 0 acquires the arrivals, fences at system scope and only then sends its
-// words; the receiver fences after the last word arrived and then releases its grid.
-// `both`: the barrier all-reduces v0 under `kind` AND v1 under FB_RR in the same exchange (lanes 0..15 / 16..31).
+// Local part: every CTA publishes its two partial sums as LL words tagged with the barrier generation (arrival and value
+// in one store, after a gpu-scope fence that orders the CTA's vector writes); the consumer threads of CTA 0 poll one
+// slot each (CTAs tid, tid + 256, ...), sum in a fixed order (thread-strided, warp tree, warps in index order); warp 0
+// exchanges with the other ranks and publishes the totals as LL words every CTA polls -- two L2 round trips end to end.
+//
+// Cross-rank part: the rank's total travels as an LL pair into slot [kind][source rank] of every rank's exchange block;
+// the receiver polls until both words carry the epoch and sums IN RANK ORDER (identical bits on every rank).  `both`:
+// v0 under `kind` AND v1 under FB_RR in the same exchange (lanes 0..15 / 16..31).
+//
+// Halo data.  halo_kind >= 0 (sweep barriers): boundary rows were flagged by fused_boundary_done when they were stored;
+// CTA 0 waits for its neighbours' flags (fused_wait_halo) BEFORE it joins the barrier, so the scalar exchange itself
+// needs no system-scope fence on either side.  halo_kind < 0 (init / ready barriers): `pushed` CTAs fence at system
+// scope before they arrive and the master fences around the exchange, which then also orders the pushed data.
 template <int NCW>
 __device__ __forceinline__ bool fused_barrier(const FusedArgs& a, unsigned long long& gen, int kind, double v0, double v1,
-                                              bool pushed, double* red, double& t0, double& t1, bool both = false) {
+                                              bool pushed, double* red, double& t0, double& t1, bool both = false,
+                                              int halo_kind = -1, unsigned long long halo_epoch = 0ull) {
   constexpr int NCT = NCW * 32;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned G = gridDim.x;
+  const bool master = blockIdx.x == 0;
+  const bool fenced = halo_kind < 0;  // the exchange itself orders pushed data
   gen += 1;
+  const unsigned long long g32 = gen & 0xffffffffull;
+  unsigned long long* ll = reinterpret_cast<unsigned long long*>(a.partials);  // [G][4] LL words
+  unsigned long long* red64 = reinterpret_cast<unsigned long long*>(red);
+  const bool timed = master && a.prof != nullptr && a.peer.world > 1;
+  unsigned long long ns_arrive = 0ull;
+  if (master && tid == 0) {
+    red[35] = 1.0;
+    if (!fenced && a.peer.world > 1 && a.peer.n_recv > 0 && !fused_wait_halo(a, halo_kind, halo_epoch)) red[35] = 0.0;
+  }
   v0 = warp_sum(v0);
   v1 = warp_sum(v1);
   if (lane == 0) {
@@ -220,69 +266,53 @@ __device__ __forceinline__ bool fused_barrier(const FusedArgs& a, unsigned long 
     red[16 + warp] = v1;
   }
   const bool cta_pushed = bar_or_consumers<NCT>(pushed);
-  const bool master = blockIdx.x == 0;
-  unsigned long long* red64 = reinterpret_cast<unsigned long long*>(red);
-  const bool timed = master && a.prof != nullptr && a.peer.world > 1;
-  unsigned long long ns_arrive = 0ull;
   if (warp == 0) {
     double c0 = (lane < NCW) ? red[lane] : 0.0, c1 = (lane < NCW) ? red[16 + lane] : 0.0;
     c0 = warp_sum(c0);
     c1 = warp_sum(c1);
-    if (lane == 0) {
-      a.partials[blockIdx.x] = c0;
-      a.partials[G + blockIdx.x] = c1;
-      if (cta_pushed) asm volatile("fence.acq_rel.sys;" ::: "memory");  // the CTA's peer stores are performed before it arrives
-      red_release_gpu_add_u64(&a.sync->arrive, 1ull);  // release: partials, vector writes and (fenced) peer stores
-      if (master) {  // wait for every CTA
-        if (timed) ns_arrive = global_ns();
-        int okw = 1;
-        const long long w0 = clock64();
-        while (ld_acquire_gpu_u64(&a.sync->arrive) < gen * (unsigned long long)G)
-          if (clock64() - w0 > a.spin_limit) {
-            okw = 0;
-            break;
-          }
-        red[35] = okw ? 1.0 : 0.0;
-        if (timed) {
-          const unsigned long long now = global_ns();
-          red64[FRED_T_LOCAL] += now - ns_arrive;
-          ns_arrive = now;
-        }
-      }
+    if (lane < 2) {
+      if (fenced && cta_pushed) asm volatile("fence.acq_rel.sys;" ::: "memory");  // the CTA's peer stores are performed before it arrives
+      else asm volatile("fence.acq_rel.gpu;" ::: "memory");                       // the CTA's vector writes (bar.sync: cumulative)
+      ll_store_gpu(ll + 4 * blockIdx.x + 2 * lane, (unsigned long long)__double_as_longlong(lane == 0 ? c0 : c1), g32);
     }
+    if (timed && lane == 0) ns_arrive = global_ns();
   }
   if (master) {
-    // ---- master CTA: all consumer threads fetch the per-CTA partials at once (one L2 round trip instead of G / 32 in a
-    // row), fixed order: thread-strided sums, warp tree, warps in index order; then warp 0 exchanges with the other
-    // ranks and releases the grid ----
-    bar_consumers<NCT>();  // thread 0 has acquired every arrival
-    double s0, s1;
-    {
-      const unsigned i0 = tid, i1 = tid + NCT, i2 = tid + 2 * NCT;
-      const double a0 = i0 < G ? __ldcg(a.partials + i0) : 0.0, b0 = i0 < G ? __ldcg(a.partials + G + i0) : 0.0;
-      const double a1 = i1 < G ? __ldcg(a.partials + i1) : 0.0, b1 = i1 < G ? __ldcg(a.partials + G + i1) : 0.0;
-      const double a2 = i2 < G ? __ldcg(a.partials + i2) : 0.0, b2 = i2 < G ? __ldcg(a.partials + G + i2) : 0.0;
-      s0 = (a0 + a1) + a2;
-      s1 = (b0 + b1) + b2;
-      for (unsigned i = tid + 3 * NCT; i < G; i += NCT) {
-        s0 += __ldcg(a.partials + i);
-        s1 += __ldcg(a.partials + G + i);
-      }
+    // ---- master CTA: fetch every CTA's partials (the poll IS the arrival wait) ----
+    double s0 = 0.0, s1 = 0.0;
+    bool okp = true;
+    const long long c0k = clock64();
+    for (unsigned i = tid; i < G; i += NCT) {
+      unsigned long long b0 = 0ull, b1 = 0ull;
+      while (!(ll_load_gpu(ll + 4 * i, g32, b0) & ll_load_gpu(ll + 4 * i + 2, g32, b1)))
+        if (clock64() - c0k > a.spin_limit) {
+          okp = false;
+          break;
+        }
+      s0 += __longlong_as_double((long long)b0);
+      s1 += __longlong_as_double((long long)b1);
     }
+    asm volatile("fence.acq_rel.gpu;" ::: "memory");
     s0 = warp_sum(s0);
     s1 = warp_sum(s1);
-    const int ok_arrive = red[35] != 0.0;
+    okp = __all_sync(0xffffffffu, okp);
     if (lane == 0) {
       red[warp] = s0;
       red[16 + warp] = s1;
     }
-    bar_consumers<NCT>();
+    const bool ok_halo = red[35] != 0.0;  // written before the first CTA barrier of this call
+    const bool timed_out = bar_or_consumers<NCT>(!okp);
     if (warp == 0) {
-      int ok = ok_arrive;
       s0 = (lane < NCW) ? red[lane] : 0.0;
       s1 = (lane < NCW) ? red[16 + lane] : 0.0;
+      int ok = ok_halo && !timed_out;
       s0 = warp_sum(s0);
       s1 = warp_sum(s1);
+      if (timed && lane == 0) {
+        const unsigned long long now = global_ns();
+        red64[FRED_T_LOCAL] += now - ns_arrive;
+        ns_arrive = now;
+      }
       const FusedPeer& P = a.peer;
       if (P.world > 1) {
         // lanes 0..15 carry `kind`, lanes 16..31 carry FB_RR when `both` (world <= 16)
@@ -296,20 +326,20 @@ __device__ __forceinline__ bool fused_barrier(const FusedArgs& a, unsigned long 
         double rv = 0.0;
         if (pr < P.world && (half == 0 || both)) {
           const unsigned long long bits = (unsigned long long)__double_as_longlong(sv);
-          asm volatile("fence.acq_rel.sys;" ::: "memory");  // after the acquired arrivals, before the words leave
+          if (fenced) asm volatile("fence.acq_rel.sys;" ::: "memory");  // after the acquired arrivals, before the words leave
           st_relaxed_sys_v2(&P.xchg[pr]->w[mykind][P.rank][0], ((bits & 0xffffffffull) << 32) | e32, (bits & 0xffffffff00000000ull) | e32);
           const unsigned long long* mine = &P.xchg[P.rank]->w[mykind][pr][0];
           unsigned long long w0v = 0ull, w1v = 0ull;
-          const long long c0k = clock64();
+          const long long c1k = clock64();
           while (true) {
             ld_relaxed_sys_v2(mine, w0v, w1v);
             if ((w0v & 0xffffffffull) == e32 && (w1v & 0xffffffffull) == e32) break;
-            if (clock64() - c0k > a.spin_limit) {
+            if (clock64() - c1k > a.spin_limit) {
               ok = 0;
               break;
             }
           }
-          asm volatile("fence.acq_rel.sys;" ::: "memory");
+          if (fenced) asm volatile("fence.acq_rel.sys;" ::: "memory");
           rv = __longlong_as_double((long long)((w1v & 0xffffffff00000000ull) | (w0v >> 32)));
         }
         double tot = 0.0, tot2 = 0.0;
@@ -327,34 +357,27 @@ __device__ __forceinline__ bool fused_barrier(const FusedArgs& a, unsigned long 
       }
       ok = __all_sync(0xffffffffu, ok);
       if (lane < 3) {
-        const unsigned long long g32 = gen & 0xffffffffull;
         const unsigned long long bits = lane == 0 ? (unsigned long long)__double_as_longlong(s0)
                                        : lane == 1 ? (unsigned long long)__double_as_longlong(s1) : (ok ? ~0ull : 0ull);
         asm volatile("fence.acq_rel.gpu;" ::: "memory");  // everything the arrivals released is ordered before the words
-        asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(&a.sync->rel[2 * lane]), "l"(((bits & 0xffffffffull) << 32) | g32),
-                     "l"((bits & 0xffffffff00000000ull) | g32) : "memory");
+        ll_store_gpu(&a.sync->rel[2 * lane], bits, g32);
       }
     }
   }
   if (warp == 0) {
     // every CTA: lanes 0..2 poll one pair each until both words carry this generation
-    const unsigned long long g32 = gen & 0xffffffffull;
-    unsigned long long w0v = 0ull, w1v = 0ull;
+    unsigned long long bits = 0ull;
     bool seen = true;
     if (lane < 3) {
       const long long c0k = clock64();
-      while (true) {
-        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0v), "=l"(w1v) : "l"(&a.sync->rel[2 * lane]) : "memory");
-        if ((w0v & 0xffffffffull) == g32 && (w1v & 0xffffffffull) == g32) break;
+      while (!ll_load_gpu(&a.sync->rel[2 * lane], g32, bits))
         if (clock64() - c0k > 3 * a.spin_limit) {
           seen = false;
           break;
         }
-      }
       asm volatile("fence.acq_rel.gpu;" ::: "memory");
     }
     seen = __all_sync(0xffffffffu, seen);
-    const unsigned long long bits = (w1v & 0xffffffff00000000ull) | (w0v >> 32);
     if (lane < 2) red[32 + lane] = __longlong_as_double((long long)bits);
     if (lane == 2) red[34] = (seen && bits != 0ull) ? 1.0 : 0.0;
   }
@@ -389,18 +412,7 @@ __device__ __forceinline__ bool fused_light_barrier(const FusedArgs& a, unsigned
   bar_consumers<NCT>();
   if (threadIdx.x == 0) {
     bool halo_ok = true;
-    if (halo_epoch != 0ull && blockIdx.x == 0 && a.peer.n_recv > 0) {
-      const long long w0 = clock64();
-      for (int k = 0; k < a.peer.n_recv && halo_ok; ++k) {
-        const unsigned long long* f = &a.peer.xchg[a.peer.rank]->hflag[a.peer.recv_peer[k]];
-        while (f_ld_relaxed_sys(f) < halo_epoch)
-          if (clock64() - w0 > a.spin_limit) {
-            halo_ok = false;
-            break;
-          }
-      }
-      asm volatile("fence.acq_rel.sys;" ::: "memory");
-    }
+    if (halo_epoch != 0ull && blockIdx.x == 0 && a.peer.n_recv > 0) halo_ok = fused_wait_halo(a, 0, halo_epoch);
     if (halo_ok) red_release_gpu_add_u64(&a.sync->light, 1ull);
     const unsigned long long target = lgen * (unsigned long long)gridDim.x;
     const long long w0 = clock64();
@@ -420,22 +432,24 @@ __device__ __forceinline__ bool fused_light_barrier(const FusedArgs& a, unsigned
 //   PH = 1 (G^T):  t = sum [/ d]
 //   PH = 2 (G):    z = sum + eps r [/ d] ; acc += r z
 //   PH = 3 (A):    q = sum ; acc += p q
-// Called by every consumer thread of a CTA that owns boundary blocks, right after the last of them in a t = G^T r sweep:
-// the CTA's peer stores are fenced at system scope, then counted; the CTA that completes the count raises this sweep's
-// epoch in hflag[my rank] of every neighbour it pushes to (one 8-byte NVLink store each).
+// Called by every consumer thread of a CTA that owns boundary blocks, right after the last of them in a sweep of kind
+// hk (0: t = G^T r, 1: z = G t, 2: q = A p): the CTA's peer stores are fenced at system scope, then counted; the CTA that
+// completes the count raises this sweep's epoch in hflag[hk][my rank] of every neighbour it pushes to (one 8-byte
+// NVLink store each).  This happens EARLY in the sweep -- the boundary blocks are dealt first -- so neither the fence nor
+// the neighbours' wait for the flag sits on the critical path of the barrier that closes the sweep.
 template <int NCW>
-__device__ __forceinline__ void fused_boundary_done(const FusedArgs& a, const FusedMat& M, unsigned long long halo_epoch,
+__device__ __forceinline__ void fused_boundary_done(const FusedArgs& a, const FusedMat& M, int hk, unsigned long long halo_epoch,
                                                     unsigned long long sweep_no) {
   bar_consumers<NCW * 32>();  // every consumer thread's stores of the boundary blocks are issued
   if (threadIdx.x == 0) {
     asm volatile("fence.acq_rel.sys;" ::: "memory");  // cumulative over the CTA (bar.sync): the peer stores are performed
     const unsigned long long n_bnd_ctas = (unsigned long long)min(M.nbnd, (int)gridDim.x);
     unsigned long long old;
-    asm volatile("atom.acq_rel.gpu.global.add.u64 %0, [%1], 1;" : "=l"(old) : "l"(&a.sync->bdone) : "memory");
+    asm volatile("atom.acq_rel.gpu.global.add.u64 %0, [%1], 1;" : "=l"(old) : "l"(&a.sync->bdone[hk][0]) : "memory");
     if (old + 1ull == sweep_no * n_bnd_ctas) {  // the last boundary CTA of this sweep
       asm volatile("fence.acq_rel.sys;" ::: "memory");
       for (int s = 0; s < a.peer.n_push; ++s)
-        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&a.peer.xchg[a.peer.push_peer[s]]->hflag[a.peer.rank]), "l"(halo_epoch) : "memory");
+        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(&a.peer.xchg[a.peer.push_peer[s]]->hflag[hk][a.peer.rank]), "l"(halo_epoch) : "memory");
     }
   }
 }
@@ -485,10 +499,10 @@ __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& 
       }
   };
 
-  // (row-partitioned, PH 1) boundary blocks are dealt first: block index firstb + it * G < M.nbnd
-  const int n_bnd_items = (PH == 1 && a.peer.world > 1 && firstb < M.nbnd) ? (M.nbnd - firstb + G - 1) / G : 0;
+  // (row-partitioned) boundary blocks are dealt first: block index firstb + it * G < M.nbnd
+  const int n_bnd_items = (a.peer.world > 1 && firstb < M.nbnd) ? (M.nbnd - firstb + G - 1) / G : 0;
   for (int it = 0; it < n_items; ++it, ++item) {
-    if (PH == 1 && n_bnd_items > 0 && it == n_bnd_items) fused_boundary_done<NCW>(a, M, halo_epoch, sweep_no);
+    if (n_bnd_items > 0 && it == n_bnd_items) fused_boundary_done<NCW>(a, M, PH - 1, halo_epoch, sweep_no);
     const int slot = (int)(item % STAGES);
     mbar_wait(sm.full + slot, (uint32_t)((item / STAGES) & 1));
     const int4 info = sm.hdr[slot];
@@ -547,7 +561,7 @@ __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& 
     __syncwarp();
     if (lane == 0) mbar_arrive(sm.empty + slot);
   }
-  if (PH == 1 && n_bnd_items > 0 && n_items == n_bnd_items) fused_boundary_done<NCW>(a, M, halo_epoch, sweep_no);
+  if (n_bnd_items > 0 && n_items == n_bnd_items) fused_boundary_done<NCW>(a, M, PH - 1, halo_epoch, sweep_no);
 }
 
 // MINB = resident CTAs per SM the register allocation is held to (4 -> 56 registers: the occupancy of the standalone
@@ -711,16 +725,19 @@ __global__ void __launch_bounds__((NCW + 1) * 32, MINB) pcg_fused_kernel(const _
   // Row-partitioned: the hand-over of t between P1 and P2 needs the local grid and the NEIGHBOURS' boundary rows only,
   // so barrier B1 is a local barrier + neighbour flags, and ||r||^2 of the previous update travels with rho in B2 (the
   // P2 sweep that runs ahead of a converged test only writes z).
-  const unsigned long long halo_base = (a.peer.world > 1) ? a.peer.epoch[FB_HALO] : 0ull;
-  unsigned long long n_p1 = 0;
+  // the boundaries of z and q are flagged the same way, so the scalar all-reduces B2 / B3 carry no system-scope fence
+  const bool multi = a.peer.world > 1;
+  const unsigned long long halo_base[3] = {multi ? a.peer.epoch[FB_HALO] : 0ull, multi ? a.peer.epoch[FB_HALO + 1] : 0ull,
+                                           multi ? a.peer.epoch[FB_HALO + 2] : 0ull};
+  unsigned long long n_p1 = 0, n_p2 = 0, n_p3 = 0;
 
   while (!done) {
     // ---- P1: t = G^T r ----
     acc = 0.0;
     pushed = false;
     n_p1 += 1;
-    fused_sweep<1, CAP, STAGES, NCW, VT, CT>(a, a.GT, sm, item, a.r, acc, pushed, halo_base + n_p1, n_p1);
-    ok = fused_light_barrier<NCW>(a, lgen, red, (a.peer.world > 1) ? halo_base + n_p1 : 0ull);
+    fused_sweep<1, CAP, STAGES, NCW, VT, CT>(a, a.GT, sm, item, a.r, acc, pushed, halo_base[0] + n_p1, n_p1);
+    ok = fused_light_barrier<NCW>(a, lgen, red, multi ? halo_base[0] + n_p1 : 0ull);
     stamp(0);
     if (!ok) {
       breakdown = 3;
@@ -729,8 +746,9 @@ __global__ void __launch_bounds__((NCW + 1) * 32, MINB) pcg_fused_kernel(const _
     // ---- P2: z = G t + eps r ; rho ----
     acc = 0.0;
     pushed = false;
-    fused_sweep<2, CAP, STAGES, NCW, VT, CT>(a, a.G, sm, item, a.t, acc, pushed);
-    ok = fused_barrier<NCW>(a, gen, FB_RHO, acc, pending ? acc_rr : 0.0, pushed, red, t0, t1, true);
+    n_p2 += 1;
+    fused_sweep<2, CAP, STAGES, NCW, VT, CT>(a, a.G, sm, item, a.t, acc, pushed, halo_base[1] + n_p2, n_p2);
+    ok = fused_barrier<NCW>(a, gen, FB_RHO, acc, pending ? acc_rr : 0.0, false, red, t0, t1, true, 1, halo_base[1] + n_p2);
     stamp(1);
     if (!ok) {
       breakdown = 3;
@@ -784,8 +802,9 @@ __global__ void __launch_bounds__((NCW + 1) * 32, MINB) pcg_fused_kernel(const _
     // ---- P3: q = A p ; p.q ----
     acc = 0.0;
     pushed = false;
-    fused_sweep<3, CAP, STAGES, NCW, VT, CT>(a, a.A, sm, item, a.p, acc, pushed);
-    ok = fused_barrier<NCW>(a, gen, FB_PQ, acc, 0.0, pushed, red, t0, t1);
+    n_p3 += 1;
+    fused_sweep<3, CAP, STAGES, NCW, VT, CT>(a, a.A, sm, item, a.p, acc, pushed, halo_base[2] + n_p3, n_p3);
+    ok = fused_barrier<NCW>(a, gen, FB_PQ, acc, 0.0, false, red, t0, t1, false, 2, halo_base[2] + n_p3);
     stamp(3);
     if (!ok) {
       breakdown = 3;
@@ -850,7 +869,9 @@ __global__ void __launch_bounds__((NCW + 1) * 32, MINB) pcg_fused_kernel(const _
   if (lead && a.peer.world > 1) {  // the epoch counters survive the solve (monotonic across solves and relayouts)
     const unsigned long long* red64 = reinterpret_cast<const unsigned long long*>(red);
     for (int k = 0; k < FB_KINDS; ++k) a.peer.epoch[k] = red64[FRED_EPOCH + k];
-    a.peer.epoch[FB_HALO] = halo_base + n_p1;
+    a.peer.epoch[FB_HALO] = halo_base[0] + n_p1;
+    a.peer.epoch[FB_HALO + 1] = halo_base[1] + n_p2;
+    a.peer.epoch[FB_HALO + 2] = halo_base[2] + n_p3;
   }
   if (lead) {
     sc->bnorm = bnorm;
