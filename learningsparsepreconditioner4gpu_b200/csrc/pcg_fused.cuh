@@ -69,6 +69,8 @@ struct FusedSync {  // one per solver, zeroed before every launch
   unsigned long long pad1[10];
   unsigned long long light;  // arrive counter of the value-less local barrier
   unsigned long long pad2[15];
+  unsigned long long light_rel;  // its release word (generation), written by the last arriver
+  unsigned long long pad2b[15];
   unsigned long long bdone[3][16];  // [t, z, q][0]: CTAs that finished (and fenced) the boundary blocks of such a sweep
 };
 
@@ -413,15 +415,21 @@ __device__ __forceinline__ bool fused_light_barrier(const FusedArgs& a, unsigned
   if (threadIdx.x == 0) {
     bool halo_ok = true;
     if (halo_epoch != 0ull && blockIdx.x == 0 && a.peer.n_recv > 0) halo_ok = fused_wait_halo(a, 0, halo_epoch);
-    if (halo_ok) red_release_gpu_add_u64(&a.sync->light, 1ull);
-    const unsigned long long target = lgen * (unsigned long long)gridDim.x;
-    const long long w0 = clock64();
+    // arrivals and polls use different lines: the CTA whose arrival completes the count (the atomic's return value tells
+    // it) publishes the generation; everybody else polls that word, undisturbed by the atomics
     bool seen = true;
-    while (ld_acquire_gpu_u64(&a.sync->light) < target)
-      if (clock64() - w0 > a.spin_limit) {
-        seen = false;
-        break;
-      }
+    unsigned long long old = 0ull;
+    if (halo_ok) asm volatile("atom.acq_rel.gpu.global.add.u64 %0, [%1], 1;" : "=l"(old) : "l"(&a.sync->light) : "memory");
+    if (halo_ok && old + 1ull == lgen * (unsigned long long)gridDim.x) {
+      st_release_gpu_u64(&a.sync->light_rel, lgen);
+    } else {
+      const long long w0 = clock64();
+      while (ld_acquire_gpu_u64(&a.sync->light_rel) < lgen)
+        if (clock64() - w0 > a.spin_limit) {
+          seen = false;
+          break;
+        }
+    }
     red[35] = seen ? 1.0 : 0.0;
   }
   bar_consumers<NCT>();
@@ -499,10 +507,13 @@ __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& 
       }
   };
 
-  // (row-partitioned) boundary blocks are dealt first: block index firstb + it * G < M.nbnd
+  // (row-partitioned) boundary blocks are dealt first: block index firstb + it * G < M.nbnd.  The CTA reports them
+  // BND_LAG blocks later: by then its peer stores have long been acknowledged and the system-scope fence finds nothing in
+  // flight (right behind the stores it costs an NVLink round trip with one thread of the CTA stalled)
+  constexpr int BND_LAG = 2;
   const int n_bnd_items = (a.peer.world > 1 && firstb < M.nbnd) ? (M.nbnd - firstb + G - 1) / G : 0;
   for (int it = 0; it < n_items; ++it, ++item) {
-    if (n_bnd_items > 0 && it == n_bnd_items) fused_boundary_done<NCW>(a, M, PH - 1, halo_epoch, sweep_no);
+    if (n_bnd_items > 0 && it == n_bnd_items + BND_LAG) fused_boundary_done<NCW>(a, M, PH - 1, halo_epoch, sweep_no);
     const int slot = (int)(item % STAGES);
     mbar_wait(sm.full + slot, (uint32_t)((item / STAGES) & 1));
     const int4 info = sm.hdr[slot];
@@ -561,7 +572,7 @@ __device__ __forceinline__ void fused_sweep(const FusedArgs& a, const FusedMat& 
     __syncwarp();
     if (lane == 0) mbar_arrive(sm.empty + slot);
   }
-  if (n_bnd_items > 0 && n_items == n_bnd_items) fused_boundary_done<NCW>(a, M, PH - 1, halo_epoch, sweep_no);
+  if (n_bnd_items > 0 && n_items <= n_bnd_items + BND_LAG) fused_boundary_done<NCW>(a, M, PH - 1, halo_epoch, sweep_no);
 }
 
 // MINB = resident CTAs per SM the register allocation is held to (4 -> 56 registers: the occupancy of the standalone
