@@ -24,6 +24,7 @@
 
 #include "pcg_kernels.cuh"
 #include "pcg_small.cuh"
+#include "pcg_small2.cuh"
 #include "pcg_fused.cuh"
 
 using namespace b200spai;
@@ -323,7 +324,173 @@ static int small_grid(const b200spai_pcg_s* s) {
   return (int)g;
 }
 
+// Second-generation small-system kernel (pcg_small2.cuh): L lanes per row, LL all-reduce.  B200SPAI_SMALL_KERNEL=1 keeps
+// the thread-per-row kernel (development switch for A/B measurements).
+static bool small_v1() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200SPAI_SMALL_KERNEL");
+    v = (e && atoi(e) == 1) ? 1 : 0;
+  }
+  return v == 1;
+}
+
+// Longest row of a matrix (cached in the handle): decides between the two small-system kernels.
+static __global__ void max_row_len_kernel(const int* __restrict__ rowptr, int n, int* __restrict__ out) {
+  int m = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) m = max(m, rowptr[i + 1] - rowptr[i]);
+  m = __reduce_max_sync(0xffffffffu, m);
+  if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, m);
+}
+static int csr_max_row_len(b200spai_csr_s* A, cudaStream_t st, int* out) {
+  if (A->max_row_len < 0) {
+    int* d = nullptr;
+    B2_TRY(dev_alloc(&d, 1));
+    B2_CUDA(cudaMemsetAsync(d, 0, sizeof(int), st));
+    if (A->n_rows > 0) max_row_len_kernel<<<std::min(64, (A->n_rows + 255) / 256), 256, 0, st>>>(A->rowptr, A->n_rows, d);
+    int h = 0;
+    B2_CUDA(cudaMemcpyAsync(&h, d, sizeof(int), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaStreamSynchronize(st));
+    dev_free(d);
+    A->max_row_len = h;
+    count_launches(1);
+  }
+  *out = A->max_row_len;
+  return 0;
+}
+
+// Plan of a small2 solve: lanes per row, grid, dynamic shared memory.  ok = false: the matrices do not fit into the shared
+// memory of a co-resident grid (e.g. the 49 152-row elasticity system: 67 MB) -- the thread-per-row kernel takes it.
+struct Small2Plan {
+  bool ok = false;
+  int lg = 0, grid = 0, smem = 0;
+};
+
+template <int LG>
+static int small2_occ(int smem, int* occ) {
+  // the opt-in limit is a per-function, process-wide setting: raised once to the maximum (concurrent solves on other
+  // threads launch with other sizes), the size of a launch is passed with the launch
+  static std::once_flag once;
+  static cudaError_t err = cudaSuccess;
+  std::call_once(once, [] { err = cudaFuncSetAttribute(pcg_small2_kernel<LG>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024); });
+  B2_CUDA(err);
+  B2_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, pcg_small2_kernel<LG>, S2_THREADS, smem));
+  return 0;
+}
+static int small2_occ_lg(int lg, int smem, int* occ) {
+  switch (lg) {
+    case 0: return small2_occ<0>(smem, occ);
+    case 1: return small2_occ<1>(smem, occ);
+    case 2: return small2_occ<2>(smem, occ);
+    case 3: return small2_occ<3>(smem, occ);
+    case 4: return small2_occ<4>(smem, occ);
+    default: return small2_occ<5>(smem, occ);
+  }
+}
+template <int LG>
+static int small2_launch(const Small2Args& a, const Small2Plan& pl, cudaStream_t st) {
+  B2_CUDA(cudaMemsetAsync(a.slots, 0, (size_t)2 * pl.grid * 4 * sizeof(unsigned long long), st));  // no tag of an earlier solve
+  void* args[] = {(void*)&a};
+  B2_CUDA(cudaLaunchCooperativeKernel((const void*)pcg_small2_kernel<LG>, dim3((unsigned)pl.grid), dim3(S2_THREADS), args,
+                                      (size_t)pl.smem, st));
+  return 0;
+}
+
+static int small2_plan(const b200spai_pcg_s* s, int precond, Small2Plan* pl) {
+  *pl = Small2Plan{};
+  const int n = s->n;
+  if (n < 1 || n > 131072) return 0;
+  const bool spai = precond >= B200SPAI_PRECOND_EXT_SPAI;
+  long long nnz_max = s->A->nnz, nnz_all = s->A->nnz;
+  if (spai) {
+    nnz_max = std::max(nnz_max, s->G->nnz);
+    nnz_all += s->G->nnz + s->GT->nnz;
+  }
+  const int nmat = spai ? 3 : 1;
+  // lanes per row: as many as one round of 8 passes needs for a typical row, as few as keep (about) one row per group
+  const double mean = (double)nnz_max / (double)n;
+  int lg = 0;
+  while (lg < 5 && 8.0 * (1 << lg) < mean) ++lg;
+  const long long lanes_cap = 2LL * sm_count() * S2_THREADS;
+  while (lg > 0 && (long long)n * (1 << lg) > lanes_cap) --lg;
+  const long long ng = S2_THREADS >> lg;
+  long long g = ((long long)n + ng - 1) / ng;
+  g = std::min<long long>(g, std::min<long long>(2LL * sm_count(), S2_MAX_CTAS));
+  // shared memory per CTA: its share of the matrices (12 bytes per entry + row pointers), 12 % head room for uneven rows
+  // (a CTA whose rows of a matrix do not fit reads that matrix from global memory)
+  const double share = ((double)nnz_all * 12.0 + (double)nmat * 4.0 * (double)(n + g)) / (double)g;
+  const long long want = (long long)(share * 1.12) + 48LL * nmat + 1024;
+  const int per_sm = 227 * 1024 - 2048;
+  const long long cap = (g > sm_count()) ? per_sm / 2 - 1024 : per_sm;
+  if (want > cap) return 0;
+  int smem = (int)((want + 127) & ~127LL);
+  int occ = 0;
+  B2_TRY(small2_occ_lg(lg, smem, &occ));
+  if ((long long)occ * sm_count() < g) return 0;
+  pl->ok = true;
+  pl->lg = lg;
+  pl->grid = (int)g;
+  pl->smem = smem;
+  return 0;
+}
+
+static int solve_small2(b200spai_pcg_s* s, int precond, const double* b, double* x, const Small2Plan& pl, cudaStream_t st) {
+  Small2Args a{};
+  a.A = s->A->view();
+  if (precond >= B200SPAI_PRECOND_EXT_SPAI) {
+    a.G = s->G->view();
+    a.GT = s->GT->view();
+  }
+  a.b = b;
+  a.x = x;
+  a.r0 = s->r;
+  a.r1 = s->bw;
+  a.p0 = s->p;
+  a.p1 = s->xw;
+  a.z = s->z;
+  a.q = s->q;
+  a.t = s->t;
+  a.d = (precond == B200SPAI_PRECOND_DIAGONAL || precond == B200SPAI_PRECOND_EXT_SPAI_SCALED) ? s->d : nullptr;
+  a.eps = s->eps;
+  a.precond = precond;
+  a.sc = s->sc;
+  a.slots = reinterpret_cast<unsigned long long*>(s->partials);
+  a.hist = s->hist;
+  a.smem_bytes = pl.smem;
+  static_assert(2 * S2_MAX_CTAS * 4 <= MAX_PARTIALS, "two generations of LL slots must fit the partials buffer");
+  int khz = 1965000, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
+  a.spin_limit = (long long)(20.0 * 1e3 * (double)khz);
+  switch (pl.lg) {
+    case 0: B2_TRY(small2_launch<0>(a, pl, st)); break;
+    case 1: B2_TRY(small2_launch<1>(a, pl, st)); break;
+    case 2: B2_TRY(small2_launch<2>(a, pl, st)); break;
+    case 3: B2_TRY(small2_launch<3>(a, pl, st)); break;
+    case 4: B2_TRY(small2_launch<4>(a, pl, st)); break;
+    default: B2_TRY(small2_launch<5>(a, pl, st)); break;
+  }
+  s->launches += 1;
+  count_launches(1);
+  return 0;
+}
+
 static int solve_small(b200spai_pcg_s* s, int precond, const double* b, double* x, int grid, cudaStream_t st) {
+  if (!small_v1()) {
+    // Measured (profiles/r02_shapes_small_kernels.txt): the lanes-per-row kernel wins where rows are long or of very
+    // different length (synthetic SPD: -25 % per iteration); on mesh matrices (15 +- 2 entries per row) the
+    // thread-per-row kernel is as fast (heat: 19.8 vs 21.6 us per iteration) and leaves the shared memory to other solves
+    static const int force = [] { const char* e = getenv("B200SPAI_SMALL_KERNEL"); return (e && atoi(e) == 2) ? 1 : 0; }();
+    b200spai_csr_s* W = (precond >= B200SPAI_PRECOND_EXT_SPAI && s->G->nnz > s->A->nnz) ? s->G : s->A;
+    int longest = 0;
+    B2_TRY(csr_max_row_len(W, st, &longest));
+    const double mean = (double)W->nnz / (double)std::max(1, s->n);
+    if (force || mean > 16.0 || (double)longest >= 2.5 * mean) {
+      Small2Plan pl;
+      B2_TRY(small2_plan(s, precond, &pl));
+      if (pl.ok) return solve_small2(s, precond, b, x, pl, st);
+    }
+  }
   SmallArgs a{};
   a.A = s->A->view();
   if (precond >= B200SPAI_PRECOND_EXT_SPAI) {

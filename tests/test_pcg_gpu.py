@@ -36,6 +36,22 @@ def history_within_envelope(h, ref, shift=1, slack=0.10):
     return bad
 
 
+def _reference_count_band(A, b, M, ref_it, rtol=1e-6):
+    """(min, max) iteration count of the reference recurrence (scipy cg restated, scripts/cg_order_sensitivity.cg) over
+    four summation orders of its dot products, together with the fixture's own count."""
+    import os
+    import sys
+
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts"))
+    from cg_order_sensitivity import cg
+
+    dots = (lambda u, v: float(u @ v), lambda u, v: float(u[::-1] @ v[::-1]),
+            lambda u, v: float(np.dot(u.astype(np.longdouble), v.astype(np.longdouble))),
+            lambda u, v: float(np.sum([float(x @ y) for x, y in zip(np.array_split(u, 8), np.array_split(v, 8))])))
+    counts = [ref_it] + [cg(A, b, M, dot, rtol=rtol)[0] for dot in dots]
+    return min(counts), max(counts)
+
+
 def _dev():
     from learningsparsepreconditioner4gpu_b200 import device
 
@@ -167,9 +183,14 @@ def test_pcg_matches_reference_iterations(name, mode):
         x, res, hist = solver.solve(torch.from_numpy(b).cuda(), kind, rtol=1e-6, history=True)
         assert res.reserved == mode                  # the driver that really ran
         ref_it = int(g[key])
-        assert abs(res.iterations - ref_it) <= 1, (name, kind, res.iterations, ref_it)
+        M = opcg.make_preconditioner(kind, A, G, eps)
+        # +-1 iteration of the reference's count -- where "the reference's count" is the band its OWN recurrence spans
+        # when nothing but the summation order of its dot products changes (elast_b3: 132 with numpy's dot, 133 reversed,
+        # 134 in 8 chunks; heat_b1: 211-213; the other fixtures do not move), measured here on the CPU
+        band = _reference_count_band(A, b, M, ref_it)
+        assert band[0] - 1 <= res.iterations <= band[1] + 1, (name, kind, res.iterations, ref_it, band)
         assert res.breakdown == 0
-        _, its, ohist = opcg.pcg_restated(A, b, opcg.make_preconditioner(kind, A, G, eps), rtol=1e-6)
+        _, its, ohist = opcg.pcg_restated(A, b, M, rtol=1e-6)
         h = hist.cpu().numpy()
         k = min(len(h), len(ohist))
         early = min(k, 6)
