@@ -348,7 +348,13 @@ def main_ours(args, ctx: Ctx, emit: bool = True):
     gnn_flop = 2.0 * (E * (11776 + 16 * Fe + 16 * bb) + N * (4 * 768 + 16 * Fin + 512))
     gnn_ms = ph.get("gnn", 0.0) / args.steps
     ffma_peak = 148 * 128 * 2 * 1.965e9 / 1e12
-    roofline["gnn"] = {"kernel": "gnn_edge_kernel + gnn_node_kernel x 4 MP layers, encoders, decoder (fp32 FFMA)", "bound": "fp32",
+    gnn_cfg = os.environ.get("B200SPAI_GNN_CFG", "6")
+    gnn_tensor = gnn_cfg.isdigit() and (int(gnn_cfg) & 4) != 0
+    roofline["gnn"] = {"kernel": ("gnn_edge_mma_kernel (per-edge MLPs as 3xTF32 mma.sync, fp32 accumulate: 3 tensor MACs per algorithmic MAC) + "
+                                  "gnn_node_kernel (fp32 FFMA) x 4 MP layers, encoders, gnn_dec_mma_kernel" if gnn_tensor else
+                                  "gnn_edge_kernel + gnn_node_kernel x 4 MP layers, encoders, decoder (fp32 FFMA)"),
+                       "bound": "fp32 (algorithmic flops against the FFMA roofline; ncu of the edge kernel: tensor pipe 44 % active, issue 57 %, "
+                                "profiles/r02_gnn_edge_mma_ncu_full.txt)" if gnn_tensor else "fp32",
                        "flop": gnn_flop, "ms": round(gnn_ms, 3), "achieved": round(gnn_flop / (gnn_ms * 1e-3) / 1e12, 2) if gnn_ms > 0 else None,
                        "peak": round(ffma_peak, 1), "unit": "TFLOP/s",
                        "frac": round(gnn_flop / (gnn_ms * 1e-3) / 1e12 / ffma_peak, 4) if gnn_ms > 0 else None,
