@@ -160,23 +160,39 @@ class _WorkspaceBase(nn.Module):
 
     # ---- device-resident additions ---------------------------------------------------------------------------
     @torch.no_grad()
-    def inference_step_device(self, sample) -> DeviceCSR:
-        """G as a DeviceCSR without leaving HBM (GNN forward + device assembly)."""
+    def inference_step_device(self, sample, pattern: str = "full") -> DeviceCSR:
+        """G as a DeviceCSR without leaving HBM (GNN forward + device assembly).
+
+        ``pattern="full"`` is the reference's contract on this path: one block per stored entry of A (workspace.py:92-94).
+        ``pattern="tril"`` keeps the blocks with col <= row -- ``ToLowerTriangular`` (basic_layers.py:278-294) applied
+        to the GNN output before assembly -- so G is (block) lower triangular and M = G G^T + eps I stays SPD."""
         boo_entry = self(sample.x, sample.edge_index, sample.edge_attr)
+        edge_index = sample.edge_index
+        if pattern == "tril":
+            from .nn.basic_layers import ToLowerTriangular
+
+            boo_entry, edge_index = ToLowerTriangular()(boo_entry, edge_index)
+            boo_entry, edge_index = boo_entry.contiguous(), edge_index.contiguous()
+        elif pattern != "full":
+            raise ValueError(f"pattern must be 'full' or 'tril', not {pattern!r}")
         n = sample.x.shape[0] * self.block_size
-        return to_csr_device(sample.edge_index, boo_entry, n, sample.mask)
+        return to_csr_device(edge_index, boo_entry, n, sample.mask)
 
     @torch.no_grad()
     def solve(self, sample, rhs: Optional[torch.Tensor] = None, rtol: float = 1e-6, max_iter: int = 0,
-              preconditioner: str = "ext_spai", history: bool = False, topology: Optional[FixedTopology] = None):
+              preconditioner: str = "ext_spai", history: bool = False, topology: Optional[FixedTopology] = None,
+              pattern: str = "full"):
         """GNN -> G -> PCG on the device.  ``rhs`` defaults to the reference's rhs="mask" convention
         (b = A @ mask, infer.py:297-299).  Returns (x, PcgResult, history, A, G).  ``topology``: a ``FixedTopology`` cache
-        shared by the samples of a fixed-topology dataset (A, G and the solver then belong to the cache)."""
+        shared by the samples of a fixed-topology dataset (A, G and the solver then belong to the cache).  ``pattern``:
+        "full" (the reference's contract) or "tril" (see ``inference_step_device``)."""
         if topology is not None:
+            if pattern != "full":
+                raise ValueError("the fixed-topology cache keeps the reference's full pattern of G")
             return self._solve_fixed(sample, topology, rhs, rtol, max_iter, preconditioner, history)
         n = sample.x.shape[0] * self.block_size
         A = to_csr_device(sample.edge_index, sample.matrix_values, n, sample.mask)
-        G = self.inference_step_device(sample)
+        G = self.inference_step_device(sample, pattern)
         if rhs is None:
             rhs = A.matvec(sample.mask.reshape(-1).to(torch.float64))
         solver = DevicePCG(A)

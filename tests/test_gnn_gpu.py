@@ -258,3 +258,35 @@ def test_validate_harness_matches_reference_counts():
         v.get_cg_iter_time(A, gt, method="ic")
     with pytest.raises(ValueError):
         v.get_pcg_iter_time(A, gt, G, 1e-3, device="cpu")
+
+
+@pytest.mark.parametrize("name", ["poisson_b1", "elast_b3"])
+def test_tril_pattern_switch(name):
+    """pattern="tril" = ToLowerTriangular (basic_layers.py:278-294) on the GNN output before assembly: G is the (block)
+    lower triangle of the full-pattern G, value for value, and the solve behaves like scipy's with that factor."""
+    import scipy.sparse as sp
+
+    from oracle import pcg as opcg
+
+    g = load_golden(name)
+    ws, s = _workspace(g), _sample(g)
+    b = int(g["block_size"])
+    x_full, res_full, _, A, G_full = ws.solve(s, rtol=1e-6)
+    x_tril, res_tril, _, _, G_tril = ws.solve(s, rtol=1e-6, pattern="tril")
+    Gf, Gt = G_full.to_scipy(), G_tril.to_scipy()
+    n = Gf.shape[0]
+    # block-lower mask: scalar entry (i, j) survives iff its block column <= its block row
+    coo = Gf.tocoo()
+    keep = (coo.col // b) <= (coo.row // b)
+    want = sp.csr_matrix((coo.data[keep], (coo.row[keep], coo.col[keep])), shape=(n, n))
+    want.sort_indices()
+    assert np.array_equal(Gt.indptr, want.indptr) and np.array_equal(Gt.indices, want.indices)
+    assert np.array_equal(Gt.data, want.data)
+    assert res_tril.converged == 1 and res_tril.breakdown == 0
+    As = A.to_scipy()
+    gt = g["mask"].reshape(-1).astype(np.float64)
+    it_ref = opcg.pcg_scipy(As, gt, want, ws.epsilon, rtol=1e-6)
+    print(f"[tril {name}] iterations {res_tril.iterations} (scipy on the same factor {it_ref}; full pattern {res_full.iterations})")
+    assert abs(res_tril.iterations - it_ref) <= 1 + it_ref // 100
+    with pytest.raises(ValueError):
+        ws.solve(s, pattern="upper")
