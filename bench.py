@@ -746,7 +746,22 @@ def main_batch_small(args):
         del A, G
     torch.cuda.synchronize()
 
+    collated = None
+    if args.collated:
+        # the batch as ONE block-diagonal system: one GNN forward / assembly / G^T for all systems, then every block solved
+        # by its own CTA group inside one launch per wave (batch.CollatedBatchSolver -> b200spai_pcg_solve_batch)
+        from learningsparsepreconditioner4gpu_b200.batch import CollatedBatchSolver
+
+        collated = CollatedBatchSolver(solver.workspaces[0])
+
     def one_pass():
+        if collated is not None:
+            results = collated.solve(samples, rtol=args.rtol)
+            its = [int(r.iterations) for _, r in results]
+            # same arithmetic per system; the partial sums of its dot products are grouped by another CTA count
+            assert all(r.converged == 1 for _, r in results), its
+            assert all(abs(a - b) <= 1 + b // 50 for a, b in zip(its, ref_iters)), (its, ref_iters)
+            return sum(its)
         results = solver.solve(samples, rtol=args.rtol)
         its = [int(r.iterations) for _, r in results]
         assert all(r.converged == 1 for _, r in results) and its == ref_iters, (its, ref_iters)
@@ -778,8 +793,11 @@ def main_batch_small(args):
             "warmup": max(args.warmup, 1), "ms_per_step": round(ms / args.steps, 3), "ms_per_system": round(ms / args.steps / per_rank, 3),
             "higher_is_better": True, "scaling": "weak", "dtype": "f64 (PCG) / f32 (GNN)", "data": "synthetic",
             "config": {"workload": f"{per_rank} Poisson systems per GPU, N in {{4096, 8000, 15625, 32768}}, Dirichlet patch, "
-                                   f"random-init GNN, rhs = A*mask, rtol {args.rtol:g}; {K} system(s) in flight per GPU "
-                                   f"(host threads x CUDA streams)"},
+                                   f"random-init GNN, rhs = A*mask, rtol {args.rtol:g}; " +
+                                   ("the batch collated into one block-diagonal system (one GNN forward / assembly per batch, "
+                                    "one PCG launch per wave of systems, a CTA group per system)" if args.collated else
+                                    f"{K} system(s) in flight per GPU (host threads x CUDA streams)")},
+            "collated": bool(args.collated),
             "mean_iterations": round(its / (per_rank * args.steps), 1),
             "gpu_launches": int(_lib.total_launches() - launches0)}), flush=True)
     if dist is not None:
@@ -909,6 +927,10 @@ def main():
                          "batch_small: a batch of small systems per GPU (BASELINE config C2); shapes: C1 / C3 / C4 at their sizes")
     ap.add_argument("--batch", type=int, default=64, help="batch_small: systems per step over all ranks")
     ap.add_argument("--streams", type=int, default=4, help="batch_small: systems in flight per GPU (host threads x CUDA streams)")
+    ap.add_argument("--no-collated", dest="collated", action="store_false",
+                    help="batch_small: host threads x CUDA streams, one system per workspace.solve (default: the batch collated into "
+                         "one block-diagonal system, one PCG launch per wave of systems)")
+    ap.set_defaults(collated=True)
     args = ap.parse_args()
     if args.impl == "reference":
         main_reference(args)

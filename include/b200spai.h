@@ -163,6 +163,16 @@ int b200spai_pcg_fused_profile(b200spai_pcg_t s, double* phase_ms5, int32_t* ite
  * receiving ||r_k|| (k = 0..iterations).  max_iter <= 0 means n (validate.py:100-101). */
 int b200spai_pcg_solve_dev(b200spai_pcg_t s, int precond, const double* b_dev, double* x_dev, double rtol,
                            int32_t max_iter, double* resid_hist_dev, void* stream, b200spai_pcg_result* result);
+/* Many independent small systems at once.  The solver is bound to the BLOCK-DIAGONAL matrix of a batch (the reference
+ * collates samples into one graph with offsets and splits them again by `ptr` before it solves each one on its own,
+ * neural_cg/workspace.py:137-143); block i = rows [row_ptr_host[i], row_ptr_host[i+1]) is one system.  Every system gets
+ * its own CTA group inside ONE kernel launch per wave (a device array of system descriptors; a wave = systems whose
+ * matrices stay L2-resident together), its own scalars, stopping rule (max_iter <= 0: its own row count) and entry of
+ * `results` -- the arithmetic of b200spai_pcg_solve_dev on that block.  resid_hist_dev: NULL or n_sys * hist_stride
+ * doubles (system i writes ||r_k|| at [i * hist_stride + k], hist_stride >= max_iter + 1). */
+int b200spai_pcg_solve_batch(b200spai_pcg_t s, int precond, int32_t n_sys, const int32_t* row_ptr_host, const double* b_dev,
+                             double* x_dev, double rtol, int32_t max_iter, double* resid_hist_dev, int64_t hist_stride,
+                             void* stream, b200spai_pcg_result* results);
 /* Same with host vectors: copies b in, x (and the history, if not NULL) out inside the call. */
 int b200spai_pcg_solve_host(b200spai_pcg_t s, int precond, const double* b_host, double* x_host, double rtol,
                             int32_t max_iter, double* resid_hist_host, void* stream, b200spai_pcg_result* result);

@@ -79,6 +79,8 @@ SIGNATURES = {
     "b200spai_dist_pcg_solve": [c_vp, C.c_int, c_vp, c_vp, c_f64, c_i32, c_vp, c_vp, C.POINTER(PcgResult)],
     "b200spai_dist_pcg_profile_iterations": [c_vp, C.c_int, c_vp, c_vp, c_i32, C.POINTER(C.c_float), c_vp],
     "b200spai_dist_destroy": [c_vp],
+    "b200spai_pcg_solve_batch": [c_vp, C.c_int, c_i32, C.POINTER(c_i32), c_vp, c_vp, c_f64, c_i32, c_vp, c_i64, c_vp,
+                                 C.POINTER(PcgResult)],
 }
 
 _lib = None

@@ -57,6 +57,46 @@ class BatchSolver:
             self.pool = None
 
 
+class CollatedBatchSolver:
+    """The whole batch as ONE block-diagonal system, the way the reference's DataLoader collates it (``data.collate``:
+    node / edge tensors concatenated, ``edge_index`` with cumulative node offsets, ``ptr``): one graph preprocessing, one
+    GNN forward (10 launches for all systems), one assembly of A and G, one G^T -- and then every block solved as an
+    independent system by its own CTA group inside one launch per wave (``DevicePCG.solve_batch`` ->
+    ``b200spai_pcg_solve_batch``), each with its own scalars, stopping rule and iteration count, as
+    ``log_converge_batch`` (workspace.py:137-143) does one by one.  No host thread per system, ~20 kernel launches per
+    batch instead of ~17 per system."""
+
+    def __init__(self, workspace):
+        _lib.require_cuda()
+        self.ws = workspace
+
+    @torch.no_grad()
+    def solve(self, samples: Sequence, rtol: float = 1e-6, max_iter: int = 0, preconditioner: str = "ext_spai",
+              history: bool = False):
+        """[(x, PcgResult)] in the order of ``samples`` (device-resident ``Data`` objects, b = A @ mask); with
+        ``history`` the tuples carry a third entry, the residual history of that system."""
+        from .device import DevicePCG
+        from .neural_cg.data import collate
+        from .neural_cg.utils.validate import to_csr_device
+
+        batch = collate(samples)
+        bsz = self.ws.block_size
+        n = batch.x.shape[0] * bsz
+        A = to_csr_device(batch.edge_index, batch.matrix_values, n, batch.mask)
+        G = self.ws.inference_step_device(batch)
+        rhs = A.matvec(batch.mask.reshape(-1).to(torch.float64))
+        solver = DevicePCG(A)
+        solver.set_spai(G, self.ws.epsilon)
+        ptr = (batch.ptr.detach().cpu().numpy().astype("int64") * bsz)
+        x, results, hists = solver.solve_batch(ptr, rhs, preconditioner, rtol=rtol, max_iter=max_iter, history=history)
+        out = []
+        for i in range(len(samples)):
+            xi = x[int(ptr[i]): int(ptr[i + 1])]
+            out.append((xi, results[i], hists[i]) if history else (xi, results[i]))
+        self.last = (A, G, solver)     # keeps the handles alive until the caller has consumed x
+        return out
+
+
 def solve_batch(make_workspace: Callable[[], object], samples: Sequence, streams: int = 4, **kw):
     """One-shot convenience around ``BatchSolver``."""
     bs = BatchSolver(make_workspace, streams)

@@ -749,6 +749,179 @@ int b200spai_pcg_solve_dev(b200spai_pcg_t s, int precond, const double* b, doubl
   return solve_impl(s, precond, b, x, rtol, max_iter, hist, as_stream(stream), result);
 }
 
+// Many independent small systems in waves of ONE launch each (pcg_small2.cuh, S2Sys descriptors): the solver is bound to
+// the block-diagonal batch matrix (a PyG-style batch: the reference collates samples this way and splits them by `ptr`
+// before solving, workspace.py:137-143); block s = rows [ptr[s], ptr[s+1]) is solved by its own CTA group with its own
+// scalars, stopping rule and iteration count -- the arithmetic of a stand-alone solve of that block.
+int b200spai_pcg_solve_batch(b200spai_pcg_t s, int precond, int32_t n_sys, const int32_t* row_ptr_host, const double* b,
+                             double* x, double rtol, int32_t max_iter, double* hist, int64_t hist_stride, void* stream,
+                             b200spai_pcg_result* results) {
+  B2_ARG(s && row_ptr_host && b && x && results && n_sys >= 1, "pcg_solve_batch: bad argument");
+  B2_ARG(precond >= 0 && precond <= 3, "pcg_solve_batch: unknown preconditioner");
+  B2_ARG(row_ptr_host[0] == 0 && row_ptr_host[n_sys] == s->n, "pcg_solve_batch: row_ptr must run from 0 to the number of rows");
+  B2_ARG(!hist || hist_stride > 0, "pcg_solve_batch: a history buffer needs its per-system stride");
+  if (precond >= B200SPAI_PRECOND_EXT_SPAI) B2_ARG(s->G && s->GT, "pcg_solve_batch: ext_spai needs b200spai_pcg_set_spai first");
+  cudaStream_t st = as_stream(stream);
+  if (precond == B200SPAI_PRECOND_DIAGONAL || precond == B200SPAI_PRECOND_EXT_SPAI_SCALED) B2_TRY(ensure_diag(s, st));
+  const bool spai = precond >= B200SPAI_PRECOND_EXT_SPAI;
+  long long nnz_max = s->A->nnz, nnz_all = s->A->nnz;
+  if (spai) {
+    nnz_max = std::max(nnz_max, s->G->nnz);
+    nnz_all += s->G->nnz + s->GT->nnz;
+  }
+  const double mean = (double)nnz_max / (double)std::max(1, s->n);
+  int lg = 0;
+  while (lg < 5 && 8.0 * (1 << lg) < mean) ++lg;
+  int occ = 0;
+  B2_TRY(small2_occ_lg(lg, 0, &occ));
+  const int cap = std::min<int>(sm_count() * std::min(occ, 2), S2_MAX_CTAS);
+  B2_ARG(cap >= 1, "pcg_solve_batch: the kernel does not fit this device");
+  // waves: systems whose matrices stay L2-resident together (they are re-read every iteration), at least 2 CTAs each
+  const double bytes_per_row = 12.0 * (double)nnz_all / (double)std::max(1, s->n) + 64.0;
+  const double wave_bytes = 88e6;
+  std::vector<PcgScalars> h_sc((size_t)n_sys);
+  std::vector<S2Sys> h_sys((size_t)n_sys);
+  PcgScalars* d_sc = nullptr;
+  S2Sys* d_sys = nullptr;
+  B2_TRY(dev_alloc(&d_sc, (size_t)n_sys));
+  int rc = dev_alloc(&d_sys, (size_t)n_sys);
+  if (rc) {
+    dev_free(d_sc);
+    return rc;
+  }
+  for (int i = 0; i < n_sys; ++i) {
+    const int rows = row_ptr_host[i + 1] - row_ptr_host[i];
+    if (rows < 0) {
+      dev_free(d_sc);
+      dev_free(d_sys);
+      set_error("pcg_solve_batch: row_ptr must be non-decreasing");
+      return B200SPAI_ERR_ARG;
+    }
+    PcgScalars init{};
+    init.rtol = rtol;
+    init.max_iter = max_iter > 0 ? max_iter : std::max(rows, 1);
+    h_sc[(size_t)i] = init;
+  }
+  auto fail = [&](int code) {
+    dev_free(d_sc);
+    dev_free(d_sys);
+    return code;
+  };
+  if (cudaMemcpyAsync(d_sc, h_sc.data(), sizeof(PcgScalars) * (size_t)n_sys, cudaMemcpyHostToDevice, st) != cudaSuccess)
+    return fail(B200SPAI_ERR_CUDA);
+  int khz = 1965000, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
+  B2_CUDA(cudaEventRecord(s->ev0, st));
+  int first = 0, waves = 0;
+  while (first < n_sys) {
+    int last = first;
+    double bytes = 0.0;
+    while (last < n_sys && (last - first) < cap / 2 + (cap == 1) &&
+           (last == first || bytes + bytes_per_row * (row_ptr_host[last + 1] - row_ptr_host[last]) <= wave_bytes)) {
+      bytes += bytes_per_row * (row_ptr_host[last + 1] - row_ptr_host[last]);
+      ++last;
+    }
+    const int cnt = last - first;
+    const long long rows_wave = std::max(1, row_ptr_host[last] - row_ptr_host[first]);
+    // CTAs in proportion to the rows, at least one each, never more than one row group per CTA would use
+    const long long ng = S2_THREADS >> lg;
+    int used = 0;
+    for (int i = first; i < last; ++i) {
+      const int rows = row_ptr_host[i + 1] - row_ptr_host[i];
+      long long c = (long long)((double)cap * (double)rows / (double)rows_wave);
+      c = std::max<long long>(1, std::min<long long>(c, (rows + ng - 1) / ng));
+      h_sys[(size_t)i] = S2Sys{row_ptr_host[i], rows, 0, (int)c};
+      used += (int)c;
+    }
+    while (used > cap) {  // rounding: take CTAs back from the largest groups
+      int big = first;
+      for (int i = first; i < last; ++i)
+        if (h_sys[(size_t)i].ncta > h_sys[(size_t)big].ncta) big = i;
+      if (h_sys[(size_t)big].ncta <= 1) break;
+      h_sys[(size_t)big].ncta -= 1;
+      used -= 1;
+    }
+    if (used > cap) return fail((set_error("pcg_solve_batch: more systems in a wave than co-resident CTAs"), B200SPAI_ERR_ARG));
+    int c0 = 0;
+    for (int i = first; i < last; ++i) {
+      h_sys[(size_t)i].cta0 = c0;
+      c0 += h_sys[(size_t)i].ncta;
+    }
+    if (cudaMemcpyAsync(d_sys + first, h_sys.data() + first, sizeof(S2Sys) * (size_t)cnt, cudaMemcpyHostToDevice, st) != cudaSuccess)
+      return fail(B200SPAI_ERR_CUDA);
+    Small2Args a{};
+    a.A = s->A->view();
+    if (spai) {
+      a.G = s->G->view();
+      a.GT = s->GT->view();
+    }
+    a.b = b;
+    a.x = x;
+    a.r0 = s->r;
+    a.r1 = s->bw;
+    a.p0 = s->p;
+    a.p1 = s->xw;
+    a.z = s->z;
+    a.q = s->q;
+    a.t = s->t;
+    a.d = (precond == B200SPAI_PRECOND_DIAGONAL || precond == B200SPAI_PRECOND_EXT_SPAI_SCALED) ? s->d : nullptr;
+    a.eps = s->eps;
+    a.precond = precond;
+    a.sc = d_sc + first;
+    a.slots = reinterpret_cast<unsigned long long*>(s->partials);
+    a.hist = hist ? hist + (long long)first * hist_stride : nullptr;
+    a.hist_stride = hist_stride;
+    a.smem_bytes = 0;  // the matrices of a wave (tens of MB) live in L2, not in shared memory
+    a.sys = d_sys + first;
+    a.n_sys = cnt;
+    a.spin_limit = (long long)(20.0 * 1e3 * (double)khz);
+    Small2Plan pl;
+    pl.ok = true;
+    pl.lg = lg;
+    pl.grid = used;
+    pl.smem = 0;
+    int lrc = 0;
+    switch (lg) {
+      case 0: lrc = small2_launch<0>(a, pl, st); break;
+      case 1: lrc = small2_launch<1>(a, pl, st); break;
+      case 2: lrc = small2_launch<2>(a, pl, st); break;
+      case 3: lrc = small2_launch<3>(a, pl, st); break;
+      case 4: lrc = small2_launch<4>(a, pl, st); break;
+      default: lrc = small2_launch<5>(a, pl, st); break;
+    }
+    if (lrc) return fail(lrc);
+    s->launches += 1;
+    count_launches(1);
+    first = last;
+    ++waves;
+  }
+  B2_CUDA(cudaEventRecord(s->ev1, st));
+  if (cudaMemcpyAsync(h_sc.data(), d_sc, sizeof(PcgScalars) * (size_t)n_sys, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+    return fail(B200SPAI_ERR_CUDA);
+  if (cudaStreamSynchronize(st) != cudaSuccess) {
+    set_error(std::string("pcg_solve_batch: ") + cudaGetErrorString(cudaGetLastError()));
+    return fail(B200SPAI_ERR_CUDA);
+  }
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, s->ev0, s->ev1);
+  for (int i = 0; i < n_sys; ++i) {
+    const PcgScalars& o = h_sc[(size_t)i];
+    b200spai_pcg_result& r = results[i];
+    r.iterations = o.iter;
+    r.converged = o.converged;
+    r.breakdown = o.breakdown;
+    r.reserved = 3;
+    r.b_norm = o.bnorm;
+    r.final_residual = sqrt(o.rr);
+    r.setup_ms = s->setup_ms;
+    r.solve_ms = ms;  // the whole batch (the systems of a wave run concurrently)
+  }
+  dev_free(d_sc);
+  dev_free(d_sys);
+  return 0;
+}
+
 int b200spai_pcg_solve_host(b200spai_pcg_t s, int precond, const double* b_host, double* x_host, double rtol,
                             int32_t max_iter, double* hist_host, void* stream, b200spai_pcg_result* result) {
   B2_ARG(s && b_host && x_host && result, "pcg_solve_host: NULL argument");

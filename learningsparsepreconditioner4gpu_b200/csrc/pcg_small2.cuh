@@ -42,6 +42,16 @@ struct Small2Args {
   double* hist;
   long long spin_limit;
   int smem_bytes;  // dynamic shared memory of the launch
+  // Batched launch (b200spai_pcg_solve_batch): A, G, G^T are block diagonal, block s = rows [row0, row0 + nrows) = one
+  // independent system, solved by the CTA group [cta0, cta0 + ncta) with its own scalars sc[s], all-reduce slots and
+  // (optionally) history hist + s * hist_stride.  nullptr: one system, the whole grid.
+  const struct S2Sys* sys;
+  int n_sys;
+  long long hist_stride;
+};
+
+struct S2Sys {
+  int row0, nrows, cta0, ncta;
 };
 
 constexpr int S2_THREADS = 256;
@@ -61,10 +71,16 @@ __device__ __forceinline__ bool s2_ll_load(const unsigned long long* slot, unsig
 
 // (v0, v1) summed over the grid; identical bits in every thread of every CTA.  Doubles as the grid barrier: everything
 // the CTAs wrote before the call is visible (through L2: __ldcg / ld.relaxed) after it.  false: a CTA never arrived.
-__device__ __forceinline__ bool s2_allreduce(const Small2Args& a, unsigned long long& gen, double v0, double v1, double* red,
+struct S2Group {  // the CTA group that solves one system
+  unsigned long long* slots;  // [2][G][4]
+  unsigned G, bid;
+  long long spin_limit;
+};
+
+__device__ __forceinline__ bool s2_allreduce(const S2Group& a, unsigned long long& gen, double v0, double v1, double* red,
                                              double& t0, double& t1) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const unsigned G = gridDim.x;
+  const unsigned G = a.G;
   gen += 1;
   unsigned long long* slot = a.slots + (size_t)(gen & 1ull) * G * 4;
   const unsigned long long g32 = gen & 0xffffffffull;
@@ -81,7 +97,7 @@ __device__ __forceinline__ bool s2_allreduce(const Small2Args& a, unsigned long 
     const double* w = red + 8 * tid;
     const double c = ((w[0] + w[1]) + (w[2] + w[3])) + ((w[4] + w[5]) + (w[6] + w[7]));
     asm volatile("fence.acq_rel.gpu;" ::: "memory");
-    s2_ll_store(slot + 4 * blockIdx.x + 2 * tid, c, g32);
+    s2_ll_store(slot + 4 * a.bid + 2 * tid, c, g32);
   }
   // ---- every CTA fetches every CTA's partials (the poll is the barrier) ----
   double s0 = 0.0, s1 = 0.0;
@@ -194,12 +210,34 @@ __global__ void __launch_bounds__(S2_THREADS, 2) pcg_small2_kernel(const Small2A
   __shared__ double red[32];
   extern __shared__ __align__(16) unsigned char s2_smem[];
   const int tid = threadIdx.x;
-  const int n = a.A.n_rows;
-  const int G = gridDim.x;
+  // which system, which CTA of its group
+  int row0 = 0, n = a.A.n_rows, cta0 = 0, G = gridDim.x, sys_id = 0;
+  if (a.sys != nullptr) {
+    __shared__ int s_sys;
+    if (tid == 0) {
+      int lo = 0, hi = a.n_sys - 1;  // groups are consecutive CTA ranges
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (a.sys[mid].cta0 <= (int)blockIdx.x) lo = mid;
+        else hi = mid - 1;
+      }
+      s_sys = lo;
+    }
+    __syncthreads();
+    sys_id = s_sys;
+    const S2Sys d = a.sys[sys_id];
+    row0 = d.row0;
+    n = d.nrows;
+    cta0 = d.cta0;
+    G = d.ncta;
+  }
+  const int bid = (int)blockIdx.x - cta0;
   const int chunk = (n + G - 1) / G;
-  const int r_lo = min(n, (int)blockIdx.x * chunk), r_hi = min(n, r_lo + chunk);
+  const int r_lo = row0 + min(n, bid * chunk), r_hi = row0 + min(n, bid * chunk + chunk);
   const int grp = tid >> LG, j = tid & (L - 1);
   const bool spai = a.precond >= B200SPAI_PRECOND_EXT_SPAI;
+  const S2Group grpc{a.slots + (size_t)cta0 * 8, (unsigned)G, (unsigned)bid, a.spin_limit};
+  double* const hist = a.hist ? a.hist + (long long)sys_id * a.hist_stride : nullptr;
   // the CTA's rows of G^T, G and A live in shared memory for the whole solve (when they fit)
   unsigned char* sp = s2_smem;
   int room = a.smem_bytes;
@@ -207,8 +245,8 @@ __global__ void __launch_bounds__(S2_THREADS, 2) pcg_small2_kernel(const Small2A
   const S2View vG = spai ? s2_stage(a.G, r_lo, r_hi, sp, room) : S2View{nullptr, nullptr, nullptr};
   const S2View vA = s2_stage(a.A, r_lo, r_hi, sp, room);
   const bool scaled = a.precond == B200SPAI_PRECOND_EXT_SPAI_SCALED;
-  const bool lead = (blockIdx.x == 0 && tid == 0);
-  PcgScalars* sc = a.sc;
+  const bool lead = (bid == 0 && tid == 0);
+  PcgScalars* sc = a.sc + sys_id;
   const double rtol = sc->rtol;
   const int max_iter = sc->max_iter;
   unsigned long long gen = 0;
@@ -222,7 +260,7 @@ __global__ void __launch_bounds__(S2_THREADS, 2) pcg_small2_kernel(const Small2A
     a.x[i] = 0.0;
     acc += v * v;
   }
-  bool ok = s2_allreduce(a, gen, acc, 0.0, red, t0, t1);
+  bool ok = s2_allreduce(grpc, gen, acc, 0.0, red, t0, t1);
   const double bb = t0;
   const double bnorm = sqrt(bb);
   const double atol = fmax(0.0, rtol * bnorm);
@@ -232,7 +270,7 @@ __global__ void __launch_bounds__(S2_THREADS, 2) pcg_small2_kernel(const Small2A
     done = 1;
     breakdown = 3;
   } else {
-    if (lead) a.hist[0] = bnorm;
+    if (lead && hist) hist[0] = bnorm;
     if (bnorm == 0.0) {
       done = 1;
       converged = 1;
@@ -300,7 +338,7 @@ __global__ void __launch_bounds__(S2_THREADS, 2) pcg_small2_kernel(const Small2A
       r = rn;
       rn = tmp;
     }
-    ok = s2_allreduce(a, gen, rr_part, rz_part, red, t0, t1);  // first SPAI iteration: only t has to be complete
+    ok = s2_allreduce(grpc, gen, rr_part, rz_part, red, t0, t1);  // first SPAI iteration: only t has to be complete
     if (!ok) {
       breakdown = 3;
       break;
@@ -314,7 +352,7 @@ __global__ void __launch_bounds__(S2_THREADS, 2) pcg_small2_kernel(const Small2A
       rho_prev = rho;
       iter += 1;
       const double nrm = sqrt(t0);
-      if (lead) a.hist[iter] = nrm;
+      if (lead && hist) hist[iter] = nrm;
       if (nrm < atol) {
         converged = 1;
         break;
@@ -344,7 +382,7 @@ __global__ void __launch_bounds__(S2_THREADS, 2) pcg_small2_kernel(const Small2A
           part += rv * zv;
         }
       }
-      ok = s2_allreduce(a, gen, part, 0.0, red, t0, t1);
+      ok = s2_allreduce(grpc, gen, part, 0.0, red, t0, t1);
       if (!ok) {
         breakdown = 3;
         break;
@@ -378,7 +416,7 @@ __global__ void __launch_bounds__(S2_THREADS, 2) pcg_small2_kernel(const Small2A
         }
       }
     }
-    ok = s2_allreduce(a, gen, part, 0.0, red, t0, t1);
+    ok = s2_allreduce(grpc, gen, part, 0.0, red, t0, t1);
     if (!ok) {
       breakdown = 3;
       break;

@@ -206,6 +206,32 @@ class DevicePCG:
             hist = hist[: res.iterations + 1]
         return x, res, hist
 
+    def solve_batch(self, row_ptr, b: torch.Tensor, precond: str = "ext_spai", rtol: float = 1e-6, max_iter: int = 0,
+                    x: Optional[torch.Tensor] = None, history: bool = False):
+        """Many independent systems in one launch per wave (b200spai_pcg_solve_batch): A (and G) are the block-diagonal
+        matrices of a batch, block i = rows [row_ptr[i], row_ptr[i+1]).  Returns (x, [PcgResult per system], histories or
+        None) -- histories[i] is system i's ||r_k||, k = 0..iterations."""
+        assert b.is_cuda and b.dtype == torch.float64
+        ptr = np.ascontiguousarray(np.asarray(row_ptr, dtype=np.int64))
+        n_sys = int(ptr.size) - 1
+        n = self.A.shape[0]
+        assert n_sys >= 1 and ptr[0] == 0 and ptr[-1] == n
+        ptr32 = ptr.astype(np.int32)
+        x = x if x is not None else torch.empty(n, dtype=torch.float64, device=b.device)
+        hist, stride = None, 0
+        if history:
+            stride = (int(max_iter) if max_iter > 0 else int(np.diff(ptr).max())) + 1
+            hist = torch.zeros(n_sys * stride, dtype=torch.float64, device=b.device)
+        res = (_lib.PcgResult * n_sys)()
+        _lib.check(self._lib.b200spai_pcg_solve_batch(self._h, PRECOND[precond], n_sys, ptr32.ctypes.data_as(C.POINTER(C.c_int32)),
+                                                      _ptr(b.contiguous()), _ptr(x), float(rtol), int(max_iter), _ptr(hist),
+                                                      int(stride), _stream(), res), "pcg_solve_batch")
+        results = list(res)
+        hists = None
+        if hist is not None:
+            hists = [hist[i * stride: i * stride + results[i].iterations + 1] for i in range(n_sys)]
+        return x, results, hists
+
     def solve_host(self, b: np.ndarray, x: np.ndarray, precond: str = "ext_spai", rtol: float = 1e-6, max_iter: int = 0,
                    history: Optional[np.ndarray] = None):
         """Host-buffer solve (copies inside the call); x is updated in place."""

@@ -307,3 +307,51 @@ def test_concurrent_solves_on_threads_and_streams_reproduce_sequential_results()
     solver.close()
     one = solve_batch(make, samples[:5], streams=1, rtol=1e-8)               # K = 1 runs in the calling thread
     assert [int(r.iterations) for _, r in one] == [r[0] for r in ref[:5]]
+
+
+def test_batched_solve_matches_standalone_solves():
+    """b200spai_pcg_solve_batch: the blocks of a block-diagonal batch matrix solved by CTA groups of one launch carry the
+    arithmetic of stand-alone solves -- same iteration counts (+-1: the dot-product partials are grouped by another CTA
+    count), same solutions, per-system stopping rule, histories and max_iter; every preconditioner kind."""
+    import scipy.sparse as sp
+
+    d = _dev()
+    names = ["poisson_b1", "heat_b1", "elast_b3", "synthetic_mild_b1", "poisson_zeros_b1"]
+    As, Gs, bs, eps = [], [], [], None
+    for name in names:
+        g = load_golden(name)
+        A, G = golden_csr(g, "A"), golden_csr(g, "G")
+        As.append(A)
+        Gs.append(G)
+        bs.append(A @ g["mask"].reshape(-1).astype(np.float64))
+        eps = float(g["epsilon"])
+    Ab, Gb = sp.block_diag(As, format="csr"), sp.block_diag(Gs, format="csr")
+    Ab.sort_indices()
+    Gb.sort_indices()
+    ptr = np.cumsum([0] + [A.shape[0] for A in As])
+    b = torch.from_numpy(np.concatenate(bs)).cuda()
+    solver = d.DevicePCG(d.DeviceCSR.from_scipy(Ab))
+    solver.set_spai(d.DeviceCSR.from_scipy(Gb), eps)
+    for kind in ("ext_spai", "none", "diagonal", "ext_spai_scaled"):
+        x, results, hists = solver.solve_batch(ptr, b, kind, rtol=1e-6, history=True)
+        for i, name in enumerate(names):
+            one = d.DevicePCG(d.DeviceCSR.from_scipy(As[i]), mode=3)
+            one.set_spai(d.DeviceCSR.from_scipy(Gs[i]), eps)
+            xi, ri, hi = one.solve(torch.from_numpy(bs[i]).cuda(), kind, rtol=1e-6, history=True)
+            r = results[i]
+            assert r.converged == ri.converged and r.breakdown == 0, (kind, name)
+            assert abs(r.iterations - ri.iterations) <= 1, (kind, name, r.iterations, ri.iterations)
+            h, h1 = hists[i].cpu().numpy(), hi.cpu().numpy()
+            assert len(h) == r.iterations + 1 and np.allclose(h[:6], h1[:6], rtol=1e-12), (kind, name)
+            xs = x[ptr[i]:ptr[i + 1]].cpu().numpy()
+            if r.converged:
+                assert np.allclose(xs, xi.cpu().numpy(), rtol=0, atol=2e-5 * np.abs(xi.cpu().numpy()).max()), (kind, name)
+    # per-system max_iter cut-off
+    x, results, _ = solver.solve_batch(ptr, b, "ext_spai", rtol=1e-14, max_iter=7)
+    assert all(r.iterations == 7 and r.converged == 0 for r in results)
+    # a zero right-hand side in one block does not disturb the others
+    b0 = b.clone()
+    b0[ptr[1]:ptr[2]] = 0.0
+    x, results, _ = solver.solve_batch(ptr, b0, "ext_spai", rtol=1e-6)
+    assert results[1].iterations == 0 and results[1].converged == 1 and float(x[ptr[1]:ptr[2]].abs().max()) == 0.0
+    assert results[0].converged == 1 and results[0].iterations > 0
