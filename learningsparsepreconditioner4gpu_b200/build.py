@@ -29,6 +29,8 @@ NVCC_FLAGS = [
 ]
 if os.environ.get("B200SPAI_PROBE"):  # development: cycle counters inside the streaming SpMV
     NVCC_FLAGS.append("-DB200SPAI_PROBE")
+if os.environ.get("B200SPAI_S2_NO_PREFETCH"):  # development: A/B of the row-pointer prefetch in pcg_small2.cuh
+    NVCC_FLAGS.append("-DB200SPAI_S2_NO_PREFETCH")
 if os.environ.get("B200SPAI_PART_W"):  # development: row-block partition weight
     NVCC_FLAGS.append("-DB200SPAI_PART_W=" + os.environ["B200SPAI_PART_W"])
 LIB = os.environ.get("B200SPAI_LIB_OUT", LIB)

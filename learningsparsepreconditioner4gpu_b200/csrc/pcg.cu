@@ -410,19 +410,28 @@ static int small2_plan(const b200spai_pcg_s* s, int precond, Small2Plan* pl) {
   // lanes per row: as many as one round of 8 passes needs for a typical row, as few as keep (about) one row per group
   const double mean = (double)nnz_max / (double)n;
   int lg = 0;
-  while (lg < 5 && 8.0 * (1 << lg) < mean) ++lg;
+  while (lg < 5 && 8.0 * (1 << lg) < mean) ++lg;  // (this kernel takes single systems with long / irregular rows: measured, one lane per row loses there)
   const long long lanes_cap = 2LL * sm_count() * S2_THREADS;
   while (lg > 0 && (long long)n * (1 << lg) > lanes_cap) --lg;
   const long long ng = S2_THREADS >> lg;
-  long long g = ((long long)n + ng - 1) / ng;
-  g = std::min<long long>(g, std::min<long long>(2LL * sm_count(), S2_MAX_CTAS));
+  const long long g_max = std::min<long long>(2LL * sm_count(), S2_MAX_CTAS);
+  const long long g_rows = std::min<long long>(((long long)n + ng - 1) / ng, g_max);
   // shared memory per CTA: its share of the matrices (12 bytes per entry + row pointers), 12 % head room for uneven rows
-  // (a CTA whose rows of a matrix do not fit reads that matrix from global memory)
-  const double share = ((double)nnz_all * 12.0 + (double)nmat * 4.0 * (double)(n + g)) / (double)g;
-  const long long want = (long long)(share * 1.12) + 48LL * nmat + 1024;
+  // (a CTA whose rows of a matrix do not fit reads that matrix from global memory).  More CTAs than the rows need are
+  // taken when that is what makes the share fit (some row groups then idle).
   const int per_sm = 227 * 1024 - 2048;
-  const long long cap = (g > sm_count()) ? per_sm / 2 - 1024 : per_sm;
-  if (want > cap) return 0;
+  long long g = 0, want = 0;
+  for (long long cand : {g_rows, g_max, std::max<long long>(g_rows, (long long)sm_count())}) {
+    const double share = ((double)nnz_all * 12.0 + (double)nmat * 4.0 * (double)(n + cand)) / (double)cand;
+    const long long w = (long long)(share * 1.12) + 48LL * nmat + 1024;
+    const long long cap = (cand > sm_count()) ? per_sm / 2 - 1024 : per_sm;
+    if (w <= cap) {
+      g = cand;
+      want = w;
+      break;
+    }
+  }
+  if (g == 0) return 0;
   int smem = (int)((want + 127) & ~127LL);
   int occ = 0;
   B2_TRY(small2_occ_lg(lg, smem, &occ));
@@ -771,7 +780,7 @@ int b200spai_pcg_solve_batch(b200spai_pcg_t s, int precond, int32_t n_sys, const
   }
   const double mean = (double)nnz_max / (double)std::max(1, s->n);
   int lg = 0;
-  while (lg < 5 && 8.0 * (1 << lg) < mean) ++lg;
+  while (lg < 5 && (lg == 0 ? 16.0 : 8.0 * (1 << lg)) < mean) ++lg;  // entries per round: 16 with one lane per row, else 8 L
   int occ = 0;
   B2_TRY(small2_occ_lg(lg, 0, &occ));
   const int cap = std::min<int>(sm_count() * std::min(occ, 2), S2_MAX_CTAS);

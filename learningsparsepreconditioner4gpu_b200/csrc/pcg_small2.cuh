@@ -162,20 +162,30 @@ __device__ __forceinline__ S2View s2_stage(const CsrView& M, int r_lo, int r_hi,
 
 // One row of M times a vector whose entry c is produced by `entry(c)`, walked by the L = 1 << LG lanes of a group (lane j
 // of the group takes entries j, j + L, ...); called by all 32 lanes of a warp together (`valid` = this group has a row).
-// Eight passes of loads are in flight at once (one round covers rows of up to 8 L entries); the sum is formed in entry
-// order (rounded product, rounded add).  Every lane of the group returns the row sum.
-template <int LG, class Entry>
-__device__ __forceinline__ double s2_row(const S2View& M, int row, bool valid, int j, Entry entry) {
-  constexpr int L = 1 << LG;
-  int s = 0, e = 0;
+// Eight passes of loads (16 with one lane per row) are in flight at once; the sum is formed in entry order (rounded
+// product, rounded add).  Every lane of the group returns the row sum.
+// (s, e) of a group's row, requested one row ahead of its use (the row loop prefetches the next pair while it walks the
+// current row: with the matrices in global memory that takes one of three dependent L2 round trips off every pass)
+struct S2Range {
+  int s, e;
+};
+__device__ __forceinline__ S2Range s2_range(const S2View& M, int row, bool valid) {
+  S2Range r{0, 0};
   if (valid) {
-    s = M.rowptr[row];
-    e = M.rowptr[row + 1];
+    r.s = M.rowptr[row];
+    r.e = M.rowptr[row + 1];
   }
+  return r;
+}
+
+template <int LG, class Entry>
+__device__ __forceinline__ double s2_row(const S2View& M, const S2Range rg, int j, Entry entry) {
+  constexpr int L = 1 << LG;
+  const int s = rg.s, e = rg.e;
   const int len = e - s;
   const int npass = __reduce_max_sync(0xffffffffu, (len + L - 1) >> LG);
   double sum = 0.0;
-  constexpr int U = 8;
+  constexpr int U = (LG == 0) ? 16 : 8;  // thread per row: a 15-entry mesh row in one round
   for (int ps = 0; ps < npass; ps += U) {
     int c[U];
     double v[U], pr[U];
@@ -286,10 +296,17 @@ __global__ void __launch_bounds__(S2_THREADS, 2) pcg_small2_kernel(const Small2A
     // ---- P1 -------------------------------------------------------------------------------------------
     double rr_part = 0.0, rz_part = 0.0;
     if (spai) {
+      S2Range nxt = s2_range(vGT, r_lo + grp, r_lo + grp < r_hi);
       for (int base = r_lo; base < r_hi; base += NG) {
         const int i = base + grp;
         const bool valid = i < r_hi;
         const bool mine = valid && j == 0;
+#ifdef B200SPAI_S2_NO_PREFETCH
+        const S2Range cur = s2_range(vGT, i, valid);
+#else
+        const S2Range cur = nxt;
+        nxt = s2_range(vGT, i + NG, i + NG < r_hi);
+#endif
         // the row owner's operands are requested before the row walk: their L2 round trip overlaps the gathers
         double xi = 0.0, pi = 0.0, ri = 0.0, qi = 0.0, di = 1.0;
         if (mine) {
@@ -305,9 +322,9 @@ __global__ void __launch_bounds__(S2_THREADS, 2) pcg_small2_kernel(const Small2A
         if (pending) {
           const double* rq = a.q;
           const double al = alpha;
-          tv = s2_row<LG>(vGT, i, valid, j, [r, rq, al](int c) { return __dsub_rn(__ldcg(r + c), __dmul_rn(al, __ldcg(rq + c))); });
+          tv = s2_row<LG>(vGT, cur, j, [r, rq, al](int c) { return __dsub_rn(__ldcg(r + c), __dmul_rn(al, __ldcg(rq + c))); });
         } else {
-          tv = s2_row<LG>(vGT, i, valid, j, [r](int c) { return __ldcg(r + c); });
+          tv = s2_row<LG>(vGT, cur, j, [r](int c) { return __ldcg(r + c); });
         }
         if (mine) {
           if (pending) {
@@ -364,16 +381,23 @@ __global__ void __launch_bounds__(S2_THREADS, 2) pcg_small2_kernel(const Small2A
     if (spai) {
       double part = 0.0;
       const double* tt = a.t;
+      S2Range nxt = s2_range(vG, r_lo + grp, r_lo + grp < r_hi);
       for (int base = r_lo; base < r_hi; base += NG) {
         const int i = base + grp;
         const bool valid = i < r_hi;
         const bool mine = valid && j == 0;
+#ifdef B200SPAI_S2_NO_PREFETCH
+        const S2Range cur = s2_range(vG, i, valid);
+#else
+        const S2Range cur = nxt;
+        nxt = s2_range(vG, i + NG, i + NG < r_hi);
+#endif
         double rv = 0.0, di = 1.0;
         if (mine) {
           rv = __ldcg(r + i);
           if (scaled) di = __ldg(a.d + i);
         }
-        const double gv = s2_row<LG>(vG, i, valid, j, [tt](int c) { return __ldcg(tt + c); });
+        const double gv = s2_row<LG>(vG, cur, j, [tt](int c) { return __ldcg(tt + c); });
         if (mine) {
           double e = a.eps * rv;
           if (scaled) e = e / di;
@@ -396,18 +420,25 @@ __global__ void __launch_bounds__(S2_THREADS, 2) pcg_small2_kernel(const Small2A
     {
       const double* zz = a.z;
       const double be = beta;
+      S2Range nxt = s2_range(vA, r_lo + grp, r_lo + grp < r_hi);
       for (int base = r_lo; base < r_hi; base += NG) {
         const int i = base + grp;
         const bool valid = i < r_hi;
         const bool mine = valid && j == 0;
+#ifdef B200SPAI_S2_NO_PREFETCH
+        const S2Range cur = s2_range(vA, i, valid);
+#else
+        const S2Range cur = nxt;
+        nxt = s2_range(vA, i + NG, i + NG < r_hi);
+#endif
         double zi = 0.0, pi = 0.0;
         if (mine) {
           zi = __ldcg(zz + i);
           if (!first) pi = __ldcg(p + i);
         }
         double qv;
-        if (first) qv = s2_row<LG>(vA, i, valid, j, [zz](int c) { return __ldcg(zz + c); });
-        else qv = s2_row<LG>(vA, i, valid, j, [zz, p, be](int c) { return __dadd_rn(__dmul_rn(__ldcg(p + c), be), __ldcg(zz + c)); });
+        if (first) qv = s2_row<LG>(vA, cur, j, [zz](int c) { return __ldcg(zz + c); });
+        else qv = s2_row<LG>(vA, cur, j, [zz, p, be](int c) { return __dadd_rn(__dmul_rn(__ldcg(p + c), be), __ldcg(zz + c)); });
         if (mine) {
           const double pv = first ? zi : __dadd_rn(__dmul_rn(pi, beta), zi);
           pn[i] = pv;
