@@ -816,7 +816,14 @@ def main_shapes(args):
     from learningsparsepreconditioner4gpu_b200.device import DevicePCG
 
     _lib.require_cuda()
-    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:      # N GPUs: one independent system of the shape per GPU (weak scaling, no data-path collective)
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     peak, peak_src = peaks()
     names = args.shapes.split(",") if args.shapes else list(systems.SHAPES)
     for name in names:
@@ -828,6 +835,9 @@ def main_shapes(args):
             x, res, solver, A, G, rhs = run_step(ws, sample, args.rtol)
             del solver, A, G, rhs
         torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
         launches0 = _lib.total_launches()
         timers = []
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -842,6 +852,10 @@ def main_shapes(args):
         ev1.record()
         torch.cuda.synchronize()
         dev_ms = ev0.elapsed_time(ev1)
+        if dist is not None:     # max over ranks
+            tmax = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            dev_ms = float(tmax.item())
         launches = _lib.total_launches() - launches0
         ph = phases_ms(timers)
         mode_ran = int(res.reserved)
@@ -862,7 +876,7 @@ def main_shapes(args):
         # ---- the oracle beside it: a REAL run of the same system on the host cores ----
         cpu = None
         parity = None
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and rank == 0 and world == 1:
             from oracle import assemble as oasm, gnn as ognn, pcg as opcg
 
             sd = {k: v.detach().cpu() for k, v in ws.state_dict().items()}
@@ -886,8 +900,8 @@ def main_shapes(args):
                       "pattern_A_bit_exact": bool(np.array_equal(As.indptr, Ao.indptr) and np.array_equal(As.indices, Ao.indices)
                                                   and np.array_equal(As.data, Ao.data))}
         line = {
-            "metric": METRIC, "mode": "shapes", "shape": name, "value": round(args.steps / (dev_ms * 1e-3), 3), "unit": UNIT,
-            "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(dev_ms / args.steps, 3),
+            "metric": METRIC, "mode": "shapes", "shape": name, "value": round(world * args.steps / (dev_ms * 1e-3), 3), "unit": UNIT,
+            "n_gpus": world, "parallelism": f"{world} independent system(s) of this shape, one per GPU", "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(dev_ms / args.steps, 3),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64 (PCG) / f32 (GNN)", "data": "synthetic",
             "config": {"workload": f"{name}: N = {N} nodes, block {b}, n = {n} rows, E = {E} stored blocks, nnz(A) = {nnzA}, "
                                    f"nnz(G) = {nnzG}; random-init GNN (seed 42), eps 3e-3, rhs = A*mask, rtol {args.rtol:g}",
@@ -904,9 +918,13 @@ def main_shapes(args):
                          "per_kernel": per_kernel},
             "gpu_launches": int(launches), "cpu_baseline": cpu, "parity": parity,
         }
-        print(json.dumps(line), flush=True)
+        if rank == 0:
+            print(json.dumps(line), flush=True)
         del solver, A, G, rhs
         torch.cuda.empty_cache()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 def main():
