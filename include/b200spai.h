@@ -149,7 +149,9 @@ int b200spai_pcg_refresh(b200spai_pcg_t s, void* stream);
 /* mode: 0 = auto (3 for systems of <= 131072 rows, else 2; B200SPAI_PCG_MODE=1 forces 1, B200SPAI_PCG_MODE=4 makes
  * the auto choice for large SPAI solves 4 when it applies), 1 = stream-enqueued kernels with a device-side done flag
  * polled every few iterations, 2 = one CUDA graph with a device-driven WHILE node (no host involvement at all),
- * 3 = the whole solve in ONE cooperative kernel with 2-3 grid barriers per iteration (small systems, thread per row),
+ * 3 = the whole solve in ONE co-resident kernel with 2-3 grid-wide all-reduces per iteration (small systems; thread per
+ *     row, csrc/pcg_small.cuh, or -- for long / irregular rows that fit shared memory -- L lanes per row with the row sum
+ *     formed in entry order, csrc/pcg_small2.cuh; B200SPAI_SMALL_KERNEL=1|2 forces one),
  * 4 = the whole solve in ONE persistent kernel: three TMA-staged matrix sweeps and two vector phases per iteration
  * separated by grid barriers, the stream producer running ahead across sweeps (large systems with a SPAI
  * preconditioner whose A, G and G^T share one stream format; csrc/pcg_fused.cuh; the row-partitioned solver's default).

@@ -171,3 +171,7 @@ def test_batch_solver_needs_cuda():
         pytest.skip("needs a CPU-only box")
     with pytest.raises(_lib.B200SpaiError):
         BatchSolver(lambda: None, streams=2)
+    from learningsparsepreconditioner4gpu_b200.batch import CollatedBatchSolver
+
+    with pytest.raises(_lib.B200SpaiError):
+        CollatedBatchSolver(None)               # the collated (one launch per wave) path has no CPU fallback either
