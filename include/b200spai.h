@@ -228,6 +228,34 @@ int b200spai_graph_spmv_f32(b200spai_graph_t g, int32_t block_size, const float*
                             const float* mask_dev, int32_t transpose, float* y_dev, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Training through the fused kernels.  Stand in for what torch autograd records and replays
+ * when SimpleTrainingWorkspace.training_step (neural_cg/workspace.py:96-112,178-180) runs
+ * self(batch.x, batch.edge_index, batch.edge_attr) -> AATPE -> loss (neural_cg/loss.py:168-188) -> backward().
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct b200spai_gnn_tape_s* b200spai_gnn_tape_t; /* what one forward keeps for its backward */
+/* Activation store of ONE forward / backward pair on graph g: node features after the encoder and every MP layer,
+ * edge features after every MP layer, aggregated messages of every layer (everything inside the MLPs is recomputed
+ * by the backward), plus the backward's workspaces. */
+int b200spai_gnn_tape_create(b200spai_gnn_t m, b200spai_graph_t g, b200spai_gnn_tape_t* out);
+int b200spai_gnn_tape_destroy(b200spai_gnn_tape_t t);
+/* b200spai_gnn_forward that fills the tape: NodeEdgeProcessing.forward (neural_cg/nn/gnns.py:77-97) under autograd. */
+int b200spai_gnn_forward_train(b200spai_gnn_t m, b200spai_graph_t g, b200spai_gnn_tape_t t, const float* x_dev,
+                               const float* edge_attr_dev, float* g_out_dev, void* stream);
+/* grad_blob_dev[blob_len] = dL/d(weight blob) given grad_g_dev[E, b*b] = dL/dG (caller's edge order); same x / edge_attr
+ * as the forward.  The blob layout is that of b200spai_gnn_create (LayerNorm affines folded into the first Linear: the
+ * host mirror maps the result back to the state_dict parameters, neural_cg/nn/gnns.py).  Deterministic (no atomics). */
+int b200spai_gnn_backward(b200spai_gnn_t m, b200spai_graph_t g, b200spai_gnn_tape_t t, const float* x_dev,
+                          const float* edge_attr_dev, const float* grad_g_dev, float* grad_blob_dev, void* stream);
+/* Replace the weights of an engine from a DEVICE blob (after an optimiser step; no host round trip). */
+int b200spai_gnn_set_weights_dev(b200spai_gnn_t m, const float* blob_dev, int64_t blob_len, void* stream);
+/* Gradient of GraphSpmv (neural_cg/nn/basic_layers.py:112-142) w.r.t. its matrix values [E,b,b] (caller's edge order):
+ * transpose == 0: dA_e = gy[row_e] (x) x[col_e];  transpose != 0: dA_e = x[row_e] (x) gy[col_e]  (outer products);
+ * accumulate != 0 adds to grad_values_dev.  gy is the gradient of the operator's output AFTER the mask was applied to
+ * it (the caller multiplies by the mask).  The gradient w.r.t. x is b200spai_graph_spmv_f32 with the other transpose. */
+int b200spai_graph_outer_f32(b200spai_graph_t g, int32_t block_size, const float* gy_dev, const float* x_dev,
+                             int32_t transpose, int32_t accumulate, float* grad_values_dev, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Device memory pool.  The library caches the device blocks it releases (a solve step allocates the same
  * multi-GB blocks every time; cudaMalloc/cudaFree of those cost ~0.1 s per step).  Cached blocks are handed out
  * again in the order of the one stream a handle works on.  Limit: B200SPAI_POOL_MAX_GB (default 64).

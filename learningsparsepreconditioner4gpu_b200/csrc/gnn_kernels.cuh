@@ -26,12 +26,16 @@ __device__ __forceinline__ float gelu(float x) { return G ? gelu_as(x) : gelu_er
 
 // Packed fp32 FMA (Blackwell FFMA2): two independent fma.rn.f32 per instruction, same bits as two FFMA.
 __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+#ifdef B200SPAI_HOST_EMU  // host build of the backward kernels (tests/host_emu): the same two rounded FMAs
+  return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y));
+#else
   float2 d;
   asm("fma.rn.f32x2 %0, %1, %2, %3;"
       : "=l"(reinterpret_cast<unsigned long long&>(d))
       : "l"(reinterpret_cast<const unsigned long long&>(a)), "l"(reinterpret_cast<const unsigned long long&>(b)),
         "l"(reinterpret_cast<const unsigned long long&>(c)));
   return d;
+#endif
 }
 
 // y[j] = bias[j] + sum_k x[k] * W[k][j];  W [K][16] and bias [16] in shared memory (16-byte aligned).

@@ -75,6 +75,78 @@ def pack_state_dict(sd: Dict[str, torch.Tensor], num_layers: int, prefix: str = 
     return blob
 
 
+def blob_layout(num_layers: int, prefix: str = ""):
+    """(state_dict prefix, offset in the blob, padded input width) of every FeedForward in the weight blob."""
+    out = [(prefix + "node_enc.", 0, F), (prefix + "edge_enc.", MLP16, F)]
+    off = 2 * MLP16
+    for k in range(num_layers):
+        p = f"{prefix}mp_layers.{k}."
+        out += [(p + "msg_mlp.", off, 48), (p + "edge_mlp.", off + MLP48, 48), (p + "node_mlp.", off + 2 * MLP48, F)]
+        off += LAYER_FLOATS
+    out.append((prefix + "edge_dec.", off, 48))
+    return out
+
+
+def pack_state_dict_torch(sd: Dict[str, torch.Tensor], num_layers: int, prefix: str = "") -> torch.Tensor:
+    """``pack_state_dict`` with torch ops on the device the parameters live on (the blob after an optimiser step, no
+    host round trip: ``b200spai_gnn_set_weights_dev``).  Same folding of the LayerNorm affine, in float64."""
+    parts = []
+    for pre, _, k_pad in blob_layout(num_layers, prefix):
+        W1 = sd[pre + "lift.0.weight"].detach().double()
+        b1 = sd[pre + "lift.0.bias"].detach().double()
+        if pre + "pre_norm.weight" in sd:
+            g, c = sd[pre + "pre_norm.weight"].detach().double(), sd[pre + "pre_norm.bias"].detach().double()
+            b1 = b1 + W1 @ c
+            W1 = W1 * g[None, :]
+        W3 = sd[pre + "proj.0.weight"].detach().double()
+        W1t = W1.new_zeros((k_pad, F))
+        W1t[: W1.shape[1]] = W1.T
+        W3t = W1.new_zeros((F, F))
+        W3t[:, : W3.shape[0]] = W3.T
+        b3 = W1.new_zeros(F)
+        b3[: W3.shape[0]] = sd[pre + "proj.0.bias"].detach().double()
+        parts += [W1t.reshape(-1), b1, sd[pre + "body.0.0.weight"].detach().double().T.reshape(-1),
+                  sd[pre + "body.0.0.bias"].detach().double(), W3t.reshape(-1), b3]
+    return torch.cat(parts).to(torch.float32).contiguous()
+
+
+def unpack_grad_blob(gblob: torch.Tensor, sd: Dict[str, torch.Tensor], num_layers: int, prefix: str = "") -> Dict[str, torch.Tensor]:
+    """dL/d(weight blob) (``b200spai_gnn_backward``) -> dL/d(state_dict parameter), the inverse of ``pack_state_dict``:
+    transposes undone, padding dropped, and the LayerNorm affine (weight g, bias c) un-folded from the first Linear --
+    with W1'[k][j] = g[k] W1[j][k] and b1'[j] = b1[j] + sum_k c[k] W1[j][k]:
+        dW1[j][k] = g[k] dW1'[k][j] + db1'[j] c[k],   dg[k] = sum_j dW1'[k][j] W1[j][k],   dc[k] = sum_j db1'[j] W1[j][k]."""
+    out: Dict[str, torch.Tensor] = {}
+    for pre, off, k_pad in blob_layout(num_layers, prefix):
+        W1 = sd[pre + "lift.0.weight"].detach()
+        W3 = sd[pre + "proj.0.weight"].detach()
+        n_in, n_out = W1.shape[1], W3.shape[0]
+        o = off
+        dW1p = gblob[o:o + k_pad * F].view(k_pad, F)[:n_in]
+        o += k_pad * F
+        db1p = gblob[o:o + F]
+        o += F
+        dW2t = gblob[o:o + F * F].view(F, F)
+        o += F * F
+        db2 = gblob[o:o + F]
+        o += F
+        dW3t = gblob[o:o + F * F].view(F, F)
+        o += F * F
+        db3 = gblob[o:o + F]
+        if pre + "pre_norm.weight" in sd:
+            g, c = sd[pre + "pre_norm.weight"].detach(), sd[pre + "pre_norm.bias"].detach()
+            out[pre + "pre_norm.weight"] = (dW1p * W1.T).sum(dim=1)
+            out[pre + "pre_norm.bias"] = W1.T @ db1p
+            out[pre + "lift.0.weight"] = (dW1p * g[:, None]).T + db1p[:, None] * c[None, :]
+        else:
+            out[pre + "lift.0.weight"] = dW1p.T.clone()
+        out[pre + "lift.0.bias"] = db1p.clone()
+        out[pre + "body.0.0.weight"] = dW2t.T.clone()
+        out[pre + "body.0.0.bias"] = db2.clone()
+        out[pre + "proj.0.weight"] = dW3t[:, :n_out].T.clone()
+        out[pre + "proj.0.bias"] = db3[:n_out].clone()
+    return out
+
+
 def _check_mlp(cfg: dict, pre_norm: str, what: str):
     ok = (str(cfg.get("pre_norm", "none")).lower() in pre_norm and int(cfg["hidden_channels"]) == F
           and int(cfg["num_layers"]) == 2 and cfg.get("activation", "gelu") == "gelu"
