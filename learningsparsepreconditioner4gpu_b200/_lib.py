@@ -62,6 +62,12 @@ SIGNATURES = {
     "b200spai_gnn_node_features": [c_vp, c_i32, C.POINTER(c_vp)],
     "b200spai_gnn_launch_count": [c_vp, C.POINTER(c_i64)],
     "b200spai_graph_spmv_f32": [c_vp, c_i32, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp],
+    "b200spai_gnn_tape_create": [c_vp, c_vp, C.POINTER(c_vp)],
+    "b200spai_gnn_tape_destroy": [c_vp],
+    "b200spai_gnn_forward_train": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp],
+    "b200spai_gnn_backward": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp],
+    "b200spai_gnn_set_weights_dev": [c_vp, c_vp, c_i64, c_vp],
+    "b200spai_graph_outer_f32": [c_vp, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp],
     "b200spai_csr_stream_info": [c_vp, C.POINTER(c_i32), C.POINTER(c_i32), c_vp],
     "b200spai_pool_trim": [],
     "b200spai_pool_cached_bytes": [C.POINTER(c_i64)],

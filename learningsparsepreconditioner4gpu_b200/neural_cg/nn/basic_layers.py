@@ -106,14 +106,52 @@ def _graph_for(edge_index: torch.Tensor, num_nodes: int):
     return _graph_cache["g"][1]
 
 
+def _spmv_raw(graph, b: int, a: torch.Tensor, x: torch.Tensor, m: Optional[torch.Tensor], transpose: bool) -> torch.Tensor:
+    """b200spai_graph_spmv_f32 on contiguous fp32 device tensors: y[N,b] = m * (A x)  (A^T x when ``transpose``)."""
+    y = torch.empty((graph.num_nodes, b), dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().b200spai_graph_spmv_f32(graph._h, b, C.c_void_p(a.data_ptr()), C.c_void_p(x.data_ptr()),
+                                                   C.c_void_p(m.data_ptr() if m is not None else 0), int(transpose),
+                                                   C.c_void_p(y.data_ptr()),
+                                                   C.c_void_p(torch.cuda.current_stream().cuda_stream)), "graph_spmv_f32")
+    return y
+
+
+class _GraphSpmvFn(torch.autograd.Function):
+    """GraphSpmv under autograd (the reference differentiates PyG's propagate + bmm, basic_layers.py:130-142).  With
+    gy' = mask * gy:  dL/dx = the operator with the OTHER transpose flag applied to gy' (b200spai_graph_spmv_f32),
+    dL/dA_e = gy'[row_e] (x) x[col_e]  (transpose: x[row_e] (x) gy'[col_e])  (b200spai_graph_outer_f32)."""
+
+    @staticmethod
+    def forward(ctx, graph, b, transpose, x, a, m):
+        ctx.graph, ctx.b, ctx.transpose, ctx.has_mask = graph, b, transpose, m is not None
+        ctx.save_for_backward(x, a, m if m is not None else x.new_empty(0))
+        return _spmv_raw(graph, b, a, x, m, transpose)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, a, m = ctx.saved_tensors
+        gy = gy.detach().to(torch.float32).reshape(-1, ctx.b)
+        gy = (gy * m).contiguous() if ctx.has_mask else gy.contiguous()
+        gx = ga = None
+        if ctx.needs_input_grad[3]:
+            gx = _spmv_raw(ctx.graph, ctx.b, a, gy, None, not ctx.transpose)
+        if ctx.needs_input_grad[4]:
+            ga = torch.empty_like(a)
+            _lib.check(_lib.load().b200spai_graph_outer_f32(ctx.graph._h, ctx.b, C.c_void_p(gy.data_ptr()), C.c_void_p(x.data_ptr()),
+                                                            int(ctx.transpose), 0, C.c_void_p(ga.data_ptr()),
+                                                            C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+                       "graph_outer_f32")
+        return None, None, None, gx, ga, None
+
+
 class GraphSpmv(nn.Module):
-    """y_i = sum_j A_ij x_j on an edge list (``use_transpose``: y_j = sum_i A_ij^T x_i), then ``* mask``."""
+    """y_i = sum_j A_ij x_j on an edge list (``use_transpose``: y_j = sum_i A_ij^T x_i), then ``* mask``.
+    Differentiable w.r.t. X and A when either requires grad (training); plain kernel call otherwise."""
 
     def __init__(self, use_transpose: bool = False):
         super().__init__()
         self.transpose = use_transpose
 
-    @torch.no_grad()
     def forward(self, X: torch.Tensor, edge_index: torch.Tensor, A: torch.Tensor, mask: Optional[torch.Tensor] = None,
                 graph=None) -> torch.Tensor:
         _lib.require_cuda()
@@ -123,20 +161,19 @@ class GraphSpmv(nn.Module):
         b = 1 if A.dim() == 1 else A.shape[-1]
         assert X.numel() == N * b and A.numel() == edge_index.shape[1] * b * b
         graph = graph or _graph_for(edge_index, N)
-        x = X.detach().to(torch.float32).contiguous()
-        a = A.detach().to(torch.float32).contiguous()
+        x = X.to(torch.float32).reshape(N, b).contiguous()
+        a = A.to(torch.float32).contiguous()
         m = None if mask is None else mask.detach().to(torch.float32).expand(N, b).contiguous()
-        y = torch.empty((N, b), dtype=torch.float32, device=X.device)
-        lib = _lib.load()
-        _lib.check(lib.b200spai_graph_spmv_f32(graph._h, b, C.c_void_p(a.data_ptr()), C.c_void_p(x.data_ptr()),
-                                               C.c_void_p(m.data_ptr() if m is not None else 0), int(self.transpose),
-                                               C.c_void_p(y.data_ptr()),
-                                               C.c_void_p(torch.cuda.current_stream().cuda_stream)), "graph_spmv_f32")
+        if torch.is_grad_enabled() and (x.requires_grad or a.requires_grad):
+            y = _GraphSpmvFn.apply(graph, b, bool(self.transpose), x, a, m)
+        else:
+            y = _spmv_raw(graph, b, a.detach(), x.detach(), m, bool(self.transpose))
         return y.reshape(X.shape)
 
 
 class AATPE(nn.Module):
-    """y = eps x + G (G^T x)  (with ``diag``: eps diag x + G (diag (G^T x)))  -- basic_layers.py:235-261."""
+    """y = eps x + G (G^T x)  (with ``diag``: eps diag x + G (diag (G^T x)))  -- basic_layers.py:235-261.
+    Differentiable w.r.t. ``boo_values`` (through GraphSpmv) when they require grad."""
 
     def __init__(self, epsilon):
         super().__init__()
@@ -144,7 +181,6 @@ class AATPE(nn.Module):
         self.spmv_t = GraphSpmv(use_transpose=True)
         self.epsilon = epsilon
 
-    @torch.no_grad()
     def forward(self, x: torch.Tensor, edge_index, boo_values, mask: Union[torch.Tensor, None] = None,
                 diag: Optional[torch.Tensor] = None):
         graph = _graph_for(edge_index, x.shape[0])

@@ -193,6 +193,68 @@ class DeviceGraph:
             pass
 
 
+class GnnTape:
+    """What ONE training forward keeps for its backward (b200spai_gnn_tape_create): per-layer node features, edge
+    features and aggregated messages; everything inside the MLPs is recomputed by the backward kernels."""
+
+    def __init__(self, engine, graph: DeviceGraph):
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        _lib.check(self._lib.b200spai_gnn_tape_create(engine, graph._h, C.byref(self._h)), "gnn_tape_create")
+
+    def close(self):
+        if self._h:
+            self._lib.b200spai_gnn_tape_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class _GnnTrainFn(torch.autograd.Function):
+    """NodeEdgeProcessing.forward under autograd (the reference gets this from torch autograd through PyG ops,
+    gnns.py:77-97): forward = b200spai_gnn_forward_train (the inference kernels + a tape), backward =
+    b200spai_gnn_backward (dL/dG -> dL/d weight blob) + ``unpack_grad_blob``.  The inputs x / edge_attr get no gradient
+    (the reference never asks for one: they are data)."""
+
+    @staticmethod
+    def forward(ctx, module, graph, x, ea, names, *params):
+        lib = _lib.load()
+        engine = module._get_engine(device_pack=True)
+        tape = GnnTape(engine, graph)
+        E = graph.num_edges
+        edge_out = torch.empty((E, module.edge_out), dtype=torch.float32, device=x.device)
+        _lib.check(lib.b200spai_gnn_forward_train(engine, graph._h, tape._h, C.c_void_p(x.data_ptr()), C.c_void_p(ea.data_ptr()),
+                                                  C.c_void_p(edge_out.data_ptr()),
+                                                  C.c_void_p(torch.cuda.current_stream().cuda_stream)), "gnn_forward_train")
+        ctx.module, ctx.graph, ctx.tape, ctx.x, ctx.ea, ctx.names = module, graph, tape, x, ea, names
+        ctx.weights_version = module._weights_version()
+        ctx.save_for_backward(*params)
+        return edge_out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        module = ctx.module
+        if module._weights_version() != ctx.weights_version:
+            raise _lib.B200SpaiError("the GNN weights changed between forward and backward (the backward recomputes the "
+                                     "MLP internals from the weights: call backward() before optimizer.step())")
+        lib = _lib.load()
+        params = ctx.saved_tensors
+        gG = grad_out.detach().to(torch.float32).contiguous()
+        gblob = torch.empty(blob_length(module.num_mp_layers), dtype=torch.float32, device=gG.device)
+        _lib.check(lib.b200spai_gnn_backward(module._engine, ctx.graph._h, ctx.tape._h, C.c_void_p(ctx.x.data_ptr()),
+                                             C.c_void_p(ctx.ea.data_ptr()), C.c_void_p(gG.data_ptr()),
+                                             C.c_void_p(gblob.data_ptr()),
+                                             C.c_void_p(torch.cuda.current_stream().cuda_stream)), "gnn_backward")
+        ctx.tape.close()
+        grads = unpack_grad_blob(gblob, dict(zip(ctx.names, params)), module.num_mp_layers)
+        return (None, None, None, None, None) + tuple(
+            grads[n].to(p.dtype) if ctx.needs_input_grad[5 + i] else None for i, (n, p) in enumerate(zip(ctx.names, params)))
+
+
 class NodeEdgeProcessing(nn.Module):
     def __init__(
         self,
@@ -261,8 +323,17 @@ class NodeEdgeProcessing(nn.Module):
         self.__dict__["_plist"] = None
         return super()._apply(fn, *args, **kwargs)
 
-    def _get_engine(self):
+    def _get_engine(self, device_pack: bool = False):
         ver = self._weights_version()
+        if device_pack and self._engine is not None and ver != self._engine_version:
+            # training: the weights moved by an optimiser step -- repack on the device, no host round trip
+            blob = pack_state_dict_torch(self.state_dict(), self.num_mp_layers)
+            _lib.check(_lib.load().b200spai_gnn_set_weights_dev(self._engine, C.c_void_p(blob.data_ptr()), blob.numel(),
+                                                                C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+                       "gnn_set_weights_dev")
+            self._engine_version = ver
+            self._blob_keepalive = blob   # the copy is asynchronous on the current stream
+            return self._engine
         if self._engine is None or ver != self._engine_version:
             self.release_engine()
             lib = _lib.load()
@@ -298,9 +369,11 @@ class NodeEdgeProcessing(nn.Module):
         _lib.check(_lib.load().b200spai_gnn_launch_count(self._engine, C.byref(v)), "gnn_launch_count")
         return v.value
 
-    @torch.no_grad()
     def forward(self, node_attr: torch.Tensor, edge_index: torch.Tensor, edge_attr: torch.Tensor,
-                graph: Optional[DeviceGraph] = None):
+                graph: Optional[DeviceGraph] = None, autograd: bool = False):
+        """``autograd=False`` (default): inference, no graph is recorded whatever the grad mode.  ``autograd=True`` (the
+        workspaces' training / validation steps): the edge output carries a grad_fn whose backward runs the CUDA
+        backward kernels; the node output is returned detached (the workspaces use node_out_features=None)."""
         _lib.require_cuda()
         if not (node_attr.is_cuda and edge_index.is_cuda and edge_attr.is_cuda):
             raise _lib.B200SpaiError("NodeEdgeProcessing.forward needs CUDA tensors: there is no CPU path")
@@ -309,6 +382,16 @@ class NodeEdgeProcessing(nn.Module):
         graph = graph or self.graph_for(edge_index, N)
         x = node_attr.detach().to(torch.float32).contiguous()
         ea = edge_attr.detach().to(torch.float32).contiguous()
+        if autograd and torch.is_grad_enabled():
+            named = [(n, p) for n, p in self.named_parameters() if "node_msg_norm" not in n]
+            if any(p.requires_grad for _, p in named):
+                names = tuple(n for n, _ in named)
+                edge_out = _GnnTrainFn.apply(self, graph, x, ea, names, *[p for _, p in named])
+                return None, edge_out
+        return self._forward_inference(graph, x, ea, N, E)
+
+    @torch.no_grad()
+    def _forward_inference(self, graph, x, ea, N, E):
         edge_out = torch.empty((E, self.edge_out), dtype=torch.float32, device=x.device)
         node_out = torch.empty((N, F), dtype=torch.float32, device=x.device)
         lib = _lib.load()

@@ -23,6 +23,10 @@ class ScaledTrainingWorkspace(_WorkspaceBase):
     def _pcg(self, A, r, L, device, repeat):
         return get_pcg_scaled_iter_time(A, r, L, self.epsilon, device=device, repeat=repeat)
 
+    def _precondition_residual(self, batch, boo_entry):
+        assert hasattr(batch, "inv_diag"), "Relying on batch.inv_diag to maintain stability"   # scaled_workspace.py:98
+        return self.spai_preconditioner(batch.residual, batch.edge_index, boo_entry, mask=batch.mask, diag=batch.inv_diag)
+
     def _export_factor(self, L: csr_matrix, batch) -> csr_matrix:
         rsqrt_diag = to_numpy(batch.rsqrt_diag).flatten().astype(np.float64, copy=True)
         return csr_matrix(L @ diags(rsqrt_diag))

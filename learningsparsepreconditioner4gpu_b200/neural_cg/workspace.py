@@ -8,8 +8,11 @@ Differences, all forced by the environment or the scope:
   ``save_hyperparameters`` fills ``self.hparams``; checkpoints are plain ``state_dict``s with the reference's keys;
 * the GNN forward, CSR assembly and PCG run in libb200spai.so; convergence checks always solve on "cuda"
   (a "cpu" entry in ``check_devices`` is mapped to "cuda" with a warning) with the methods the library has;
-* training (``training_step``, losses, optimisers) is out of scope: the ``loss`` / ``optimizer`` /
-  ``scheduler`` configs are accepted and stored so that the reference's YAML splats in unchanged;
+* training: ``_shared_step`` / ``training_step`` / ``validation_step`` / ``test_step`` /
+  ``configure_optimizers`` (:96-112,178-193,213-226) run the GNN forward with a tape, ``AATPE`` and the loss
+  (``neural_cg/loss.py``) on the device; ``loss.backward()`` runs the CUDA backward kernels (``b200spai_gnn_backward``,
+  ``b200spai_graph_outer_f32``) behind torch autograd Functions.  ``neural_cg/trainer.py`` is the small stand-in for the
+  ``L.Trainer(...).fit`` loop of train.py:98-110;
 * additions: ``inference_step_device`` (G stays in HBM) and ``solve`` (GNN -> G -> PCG, end to end on the device).
 """
 from __future__ import annotations
@@ -24,8 +27,10 @@ from scipy.sparse import csr_matrix
 from torch import nn
 
 from ..device import DeviceCSR, DevicePCG
+from .loss import create_loss_item
 from .nn.basic_layers import AATPE
 from .nn.gnns import NodeEdgeProcessing
+from .utils.optim import create_optimizer, create_scheduler
 from .utils.validate import get_cg_iter_time, get_pcg_iter_time, to_csr_cpu, to_csr_device, to_numpy
 
 
@@ -81,6 +86,8 @@ class _WorkspaceBase(nn.Module):
         self.epsilon = epsilon
         self.test_max_iter = test_max_iter
         self.loss_name = _cfg_get(loss, "name")
+        self.loss_fn = create_loss_item(self.loss_name, batch_less=batch_less, block_size=block_size,
+                                        **dict(_cfg_get(loss, "params") or {})) if self.loss_name else None
         self.gnn = NodeEdgeProcessing(node_in_features=node_features, node_out_features=None,
                                       edge_in_features=edge_features, edge_out_features=block_size * block_size,
                                       **dict(gnn))
@@ -100,13 +107,55 @@ class _WorkspaceBase(nn.Module):
         for k, v in values.items():
             self.log(k, v)
 
+    # ---- training (workspace.py:96-112,178-193,213-226) ---------------------------------------------------------
+    def _precondition_residual(self, batch, boo_entry):
+        return self.spai_preconditioner(batch.residual, batch.edge_index, boo_entry, mask=batch.mask)
+
+    def _shared_step(self, batch, prefix: str, batch_idx: int):
+        assert hasattr(batch, "ptr"), "Relying on batch.ptr to compute batch size"
+        if self.loss_fn is None:
+            raise ValueError("the workspace was built without a loss config")
+        bsize = int(batch.ptr.shape[0]) - 1
+        boo_entry = self(batch.x, batch.edge_index, batch.edge_attr, autograd=True)
+        d = self._precondition_residual(batch, boo_entry)
+        total_loss = self.loss_fn(batch, d, boo_entry)
+        self.log_dict({f"{prefix}/Loss": total_loss.detach()}, batch_size=bsize, prog_bar=(prefix == "Train"))
+        # (the reference probes convergence here for Val / Test at batch 0 AND again in validation_step / test_step,
+        # workspace.py:107-108,184-185: the same numbers twice; _eval_step below runs the probe once)
+        self._log_norms(boo_entry.detach(), bsize, prefix)
+        return boo_entry, total_loss
+
     def training_step(self, batch, batch_idx: int):
-        raise NotImplementedError("training is outside the B200 solve path (SURVEY.md §8f rank 4); "
-                                  "train with the reference and load the state_dict here")
+        _, loss = self._shared_step(batch, "Train", batch_idx)
+        return loss
+
+    def _eval_step(self, batch, prefix: str, batch_idx: int, repeat: int, every_batch: bool):
+        """validation_step / test_step (workspace.py:182-193): loss + convergence probe.  Batches made for inference only
+        (no ``residual``: ``make_data(is_inference=True)``) have no loss; they get the probe and return G."""
+        if "residual" in batch and self.loss_fn is not None:
+            boo_entry, out = self._shared_step(batch, prefix, batch_idx)
+            boo_entry = boo_entry.detach()
+        else:
+            with torch.no_grad():
+                boo_entry = out = self(batch.x, batch.edge_index, batch.edge_attr)
+            self._log_norms(boo_entry, int(batch.ptr.shape[0]) - 1, prefix)
+        if every_batch or batch_idx == 0:
+            self.log_converge_batch(boo_entry, batch, prefix, repeat)
+        return out
+
+    def validation_step(self, batch, batch_idx: int):
+        return self._eval_step(batch, "Val", batch_idx, repeat=1, every_batch=False)
+
+    def configure_optimizers(self):
+        opt = create_optimizer(self.parameters(), _cfg_get(self.optimizer_cfg, "name"), _cfg_get(self.optimizer_cfg, "params"))
+        sched = create_scheduler(opt, _cfg_get(self.scheduler_cfg, "name"), _cfg_get(self.scheduler_cfg, "params"))
+        return {"optimizer": opt, "lr_scheduler": sched} if sched is not None else opt
 
     # ---- the model -----------------------------------------------------------------------------------------
-    def forward(self, node_attr, edge_index, edge_attr):
-        _, boo_entry = self.gnn(node_attr, edge_index, edge_attr)
+    def forward(self, node_attr, edge_index, edge_attr, autograd: bool = False):
+        """[nE, b, b].  ``autograd=True`` (the training / validation steps): the result carries the grad_fn of the CUDA
+        backward; every other caller gets the plain inference forward."""
+        _, boo_entry = self.gnn(node_attr, edge_index, edge_attr, autograd=autograd)
         return boo_entry.reshape(-1, self.block_size, self.block_size)  # [nE, b, b]
 
     def _devices(self) -> List[str]:
@@ -250,16 +299,8 @@ class SimpleTrainingWorkspace(_WorkspaceBase):
         M = L @ L.T
         return M.todense() + self.epsilon * np.eye(M.shape[0], dtype=np.float64)
 
-    def validation_step(self, batch, batch_idx: int):
-        boo_entry = self(batch.x, batch.edge_index, batch.edge_attr)
-        self._log_norms(boo_entry, int(batch.ptr.shape[0]) - 1, "Val")
-        if batch_idx == 0:
-            self.log_converge_batch(boo_entry, batch, "Val", 1)
-        return boo_entry
-
     def test_step(self, batch, batch_idx: int):
-        boo_entry = self(batch.x, batch.edge_index, batch.edge_attr)
-        self.log_converge_batch(boo_entry, batch, "Test", 3)
+        out = self._eval_step(batch, "Test", batch_idx, repeat=3, every_batch=True)
         _, dt = self.inference_step(batch)
         self.log("Test/time_neural_prec", dt, batch_size=1)
-        return boo_entry
+        return out

@@ -34,6 +34,31 @@ def golden_csr(g, prefix):
     return csr_matrix((g[prefix + "_data"], g[prefix + "_indices"], g[prefix + "_indptr"]), shape=(n, n))
 
 
+TRAIN_CASES = ["poisson_b1", "heat_b1", "elast_b3", "synthetic_mild_b1", "poisson_pair_b1"]
+
+
+def load_train_case(name):
+    """tests/golden/train_<name>.npz (minted from the unmodified reference by make_golden_train.py) as
+    (batch: dict of CPU tensors incl. residual / ptr / batch, state_dict, fixture)."""
+    import numpy as np
+    import torch
+
+    t = load_golden("train_" + name)
+    gs = [load_golden(str(c)) for c in t["cases"]]
+    offs = np.cumsum([0] + [g["x"].shape[0] for g in gs])
+
+    def cat(k):
+        return torch.cat([torch.from_numpy(g[k]) for g in gs])
+
+    batch = dict(x=cat("x"), edge_attr=cat("edge_attr"), mask=cat("mask"), matrix_values=cat("matrix_values"),
+                 inv_diag=cat("inv_diag"), rsqrt_diag=cat("rsqrt_diag"),
+                 edge_index=torch.cat([torch.from_numpy(g["raw_edge_index"]) + int(o) for g, o in zip(gs, offs[:-1])], dim=1),
+                 residual=torch.from_numpy(t["residual"]), ptr=torch.from_numpy(t["ptr"]),
+                 batch=torch.repeat_interleave(torch.arange(len(gs)), torch.as_tensor(np.diff(offs))))
+    sd = {str(k): torch.from_numpy(t["sd/" + str(k)].copy()) for k in t["sd_keys"]}
+    return batch, sd, t
+
+
 @pytest.fixture(params=GOLDEN_CASES)
 def golden(request):
     return request.param, load_golden(request.param)

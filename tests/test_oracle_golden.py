@@ -143,3 +143,23 @@ def test_pcg_zero_rhs():
 
     x, its, hist = opcg.pcg_restated(identity(5, format="csr"), np.zeros(5), lambda r: r)
     assert its == 0 and hist == [0.0]
+
+
+# ---- training step: oracle/train.py against the reference's own workspaces + loss under autograd --------
+from conftest import TRAIN_CASES, load_train_case  # noqa: E402
+
+
+@pytest.mark.parametrize("name", TRAIN_CASES)
+@pytest.mark.parametrize("scaled", [False, True], ids=["simple", "scaled"])
+def test_oracle_training_step_matches_reference(name, scaled):
+    """Loss equal to the last bit, every parameter gradient within 2e-6 of max|grad| (autograd accumulation order)."""
+    from oracle import train as otrain
+
+    batch, sd, t = load_train_case(name)
+    tag = "scaled" if scaled else "simple"
+    loss, grads, _ = otrain.training_step(sd, batch, float(t["epsilon"]), int(t["block_size"]), scaled=scaled)
+    assert float(loss) == float(np.float32(t[f"{tag}/loss"]))
+    assert len(grads) == 114
+    for k, g in grads.items():
+        ref = t[f"{tag}/grad/{k}"]
+        assert np.abs(g.numpy() - ref).max() <= 2e-6 * max(np.abs(ref).max(), 1e-12), k
