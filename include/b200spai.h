@@ -256,6 +256,22 @@ int b200spai_graph_outer_f32(b200spai_graph_t g, int32_t block_size, const float
                              int32_t transpose, int32_t accumulate, float* grad_values_dev, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Allocation-free preconditioner apply.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * z = G (G^T r) + epsilon r -- what b200spai_pcg_apply_precond(..., EXT_SPAI, ...) computes -- with the intermediate
+ * G^T r in a file-scope static device array of B200SPAI_NOALLOC_MAX_ROWS doubles (8 MiB per GPU that loads the library,
+ * held until exit) instead of a buffer a solver handle allocated.  G must be square with at most
+ * B200SPAI_NOALLOC_MAX_ROWS rows (larger: B200SPAI_ERR_ARG and a message; nothing is launched) and GT its transpose
+ * (b200spai_csr_transpose, made beforehand).  The call enqueues two kernels on `stream` and allocates nothing: no
+ * cudaMalloc / cudaFree, no pool call, no lazily built matrix stream.  All calls share the one scratch array, which
+ * keeps the last call's contents (every entry read is overwritten first, nothing needs clearing): calls that overlap on
+ * the GPU -- other streams, other host threads -- race on it and must be serialised by the caller.
+ * ---------------------------------------------------------------------------------------------- */
+#define B200SPAI_NOALLOC_MAX_ROWS (1 << 20)
+int b200spai_spai_apply_noalloc(b200spai_csr_t G, b200spai_csr_t GT, double epsilon, const double* r_dev, double* z_dev,
+                                void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Device memory pool.  The library caches the device blocks it releases (a solve step allocates the same
  * multi-GB blocks every time; cudaMalloc/cudaFree of those cost ~0.1 s per step).  Cached blocks are handed out
  * again in the order of the one stream a handle works on.  Limit: B200SPAI_POOL_MAX_GB (default 64).

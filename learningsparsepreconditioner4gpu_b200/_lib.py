@@ -69,6 +69,7 @@ SIGNATURES = {
     "b200spai_gnn_set_weights_dev": [c_vp, c_vp, c_i64, c_vp],
     "b200spai_graph_outer_f32": [c_vp, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp],
     "b200spai_csr_stream_info": [c_vp, C.POINTER(c_i32), C.POINTER(c_i32), c_vp],
+    "b200spai_spai_apply_noalloc": [c_vp, c_vp, c_f64, c_vp, c_vp, c_vp],
     "b200spai_pool_trim": [],
     "b200spai_pool_cached_bytes": [C.POINTER(c_i64)],
     "b200spai_dist_create": [c_i32, c_i32, c_i64, C.POINTER(c_vp)],

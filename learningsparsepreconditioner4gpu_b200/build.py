@@ -19,7 +19,7 @@ OBJ = os.path.join(CSRC, "_obj")
 LIB = os.path.join(HERE, "libb200spai.so")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
-SOURCES = ["csr.cu", "pcg.cu", "pcg_fused.cu", "assemble.cu", "gnn.cu", "dist.cu"]
+SOURCES = ["csr.cu", "pcg.cu", "pcg_fused.cu", "assemble.cu", "gnn.cu", "dist.cu", "noalloc.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
