@@ -927,6 +927,97 @@ def main_shapes(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------------------------------------
+# --mode train: one optimiser step through the fused kernels (the reference's training_step)
+# ---------------------------------------------------------------------------------------------------------
+def main_train(args):
+    """A step = training_step (GNN forward with tape -> AATPE -> RelativeL2Loss_ANorm) + backward + clip + AdamW on ONE
+    collated batch of `--batch` Poisson systems (reference defaults: batch_size 4, config/basic.yaml:9; adamw lr 1e-3,
+    gradient_clip_val 10, config/trainer.yaml; meshes of 4 k - 32 k nodes like its poisson3d_tetmesh set).  One GPU: a
+    data-parallel run would add one all-reduce of the 70 KB gradient per step, which this mode does not measure."""
+    from learningsparsepreconditioner4gpu_b200 import _lib, systems
+    from learningsparsepreconditioner4gpu_b200.neural_cg.data import collate
+
+    _lib.require_cuda()
+    torch.cuda.set_device(0)
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        if int(os.environ.get("RANK", "0")) == 0:
+            print(json.dumps({"mode": "train", "unavailable": "one GPU only (no gradient all-reduce in this mode)"}), flush=True)
+        return
+    B = max(min(args.batch, 16), 1) if args.batch != 64 else 4
+    grids = [16, 20, 25, 32]
+    gen = torch.Generator().manual_seed(0)
+    batches_host = []
+    for k in range(4):                                   # four different batches, cycled: no step sees a cached input
+        samples = [systems.poisson_sample(grids[(k + j) % 4], seed=2000 + 10 * k + j, device="cpu") for j in range(B)]
+        for s_ in samples:
+            s_.residual = torch.randn(s_.num_nodes, 1, generator=gen) * s_.mask
+        batches_host.append(collate(samples).pin_memory())
+    dev_batches = [b.to("cuda") for b in batches_host]
+    ws = systems.default_workspace(dev_batches[0]).cuda().train()
+    opt = torch.optim.AdamW(ws.parameters(), lr=1e-3, weight_decay=3e-3)
+    params = [p for p in ws.parameters() if p.requires_grad]
+
+    def step(batch):
+        opt.zero_grad(set_to_none=True)
+        loss = ws.training_step(batch, 0)
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(params, 10.0)
+        opt.step()
+        return loss.detach()
+
+    for k in range(max(args.warmup, 3)):
+        step(dev_batches[k % 4])
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > the 126 MB L2, rewritten between steps
+    sampler = ClockSampler(0)
+    sampler.start()
+    launches0 = _lib.total_launches()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    torch.cuda.synchronize()
+    losses = []
+    for k in range(args.steps):
+        flush.fill_(k & 255)
+        ev[k][0].record()
+        losses.append(step(dev_batches[k % 4]))
+        ev[k][1].record()
+    torch.cuda.synchronize()
+    launches = _lib.total_launches() - launches0
+    ms = sum(a.elapsed_time(b) for a, b in ev)
+    # end to end: the batch comes from pinned host memory every step, the loss goes back to the host
+    h2d = sum(tensor_bytes(*[v for v in batches_host[k % 4].__dict__.values() if torch.is_tensor(v)]) for k in range(args.steps))
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    t0.record()
+    for k in range(args.steps):
+        flush.fill_(k & 255)
+        loss_host = float(step(batches_host[k % 4].to("cuda", non_blocking=True)).cpu())
+    t1.record()
+    torch.cuda.synchronize()
+    e2e_ms = t0.elapsed_time(t1)
+    clocks = sampler.stop()
+    nodes = sum(int(b.num_nodes) for b in batches_host) / 4.0
+    edges = sum(int(b.num_edges) for b in batches_host) / 4.0
+    # algorithmic flops of the GNN per step: forward 2 * (23.6 k per edge + 7.3 k per node) MAC-flops (VERDICT r01 item 6),
+    # backward = recompute + input gradients + weight gradients = 3 x forward
+    gnn_flops = 4.0 * (edges * 23.6e3 + nodes * 7.3e3)
+    print(json.dumps({
+        "metric": "training samples/s through the fused kernels (training_step + backward + clip + AdamW; SURVEY 8f-4)",
+        "mode": "train", "value": round(B * args.steps / (ms * 1e-3), 2), "unit": "samples/s", "n_gpus": 1, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"collated batches of {B} jittered Kuhn-tet Poisson systems, N in {{4096, 8000, 15625, 32768}} "
+                               f"(mean {nodes:.0f} nodes, {edges:.0f} edges per batch), Dirichlet patch, random rhs, "
+                               "RelativeL2Loss_ANorm, AdamW lr 1e-3, clip 10; L2 flushed between steps (256 MB fill)"},
+        "e2e": {"value": round(B * args.steps / (e2e_ms * 1e-3), 2), "unit": "samples/s",
+                "h2d_bytes_per_step": int(h2d / args.steps), "d2h_bytes_per_step": 4},
+        "roofline": {"bound": "fp32 FFMA", "achieved": round(gnn_flops / (ms / args.steps * 1e-3) / 1e12, 2), "peak": 74.5,
+                     "unit": "TFLOP/s", "frac": round(gnn_flops / (ms / args.steps * 1e-3) / 74.5e12, 3), "traffic": None,
+                     "note": "algorithmic GNN flops of forward + backward (4 x the forward MAC-flops) over the WHOLE step incl. "
+                             "loss, optimiser and host launch gaps; peak = 148 SMs x 128 FFMA x 1.965 GHz"},
+        "loss_first_last": [float(losses[0]), float(losses[-1])], "loss_e2e_last": loss_host,
+        "gpu_launches": int(launches), "clocks": clocks}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -938,7 +1029,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--shapes", default="", help="shapes: comma-separated subset of heat,elast,synth10240,synth15360,synth20480")
     ap.add_argument("--no-replicas", action="store_true", help="N > 1: skip the extra independent-systems (replicas) figure")
-    ap.add_argument("--mode", default="auto", choices=["auto", "batch", "rowpart", "batch_small", "shapes"],
+    ap.add_argument("--mode", default="auto", choices=["auto", "batch", "rowpart", "batch_small", "shapes", "train"],
                     help="auto (the bench contract): N = 1 -> one 10 M-DOF system on one GPU; N > 1 -> the SAME system "
                          "row-partitioned over the N GPUs (strong scaling) with the independent-replicas figure as an extra key; "
                          "batch: one independent system per GPU (weak scaling); rowpart: the row-partitioned line at any N; "
@@ -956,6 +1047,8 @@ def main():
         main_batch_small(args)
     elif args.mode == "shapes":
         main_shapes(args)
+    elif args.mode == "train":
+        main_train(args)
     else:
         ctx = Ctx()
         if args.mode == "rowpart" or (args.mode == "auto" and ctx.world > 1):

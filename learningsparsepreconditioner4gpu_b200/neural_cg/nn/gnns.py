@@ -358,7 +358,12 @@ class NodeEdgeProcessing(nn.Module):
         neither a recycled address nor an in-place edit can alias a stale topology (``graph_key``)."""
         key = graph_key(edge_index, num_nodes)
         if self._graph is None or self._graph.key != key:
-            self._graph = DeviceGraph(edge_index, num_nodes)
+            from . import basic_layers as _bl
+
+            hit = _bl._graph_cache.get("g")
+            self._graph = hit[1] if hit is not None and hit[0] == key else DeviceGraph(edge_index, num_nodes)
+            # the edge-list operators of the same step (AATPE, the loss product) reuse this preprocessing
+            _bl._graph_cache["g"] = (key, self._graph)
         return self._graph
 
     @property
