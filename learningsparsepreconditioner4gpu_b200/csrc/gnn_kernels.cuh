@@ -12,8 +12,13 @@ __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + e
 __device__ __forceinline__ float gelu_as(float x) {
   const float y = fabsf(x) * 0.70710678118654752440f;
   float t, e;
+#ifdef B200SPAI_HOST_EMU  // host build of the backward kernels (tests/host_emu): exact reciprocal / exp2
+  t = 1.0f / fmaf(0.3275911f, y, 1.0f);
+  e = exp2f(y * y * -1.4426950408889634f);
+#else
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, y, 1.0f)));
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(y * y * -1.4426950408889634f));
+#endif
   float p = fmaf(1.061405429f, t, -1.453152027f);
   p = fmaf(p, t, 1.421413741f);
   p = fmaf(p, t, -0.284496736f);
