@@ -137,10 +137,19 @@ __device__ __forceinline__ void mma_act(const float (&acc)[MT][2][4], float (&a)
   for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      a[mt][j][0] = gelu<G>(acc[mt][j][0]);
-      a[mt][j][1] = gelu<G>(acc[mt][j][2]);
-      a[mt][j][2] = gelu<G>(acc[mt][j][1]);
-      a[mt][j][3] = gelu<G>(acc[mt][j][3]);
+      if (G) {  // rational-erfc GELU on pairs (packed fp32 arithmetic, the bits of the scalar form)
+        const float2 u = gelu_as2(make_float2(acc[mt][j][0], acc[mt][j][2]));
+        const float2 v = gelu_as2(make_float2(acc[mt][j][1], acc[mt][j][3]));
+        a[mt][j][0] = u.x;
+        a[mt][j][1] = u.y;
+        a[mt][j][2] = v.x;
+        a[mt][j][3] = v.y;
+      } else {
+        a[mt][j][0] = gelu<G>(acc[mt][j][0]);
+        a[mt][j][1] = gelu<G>(acc[mt][j][2]);
+        a[mt][j][2] = gelu<G>(acc[mt][j][1]);
+        a[mt][j][3] = gelu<G>(acc[mt][j][3]);
+      }
     }
 }
 
