@@ -48,9 +48,27 @@ int emu_gnn_backward(long long N, long long E, int L, int node_in, int edge_in, 
   t.xs = const_cast<float*>(xs);
   t.es = const_cast<float*>(es);
   t.aggs = const_cast<float*>(aggs);
-  const float nan = std::nanf("");
-  std::vector<float> ge(esz, nan), gxs(esz, nan), gxd(esz, nan), gx(xsz, nan), gagg(xsz, nan),
-      partial((size_t)t.max_ctas * BWD_NW_MAX, nan);
+  // every buffer the kernels write sits between two guard bands holding a canary: an out-of-bounds store of up to GUARD
+  // floats on either side is detected after the run (compute-sanitizer is not available on the GPU pool; this and the
+  // comparison with the CPU reference are the memory check of these kernels).  Contents start as NaN: a read of a value no
+  // kernel produced poisons the gradient.
+  constexpr size_t GUARD = 1024;
+  const float nan = std::nanf(""), canary = -7.25e30f;
+  struct Guarded {
+    std::vector<float> v;
+    size_t n;
+    Guarded(size_t n_, float fill, float can) : v(n_ + 2 * GUARD, fill), n(n_) {
+      for (size_t i = 0; i < GUARD; ++i) v[i] = v[GUARD + n + i] = can;
+    }
+    float* data() { return v.data() + GUARD; }
+    bool intact(float can) const {
+      for (size_t i = 0; i < GUARD; ++i)
+        if (v[i] != can || v[GUARD + n + i] != can) return false;
+      return true;
+    }
+  };
+  Guarded ge(esz, nan, canary), gxs(esz, nan, canary), gxd(esz, nan, canary), gx(xsz, nan, canary), gagg(xsz, nan, canary),
+      partial((size_t)t.max_ctas * BWD_NW_MAX, nan, canary), grad((size_t)blob_len, nan, canary);
   t.ge = ge.data();
   t.gxs = gxs.data();
   t.gxd = gxd.data();
@@ -58,7 +76,12 @@ int emu_gnn_backward(long long N, long long E, int L, int node_in, int edge_in, 
   t.gagg = gagg.data();
   t.partial = partial.data();
   t.filled = true;
-  return gnn_backward_impl(&m, &g, &t, x, edge_attr, gG, grad_out, nullptr);
+  const int rc = gnn_backward_impl(&m, &g, &t, x, edge_attr, gG, grad.data(), nullptr);
+  if (rc) return rc;
+  for (const Guarded* b : {&ge, &gxs, &gxd, &gx, &gagg, &partial, &grad})
+    if (!b->intact(canary)) return -77;  // a kernel stored outside its buffer
+  std::memcpy(grad_out, grad.data(), (size_t)blob_len * sizeof(float));
+  return 0;
 }
 
 // gradient of GraphSpmv w.r.t. the matrix values
