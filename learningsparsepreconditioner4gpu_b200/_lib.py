@@ -141,3 +141,27 @@ def require_cuda():
 
     if not torch.cuda.is_available():
         raise B200SpaiError("libb200spai needs a CUDA device (sm_100a); no CPU fallback exists")
+
+
+class nvtx_range:
+    """NVTX range around a phase of the path (``with nvtx_range("b200spai/gnn"): ...``) for nsys / ncu timelines.  Off unless
+    B200SPAI_NVTX=1 (a push / pop pair costs ~1 us of host time: nothing inside a timed step by default)."""
+
+    enabled = os.environ.get("B200SPAI_NVTX", "0") not in ("", "0")
+
+    def __init__(self, name: str):
+        self.name = name
+
+    def __enter__(self):
+        if nvtx_range.enabled:
+            import torch
+
+            torch.cuda.nvtx.range_push(self.name)
+        return self
+
+    def __exit__(self, *exc):
+        if nvtx_range.enabled:
+            import torch
+
+            torch.cuda.nvtx.range_pop()
+        return False

@@ -26,6 +26,7 @@ import torch
 from scipy.sparse import csr_matrix
 from torch import nn
 
+from .._lib import nvtx_range
 from ..device import DeviceCSR, DevicePCG
 from .loss import create_loss_item
 from .nn.basic_layers import AATPE
@@ -116,9 +117,11 @@ class _WorkspaceBase(nn.Module):
         if self.loss_fn is None:
             raise ValueError("the workspace was built without a loss config")
         bsize = int(batch.ptr.shape[0]) - 1
-        boo_entry = self(batch.x, batch.edge_index, batch.edge_attr, autograd=True)
-        d = self._precondition_residual(batch, boo_entry)
-        total_loss = self.loss_fn(batch, d, boo_entry)
+        with nvtx_range("b200spai/train_forward"):
+            boo_entry = self(batch.x, batch.edge_index, batch.edge_attr, autograd=True)
+        with nvtx_range("b200spai/train_aatpe+loss"):
+            d = self._precondition_residual(batch, boo_entry)
+            total_loss = self.loss_fn(batch, d, boo_entry)
         self.log_dict({f"{prefix}/Loss": total_loss.detach()}, batch_size=bsize, prog_bar=(prefix == "Train"))
         # (the reference probes convergence here for Val / Test at batch 0 AND again in validation_step / test_step,
         # workspace.py:107-108,184-185: the same numbers twice; _eval_step below runs the probe once)
@@ -240,14 +243,18 @@ class _WorkspaceBase(nn.Module):
                 raise ValueError("the fixed-topology cache keeps the reference's full pattern of G")
             return self._solve_fixed(sample, topology, rhs, rtol, max_iter, preconditioner, history)
         n = sample.x.shape[0] * self.block_size
-        A = to_csr_device(sample.edge_index, sample.matrix_values, n, sample.mask)
-        G = self.inference_step_device(sample, pattern)
+        with nvtx_range("b200spai/assemble_A"):
+            A = to_csr_device(sample.edge_index, sample.matrix_values, n, sample.mask)
+        with nvtx_range("b200spai/gnn+assemble_G"):
+            G = self.inference_step_device(sample, pattern)
         if rhs is None:
             rhs = A.matvec(sample.mask.reshape(-1).to(torch.float64))
-        solver = DevicePCG(A)
-        solver.set_spai(G, self.epsilon)
-        x, res, hist = solver.solve(rhs.to(torch.float64).reshape(-1), preconditioner, rtol=rtol, max_iter=max_iter,
-                                    history=history)
+        with nvtx_range("b200spai/pcg_setup"):
+            solver = DevicePCG(A)
+            solver.set_spai(G, self.epsilon)
+        with nvtx_range("b200spai/pcg_solve"):
+            x, res, hist = solver.solve(rhs.to(torch.float64).reshape(-1), preconditioner, rtol=rtol, max_iter=max_iter,
+                                        history=history)
         return x, res, hist, A, G
 
 
