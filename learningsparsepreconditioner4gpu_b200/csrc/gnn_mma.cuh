@@ -172,6 +172,52 @@ __device__ __forceinline__ void mlp3_mma(const MmaMlpTab<KC1>* T, int lane, cons
   }
 }
 
+// The first Linear of TWO FeedForwards that read the same input (the message and the edge MLP of a layer share the
+// LayerNorm'ed [x_i, x_j, e]): every input chunk is split into its TF32 halves ONCE and multiplied into both weight
+// tables.  Per output the chunks and the three partial products arrive in the order of mma_linear: the same bits.
+template <int KC, int MT>
+__device__ __forceinline__ void mma_linear_pair(const float4* __restrict__ twA, const float4* __restrict__ twB, int lane,
+                                                const float (&a)[MT][KC][4], float (&accA)[MT][2][4], float (&accB)[MT][2][4]) {
+#pragma unroll
+  for (int c = 0; c < KC; ++c) {
+    uint32_t hi[MT][4], lo[MT][4];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) tf32_split(a[mt][c][i], hi[mt][i], lo[mt][i]);
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+      const float4 wa = twA[(c * 2 + nt) * 32 + lane], wb = twB[(c * 2 + nt) * 32 + lane];
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) {
+        mma_tf32(accA[mt][nt], lo[mt], __float_as_uint(wa.x), __float_as_uint(wa.y));
+        mma_tf32(accB[mt][nt], lo[mt], __float_as_uint(wb.x), __float_as_uint(wb.y));
+        mma_tf32(accA[mt][nt], hi[mt], __float_as_uint(wa.z), __float_as_uint(wa.w));
+        mma_tf32(accB[mt][nt], hi[mt], __float_as_uint(wb.z), __float_as_uint(wb.w));
+        mma_tf32(accA[mt][nt], hi[mt], __float_as_uint(wa.x), __float_as_uint(wa.y));
+        mma_tf32(accB[mt][nt], hi[mt], __float_as_uint(wb.x), __float_as_uint(wb.y));
+      }
+    }
+  }
+}
+
+// Layers 2 and 3 of a FeedForward whose first Linear is already in `acc` (bias included).
+template <int KC1, int MT, int G>
+__device__ __forceinline__ void mlp3_mma_tail(const MmaMlpTab<KC1>* T, int lane, float (&acc)[MT][2][4], float4 (&out)[MT][2]) {
+  float h[MT][2][4];
+  mma_act<MT, G>(acc, h);
+  mma_bias<MT>(T->bias, 1, lane, acc);
+  mma_linear<2, MT>(T->w + 2 * KC1 * 32, lane, h, acc);
+  mma_act<MT, G>(acc, h);
+  mma_bias<MT>(T->bias, 2, lane, acc);
+  mma_linear<2, MT>(T->w + (2 * KC1 + 4) * 32, lane, h, acc);
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt) {
+    out[mt][0] = make_float4(acc[mt][0][0], acc[mt][0][1], acc[mt][1][0], acc[mt][1][1]);
+    out[mt][1] = make_float4(acc[mt][0][2], acc[mt][0][3], acc[mt][1][2], acc[mt][1][3]);
+  }
+}
+
 // float4 of features 4t..4t+3 of the row held in half h -> the two input chunks 2B, 2B+1 of block B
 template <int KC, int MT>
 __device__ __forceinline__ void mma_put(float (&a)[MT][KC][4], int mt, int B, int h, const float4 f) {
@@ -261,21 +307,32 @@ __global__ void __launch_bounds__(MMA_THREADS, 2) gnn_edge_mma_kernel(const MpPa
         mma_put<6, MMA_MT>(v, mt, 2, h, FIRST ? ev[mt][h] : *ef_chunk(P.ef, p, t));
       }
     mma_layernorm<6, MMA_MT>(v);
-#pragma unroll 1
-    for (int m = 0; m < 2; ++m) {  // msg MLP, then edge MLP, through one copy of the code
+    // first Linear of the message and the edge MLP together (one TF32 split of the shared input), then the two tails
+    float accM[MMA_MT][2][4], accE[MMA_MT][2][4];
+    mma_bias<MMA_MT>(s_msg.bias, 0, lane, accM);
+    mma_bias<MMA_MT>(s_edge.bias, 0, lane, accE);
+    mma_linear_pair<6, MMA_MT>(s_msg.w, s_edge.w, lane, v, accM, accE);
+    {
       float4 o[MMA_MT][2];
-      mlp3_mma<6, MMA_MT, G>(m == 0 ? &s_msg : &s_edge, lane, v, o);
+      mlp3_mma_tail<6, MMA_MT, G>(&s_msg, lane, accM, o);
 #pragma unroll
       for (int mt = 0; mt < MMA_MT; ++mt)
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const long long p = p0 + 16 * mt + 8 * h + g;
-          if (m == 0) {
-            reinterpret_cast<float4*>(P.msg + p * F)[t] = o[mt][h];  // msg is padded to a whole tile
-          } else {
-            const float4 e = FIRST ? ev[mt][h] : *ef_chunk(P.ef, p, t), r = o[mt][h];
-            *ef_chunk(P.ef, p, t) = make_float4(e.x + r.x, e.y + r.y, e.z + r.z, e.w + r.w);
-          }
+          reinterpret_cast<float4*>(P.msg + p * F)[t] = o[mt][h];  // msg is padded to a whole tile
+        }
+    }
+    {
+      float4 o[MMA_MT][2];
+      mlp3_mma_tail<6, MMA_MT, G>(&s_edge, lane, accE, o);
+#pragma unroll
+      for (int mt = 0; mt < MMA_MT; ++mt)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const long long p = p0 + 16 * mt + 8 * h + g;
+          const float4 e = FIRST ? ev[mt][h] : *ef_chunk(P.ef, p, t), r = o[mt][h];
+          *ef_chunk(P.ef, p, t) = make_float4(e.x + r.x, e.y + r.y, e.z + r.z, e.w + r.w);
         }
     }
   }
