@@ -378,7 +378,8 @@ class NodeEdgeProcessing(nn.Module):
                 graph: Optional[DeviceGraph] = None, autograd: bool = False):
         """``autograd=False`` (default): inference, no graph is recorded whatever the grad mode.  ``autograd=True`` (the
         workspaces' training / validation steps): the edge output carries a grad_fn whose backward runs the CUDA
-        backward kernels; the node output is returned detached (the workspaces use node_out_features=None)."""
+        backward kernels; the node output is then ``None`` (the workspaces build the GNN with node_out_features=None and
+        use the edge output only, workspace.py:92-94)."""
         _lib.require_cuda()
         if not (node_attr.is_cuda and edge_index.is_cuda and edge_attr.is_cuda):
             raise _lib.B200SpaiError("NodeEdgeProcessing.forward needs CUDA tensors: there is no CPU path")

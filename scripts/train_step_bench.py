@@ -41,7 +41,7 @@ def main():
         torch.cuda.synchronize()
         for k in range(3):
             acc[k] += ev[k].elapsed_time(ev[k + 1])
-        losses.append(float(loss))
+        losses.append(loss.item())
     print(json.dumps({"grid": grid, "N": s.num_nodes, "E": s.num_edges, "steps": steps,
                       "ms_forward_aatpe_loss": round(acc[0] / steps, 3), "ms_backward": round(acc[1] / steps, 3),
                       "ms_optimizer": round(acc[2] / steps, 3), "ms_step": round(sum(acc) / steps, 3),

@@ -57,11 +57,11 @@ def test_training_step_matches_reference(name, scaled):
     ws, batch = _ws(b, sd, int(t["block_size"]), scaled), _batch(b)
     loss = ws.training_step(batch, 0)
     assert loss.requires_grad and loss.dim() == 0
-    ref_loss = float(t[f"{tag}/loss"])
-    assert abs(float(loss) - ref_loss) <= LOSS_RTOL * abs(ref_loss), (float(loss), ref_loss)
+    ref_loss, got_loss = float(t[f"{tag}/loss"]), loss.item()
+    assert abs(got_loss - ref_loss) <= LOSS_RTOL * abs(ref_loss), (got_loss, ref_loss)
     loss.backward()
     worst, where, n = _grad_dev(ws, lambda k: t[f"{tag}/grad/{k}"])
-    print(f"{name} [{tag}]: loss {float(loss):.7f} (reference {ref_loss:.7f}), worst |dgrad|/max|grad| = {worst:.2e} at {where} ({n} tensors)")
+    print(f"{name} [{tag}]: loss {got_loss:.7f} (reference {ref_loss:.7f}), worst |dgrad|/max|grad| = {worst:.2e} at {where} ({n} tensors)")
     assert n == 114
     assert worst <= GRAD_TOL, (where, worst)
     assert "Train/Loss" in ws.logged
@@ -70,7 +70,7 @@ def test_training_step_matches_reference(name, scaled):
     ws.zero_grad(set_to_none=True)
     loss2 = ws.training_step(batch, 0)
     loss2.backward()
-    assert float(loss2) == float(loss)
+    assert loss2.item() == got_loss
     assert all(torch.equal(g1[k], p.grad) for k, p in ws.named_parameters() if p.grad is not None)
 
 
@@ -118,6 +118,7 @@ def test_training_step_matches_oracle_larger(shape):
     sd = {k: v.detach().cpu().clone() for k, v in ws.state_dict().items()}
     loss = ws.training_step(batch.to("cuda"), 0)
     loss.backward()
+    loss = loss.detach()
     ref_loss, ref_grads, _ = otrain.training_step(sd, {k: batch[k] for k in batch.keys()}, ws.epsilon, bs)
     assert abs(float(loss) - float(ref_loss)) <= LOSS_RTOL * abs(float(ref_loss)), (float(loss), float(ref_loss))
     worst, where, n = _grad_dev(ws, lambda k: ref_grads[k].numpy())
