@@ -933,23 +933,28 @@ def main_shapes(args):
 def main_train(args):
     """A step = training_step (GNN forward with tape -> AATPE -> RelativeL2Loss_ANorm) + backward + clip + AdamW on ONE
     collated batch of `--batch` Poisson systems (reference defaults: batch_size 4, config/basic.yaml:9; adamw lr 1e-3,
-    gradient_clip_val 10, config/trainer.yaml; meshes of 4 k - 32 k nodes like its poisson3d_tetmesh set).  One GPU: a
-    data-parallel run would add one all-reduce of the 70 KB gradient per step, which this mode does not measure."""
+    gradient_clip_val 10, config/trainer.yaml; meshes of 4 k - 32 k nodes like its poisson3d_tetmesh set).  Under torchrun:
+    data parallel, every rank its own batches, one all-reduce of the 70 KB gradient per step (weak scaling)."""
     from learningsparsepreconditioner4gpu_b200 import _lib, systems
     from learningsparsepreconditioner4gpu_b200.neural_cg.data import collate
 
+    from learningsparsepreconditioner4gpu_b200.neural_cg.trainer import allreduce_mean_grads
+
     _lib.require_cuda()
-    torch.cuda.set_device(0)
-    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
-        if int(os.environ.get("RANK", "0")) == 0:
-            print(json.dumps({"mode": "train", "unavailable": "one GPU only (no gradient all-reduce in this mode)"}), flush=True)
-        return
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:   # data parallel: every rank its own batches, ONE all-reduce of the flat gradient per step (inside the timed step)
+        import torch.distributed as dist
+
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     B = max(min(args.batch, 16), 1) if args.batch != 64 else 4
     grids = [16, 20, 25, 32]
-    gen = torch.Generator().manual_seed(0)
+    gen = torch.Generator().manual_seed(rank)
     batches_host = []
     for k in range(4):                                   # four different batches, cycled: no step sees a cached input
-        samples = [systems.poisson_sample(grids[(k + j) % 4], seed=2000 + 10 * k + j, device="cpu") for j in range(B)]
+        samples = [systems.poisson_sample(grids[(k + j) % 4], seed=2000 + 100 * rank + 10 * k + j, device="cpu") for j in range(B)]
         for s_ in samples:
             s_.residual = torch.randn(s_.num_nodes, 1, generator=gen) * s_.mask
         batches_host.append(collate(samples).pin_memory())
@@ -962,6 +967,7 @@ def main_train(args):
         opt.zero_grad(set_to_none=True)
         loss = ws.training_step(batch, 0)
         loss.backward()
+        allreduce_mean_grads(params)                     # no-op on one GPU
         torch.nn.utils.clip_grad_norm_(params, 10.0)
         opt.step()
         return loss.detach()
@@ -969,10 +975,12 @@ def main_train(args):
     for k in range(max(args.warmup, 3)):
         step(dev_batches[k % 4])
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > the 126 MB L2, rewritten between steps
-    sampler = ClockSampler(0)
+    sampler = ClockSampler(local)
     sampler.start()
     launches0 = _lib.total_launches()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    if dist is not None:
+        dist.barrier()
     torch.cuda.synchronize()
     losses = []
     for k in range(args.steps):
@@ -995,6 +1003,14 @@ def main_train(args):
     torch.cuda.synchronize()
     e2e_ms = t0.elapsed_time(t1)
     clocks = sampler.stop()
+    if dist is not None:   # the slowest rank sets the pace
+        tmax = torch.tensor([ms, e2e_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        ms, e2e_ms = float(tmax[0]), float(tmax[1])
+        dist.barrier()
+        dist.destroy_process_group()
+        if rank != 0:
+            return
     nodes = sum(int(b.num_nodes) for b in batches_host) / 4.0
     edges = sum(int(b.num_edges) for b in batches_host) / 4.0
     # algorithmic flops of the GNN per step: forward 2 * (23.6 k per edge + 7.3 k per node) MAC-flops,
@@ -1002,17 +1018,18 @@ def main_train(args):
     gnn_flops = 4.0 * (edges * 23.6e3 + nodes * 7.3e3)
     print(json.dumps({
         "metric": "training samples/s through the fused kernels (training_step + backward + clip + AdamW; SURVEY 8f-4)",
-        "mode": "train", "value": round(B * args.steps / (ms * 1e-3), 2), "unit": "samples/s", "n_gpus": 1, "steps": args.steps,
+        "mode": "train", "value": round(world * B * args.steps / (ms * 1e-3), 2), "unit": "samples/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"collated batches of {B} jittered Kuhn-tet Poisson systems, N in {{4096, 8000, 15625, 32768}} "
                                f"(mean {nodes:.0f} nodes, {edges:.0f} edges per batch), Dirichlet patch, random rhs, "
                                "RelativeL2Loss_ANorm, AdamW lr 1e-3, clip 10; L2 flushed between steps (256 MB fill)"},
-        "e2e": {"value": round(B * args.steps / (e2e_ms * 1e-3), 2), "unit": "samples/s",
+        "parallelism": f"dp{world}: every rank its own batches, one all-reduce of the flat gradient (70 KB) per step" if world > 1 else "1 GPU",
+        "e2e": {"value": round(world * B * args.steps / (e2e_ms * 1e-3), 2), "unit": "samples/s",
                 "h2d_bytes_per_step": int(h2d / args.steps), "d2h_bytes_per_step": 4},
         "roofline": {"bound": "fp32 FFMA", "achieved": round(gnn_flops / (ms / args.steps * 1e-3) / 1e12, 2), "peak": 74.5,
                      "unit": "TFLOP/s", "frac": round(gnn_flops / (ms / args.steps * 1e-3) / 74.5e12, 3), "traffic": None,
-                     "note": "algorithmic GNN flops of forward + backward (4 x the forward MAC-flops) over the WHOLE step incl. "
+                     "note": "per GPU; algorithmic GNN flops of forward + backward (4 x the forward MAC-flops) over the WHOLE step incl. "
                              "loss, optimiser and host launch gaps; peak = 148 SMs x 128 FFMA x 1.965 GHz"},
         "loss_first_last": [float(losses[0]), float(losses[-1])], "loss_e2e_last": loss_host,
         "gpu_launches": int(launches), "clocks": clocks}), flush=True)
