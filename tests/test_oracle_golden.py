@@ -163,3 +163,27 @@ def test_oracle_training_step_matches_reference(name, scaled):
     for k, g in grads.items():
         ref = t[f"{tag}/grad/{k}"]
         assert np.abs(g.numpy() - ref).max() <= 2e-6 * max(np.abs(ref).max(), 1e-12), k
+
+
+LOSS_NAMES = ["RelativeL2Loss_PlainNorm", "RelativeL2Loss_ANorm", "L2Loss_ANorm", "PropLoss", "L1Loss", "RelPropLoss",
+              "CosineSimilarityLoss_PlainNorm", "CosineSimilarityLoss_ANorm", "ConjGradLoss_PlainNorm", "ConjGradLoss_ANorm",
+              "ConjGradLoss_ANorm_NoRelative", "NifLoss_Norm"]
+
+
+@pytest.mark.parametrize("batch_less", [False, True], ids=["per_sample", "batch_less"])
+@pytest.mark.parametrize("name", LOSS_NAMES)
+def test_oracle_losses_match_reference(name, batch_less):
+    """Every loss create_loss_item accepts: value and dL/dd against the reference's own classes (train_losses.npz)."""
+    from conftest import load_golden
+    from oracle import train as otrain
+
+    batch, _, _ = load_train_case("poisson_pair_b1")
+    g = load_golden("train_losses")
+    batch["gt"] = torch.from_numpy(g["gt"])
+    d = torch.from_numpy(g["d"]).clone().requires_grad_(True)
+    val = otrain.loss_value(name, batch, d, [int(v) for v in batch["ptr"]], batch_less=batch_less)
+    val.backward()
+    tag = f"{name}/{'batch_less' if batch_less else 'per_sample'}"
+    assert abs(float(val.detach()) - float(g[tag + "/loss"])) <= 2e-6 * abs(float(g[tag + "/loss"]))
+    ref = g[tag + "/grad_d"]
+    assert np.abs(d.grad.numpy() - ref).max() <= 2e-6 * np.abs(ref).max()

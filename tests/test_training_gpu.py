@@ -195,3 +195,37 @@ def test_multi_rank_data_parallel_training():
     print(out)
     assert out["world"] == world and out["identical_replicas"] and out["max_rel_dev_vs_single_process"] < 1e-5
     assert out["loss"][-1] < out["loss"][0]
+
+
+LOSS_NAMES = ["RelativeL2Loss_PlainNorm", "RelativeL2Loss_ANorm", "L2Loss_ANorm", "PropLoss", "L1Loss", "RelPropLoss",
+              "CosineSimilarityLoss_PlainNorm", "CosineSimilarityLoss_ANorm", "ConjGradLoss_PlainNorm", "ConjGradLoss_ANorm",
+              "ConjGradLoss_ANorm_NoRelative", "NifLoss_Norm"]
+
+
+@pytest.mark.parametrize("batch_less", [False, True], ids=["per_sample", "batch_less"])
+def test_every_loss_matches_the_reference(batch_less):
+    """neural_cg/loss.py mirror: every name create_loss_item accepts (loss.py:420-459), value and dL/dd against the
+    reference's own loss classes (tests/golden/train_losses.npz) -- the A d product and its gradient run through
+    b200spai_graph_spmv_f32.  Bar: 1e-5 relative (fp32; the kernel sums in the reference's CPU order)."""
+    from conftest import load_golden
+    from learningsparsepreconditioner4gpu_b200.neural_cg.loss import create_loss_item
+
+    b, _, _ = load_train_case("poisson_pair_b1")
+    g = load_golden("train_losses")
+    assert [str(n) for n in g["names"]] == LOSS_NAMES
+    b["gt"] = torch.from_numpy(g["gt"])
+    batch = _batch(b)
+    worst = 0.0
+    for name in LOSS_NAMES:
+        d = torch.from_numpy(g["d"]).cuda().requires_grad_(True)
+        loss = create_loss_item(name, batch_less=batch_less, block_size=1)(batch, d, None)
+        loss.backward()
+        tag = f"{name}/{'batch_less' if batch_less else 'per_sample'}"
+        ref_loss, ref_grad = float(g[tag + "/loss"]), g[tag + "/grad_d"]
+        e_loss = abs(loss.item() - ref_loss) / abs(ref_loss)
+        e_grad = float(np.abs(d.grad.cpu().numpy() - ref_grad).max() / np.abs(ref_grad).max())
+        worst = max(worst, e_loss, e_grad)
+        assert e_loss <= 1e-5 and e_grad <= 1e-5, (name, e_loss, e_grad)
+    print(f"{'batch_less' if batch_less else 'per_sample'}: 12 losses, worst relative deviation {worst:.2e}")
+    with pytest.raises(ValueError, match="Unknown loss"):
+        create_loss_item("NoSuchLoss", batch_less=False, block_size=1)
