@@ -175,3 +175,45 @@ def test_batch_solver_needs_cuda():
 
     with pytest.raises(_lib.B200SpaiError):
         CollatedBatchSolver(None)               # the collated (one launch per wave) path has no CPU fallback either
+
+
+def test_weight_blob_pack_and_gradient_unpack_are_consistent():
+    """Training plumbing on the host: pack_state_dict_torch (device-side repack after an optimiser step) gives the bits of
+    pack_state_dict, and unpack_grad_blob is the exact adjoint of the packing (LayerNorm affine un-folded, transposes and
+    padding undone): for L = <blob(params), c> autograd's dL/dparams must equal unpack_grad_blob(c)."""
+    from learningsparsepreconditioner4gpu_b200.neural_cg.nn import gnns
+
+    ws = make_workspace(5, 9, 3)
+    sd = {k: v.detach().clone() for k, v in ws.gnn.state_dict().items()}
+    gen = torch.Generator().manual_seed(0)
+    for k, v in sd.items():
+        if "pre_norm" in k:                                   # random init leaves the affines at 1 / 0
+            v.copy_(torch.randn(v.shape, generator=gen))
+    L = 4
+    a = gnns.pack_state_dict(sd, L)
+    assert a.size == gnns.blob_length(L) and np.array_equal(a, gnns.pack_state_dict_torch(sd, L).numpy())
+
+    params = {k: v.clone().double().requires_grad_(True) for k, v in sd.items() if "node_msg_norm" not in k}
+
+    def pack_autograd(p):
+        parts = []
+        for pre, _, k_pad in gnns.blob_layout(L):
+            W1, b1 = p[pre + "lift.0.weight"], p[pre + "lift.0.bias"]
+            if pre + "pre_norm.weight" in p:
+                b1 = b1 + W1 @ p[pre + "pre_norm.bias"]
+                W1 = W1 * p[pre + "pre_norm.weight"][None, :]
+            W3 = p[pre + "proj.0.weight"]
+            W1t = torch.cat([W1.T, W1.new_zeros(k_pad - W1.shape[1], 16)])
+            W3t = torch.cat([W3.T, W3.new_zeros(16, 16 - W3.shape[0])], dim=1)
+            b3 = torch.cat([p[pre + "proj.0.bias"], W3.new_zeros(16 - W3.shape[0])])
+            parts += [W1t.reshape(-1), b1, p[pre + "body.0.0.weight"].T.reshape(-1), p[pre + "body.0.0.bias"], W3t.reshape(-1), b3]
+        return torch.cat(parts)
+
+    blob = pack_autograd(params)
+    assert np.allclose(blob.detach().numpy(), a, rtol=0, atol=1e-6)
+    coef = torch.randn(a.size, dtype=torch.float64, generator=gen)
+    (blob * coef).sum().backward()
+    got = gnns.unpack_grad_blob(coef, {k: v.detach() for k, v in params.items()}, L)
+    assert set(got) == set(params) and len(got) == 114
+    for k, v in params.items():
+        assert got[k].shape == v.shape and torch.allclose(got[k], v.grad, rtol=0, atol=1e-12), k
