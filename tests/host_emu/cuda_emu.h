@@ -29,7 +29,8 @@
 #define __launch_bounds__(...)
 #define __restrict__
 #define __align__(n) __attribute__((aligned(n)))
-#define __shared__ static thread_local  /* only inside forward kernels that this build never instantiates */
+#define __shared__ static  /* a static array of a kernel (template instance) is shared by the host threads of the CTA that
+                              runs; CTAs run one after the other, so it behaves like per-CTA shared memory */
 
 struct float2 { float x, y; };
 struct alignas(16) float4 { float x, y, z, w; };

@@ -84,6 +84,73 @@ int emu_gnn_backward(long long N, long long E, int L, int node_in, int edge_in, 
   return 0;
 }
 
+}  // extern "C"
+
+// The FFMA forward kernels (gnn_kernels.cuh) in the stage order of gnn.cu::gnn_stage: node encoder, L x (edge kernel, node
+// kernel) with ping-pong node features, decoder.  gelu_cfg: 0 = erff, 1 = rational erfc (B200SPAI_GNN_CFG 0 / 2).
+// Workspaces are allocated here: ef (tiled) and msg [Epad][16], x0 / x1 [N][16].
+template <int G>
+static void emu_forward_impl(long long N, long long E, int L, int node_in, int edge_in, int bb, const float* blob, const int* perm,
+                             const int* src, const int* dst, const int* segptr, const float* x, const float* edge_attr,
+                             int sm_count, float* g_out, float* node_out) {
+  using namespace b200spai;
+  const long long Epad = ((E + 31) / 32) * 32;
+  const float nan = std::nanf("");
+  std::vector<float> ef((size_t)Epad * 16, nan), msg((size_t)Epad * 16, nan), x0((size_t)N * 16, nan), x1((size_t)N * 16, nan);
+  float* xb[2] = {x0.data(), x1.data()};
+  const float* w_node_enc = blob;
+  const float* w_edge_enc = blob + MLP16;
+  const float* w_layers = blob + 2 * MLP16;
+  const float* w_dec = w_layers + (long long)L * LAYER_FLOATS;
+  long long grid = std::min<long long>((N + 255) / 256, 4LL * sm_count);
+  B2_LAUNCH(gnn_node_enc_kernel<G>, grid, 256, 0, nullptr, x, node_in, N, w_node_enc, xb[0]);
+  for (int stage = 1; stage <= L; ++stage) {
+    MpParams P{};
+    P.src = src;
+    P.dst = dst;
+    P.segptr = segptr;
+    P.perm = perm;
+    P.E = E;
+    P.N = N;
+    P.ef = ef.data();
+    P.msg = msg.data();
+    P.xin = xb[(stage - 1) & 1];
+    P.xout = xb[stage & 1];
+    P.w_layer = w_layers + (long long)(stage - 1) * LAYER_FLOATS;
+    P.w_eenc = w_edge_enc;
+    P.edge_attr = edge_attr;
+    P.edge_in = edge_in;
+    grid = std::min<long long>((E + MP_THREADS - 1) / MP_THREADS, 2LL * sm_count);
+    if (stage == 1) B2_LAUNCH((gnn_edge_kernel<true, G>), grid, MP_THREADS, 0, nullptr, P);
+    else B2_LAUNCH((gnn_edge_kernel<false, G>), grid, MP_THREADS, 0, nullptr, P);
+    grid = std::min<long long>((N + 255) / 256, 4LL * sm_count);
+    B2_LAUNCH(gnn_node_kernel<G>, grid, 256, 0, nullptr, P);
+  }
+  grid = std::min<long long>((E + 255) / 256, 2LL * sm_count);
+  B2_LAUNCH(gnn_dec_kernel<G>, grid, 256, 0, nullptr, src, dst, perm, ef.data(), (const float*)xb[L & 1], w_dec, E, bb, g_out);
+  std::memcpy(node_out, xb[L & 1], (size_t)N * 16 * sizeof(float));
+}
+
+extern "C" {
+
+int emu_gnn_forward(long long N, long long E, int L, int node_in, int edge_in, int bb, const float* blob, long long blob_len,
+                    const int* perm, const int* src, const int* dst, const int* segptr, const float* x, const float* edge_attr,
+                    int gelu_cfg, int sm_count, float* g_out, float* node_out) {
+  if (blob_len != b200spai_gnn_s::expected_len(L) || N < 1 || E < 1) return -2;
+  if (gelu_cfg) emu_forward_impl<1>(N, E, L, node_in, edge_in, bb, blob, perm, src, dst, segptr, x, edge_attr, sm_count, g_out, node_out);
+  else emu_forward_impl<0>(N, E, L, node_in, edge_in, bb, blob, perm, src, dst, segptr, x, edge_attr, sm_count, g_out, node_out);
+  return 0;
+}
+
+// GraphSpmv (graph_spmv_f32_kernel): transpose -> aggregation at edge_index[1] over the target-sorted view (segptr / perm /
+// other = src), else at edge_index[0] over the row-sorted view (rsegptr / rperm / other = rcol)
+void emu_graph_spmv(long long N, int b, const int* segptr, const int* perm, const int* other, const float* vals, const float* x,
+                    const float* mask, int transpose, float* y) {
+  const long long rows = N * b;
+  if (transpose) B2_LAUNCH(b200spai::graph_spmv_f32_kernel<true>, (rows + 255) / 256, 256, 0, nullptr, segptr, perm, other, N, b, vals, x, mask, y);
+  else B2_LAUNCH(b200spai::graph_spmv_f32_kernel<false>, (rows + 255) / 256, 256, 0, nullptr, segptr, perm, other, N, b, vals, x, mask, y);
+}
+
 // gradient of GraphSpmv w.r.t. the matrix values
 void emu_graph_outer(long long E, int b, const int* perm, const int* src, const int* dst, const float* gy, const float* x,
                      int transpose, int accumulate, float* gA) {

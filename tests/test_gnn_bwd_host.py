@@ -1,4 +1,5 @@
-"""CPU check of the GNN backward kernels (csrc/gnn_bwd.cuh) and their driver (csrc/gnn_train.cuh).
+"""CPU check of the GNN backward kernels (csrc/gnn_bwd.cuh) and their driver (csrc/gnn_train.cuh) -- and, since the same
+emulation runs them, of the FFMA forward kernels and GraphSpmv (csrc/gnn_kernels.cuh) against the oracle.
 
 The kernels are compiled for the HOST by tests/host_emu (one host thread per CUDA thread, barriers for __syncwarp /
 __syncthreads, see cuda_emu.h) and run on the tape a torch forward of the oracle produces; the parameter gradients
@@ -41,6 +42,10 @@ def emu():
     lib.emu_gnn_backward.restype = C.c_int
     lib.emu_graph_outer.argtypes = [C.c_longlong, C.c_int, vp, vp, vp, vp, vp, C.c_int, C.c_int, vp]
     lib.emu_graph_outer.restype = None
+    lib.emu_gnn_forward.argtypes = [C.c_longlong, C.c_longlong, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_longlong] + [vp] * 6 + [C.c_int, C.c_int, vp, vp]
+    lib.emu_gnn_forward.restype = C.c_int
+    lib.emu_graph_spmv.argtypes = [C.c_longlong, C.c_int, vp, vp, vp, vp, vp, vp, C.c_int, vp]
+    lib.emu_graph_spmv.restype = None
     return lib
 
 
@@ -201,3 +206,58 @@ def test_backward_kernels_reproduce_reference_training_gradients(emu, name):
         worst = max(worst, err)
         assert err < 2e-4, (k, err)
     print(f"{name}: worst |dgrad|/max|grad| against the reference = {worst:.2e} over {len(got)} tensors")
+
+
+
+@pytest.mark.parametrize("name,make", CASES, ids=[c[0] for c in CASES])
+@pytest.mark.parametrize("gelu_cfg", [0, 1], ids=["erff", "rational_erfc"])
+def test_forward_ffma_kernels_match_oracle(emu, name, make, gelu_cfg):
+    """The FFMA forward kernels (node encoder, edge kernel incl. the fused edge encoder, node kernel, decoder; the path
+    B200SPAI_GNN_CFG = 0 / 2 selects on the GPU) compiled for the host against the oracle's NodeEdgeProcessing: G within
+    1e-5 of max|G| (the bar of the GPU tests), final node features likewise."""
+    s, b = make()
+    ws = systems.default_workspace(s, block_size=b)
+    sd = {k: v.detach().clone() for k, v in ws.gnn.state_dict().items()}
+    gen = torch.Generator().manual_seed(5)
+    for k, v in sd.items():
+        if "pre_norm" in k:
+            v.add_(0.3 * torch.randn(v.shape, generator=gen))
+    with torch.no_grad():
+        node_ref, out_ref = ognn.node_edge_processing({"gnn." + k: v for k, v in sd.items()}, s.x, s.edge_index, s.edge_attr)
+    N, E, L = s.num_nodes, s.num_edges, 4
+    perm, src, dst, segptr, _, _ = graph_arrays(s.edge_index, N)
+    blob = gnns.pack_state_dict(sd, L)
+    x_np = np.ascontiguousarray(s.x.numpy(), dtype=np.float32)
+    ea_np = np.ascontiguousarray(s.edge_attr.numpy(), dtype=np.float32)
+    g_out = np.full((E, b * b), np.nan, dtype=np.float32)
+    node_out = np.full((N, 16), np.nan, dtype=np.float32)
+    rc = emu.emu_gnn_forward(N, E, L, x_np.shape[1], ea_np.shape[1], b * b, _ptr(blob), blob.size, _ptr(perm), _ptr(src), _ptr(dst),
+                             _ptr(segptr), _ptr(x_np), _ptr(ea_np), gelu_cfg, 2, _ptr(g_out), _ptr(node_out))
+    assert rc == 0
+    err_g = np.abs(g_out - out_ref.numpy()).max() / np.abs(out_ref.numpy()).max()
+    err_x = np.abs(node_out - node_ref.numpy()).max() / np.abs(node_ref.numpy()).max()
+    print(f"{name} gelu_cfg={gelu_cfg}: |dG|/max|G| = {err_g:.2e}, |dx|/max|x| = {err_x:.2e}")
+    assert err_g <= 1e-5 and err_x <= 1e-5
+
+
+@pytest.mark.parametrize("b", [1, 3])
+@pytest.mark.parametrize("transpose", [0, 1])
+@pytest.mark.parametrize("masked", [False, True])
+def test_graph_spmv_kernel_matches_oracle(emu, b, transpose, masked):
+    """graph_spmv_f32_kernel (GraphSpmv, basic_layers.py:112-142) against the oracle's operator: the kernel adds a target's
+    edges in ascending edge order like the CPU scatter_add_ of the reference."""
+    s, _ = (systems.poisson_sample(5, device="cpu"), 1) if b == 1 else (systems.elasticity_sample(4, 3, 3, device="cpu"), 3)
+    N, E = s.num_nodes, s.num_edges
+    gen = torch.Generator().manual_seed(8)
+    A = torch.randn(E, b, b, generator=gen)
+    X = torch.randn(N, b, generator=gen)
+    mask = (torch.rand(N, b, generator=gen) > 0.3).float() if masked else None
+    ref = ognn.graph_spmv(X, s.edge_index, A, mask, transpose=bool(transpose)).numpy()
+    perm, src, dst, segptr, rperm, rsegptr = graph_arrays(s.edge_index, N)
+    rcol = s.edge_index[1].numpy()[rperm].astype(np.int32)
+    y = np.full((N, b), np.nan, dtype=np.float32)
+    seg, pm, other = (segptr, perm, src) if transpose else (rsegptr, rperm, rcol)
+    m_np = None if mask is None else np.ascontiguousarray(mask.numpy())
+    emu.emu_graph_spmv(N, b, _ptr(seg), _ptr(pm), _ptr(other), _ptr(np.ascontiguousarray(A.numpy())), _ptr(np.ascontiguousarray(X.numpy())),
+                       _ptr(m_np) if m_np is not None else None, transpose, _ptr(y))
+    assert np.allclose(y, ref, rtol=1e-6, atol=1e-6)
