@@ -43,14 +43,17 @@ __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
 #endif
 }
 
-#ifndef B200SPAI_HOST_EMU
 // Packed fp32 multiply (FMUL2): two independent mul.rn.f32 per instruction, same bits as two FMUL.
 __device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+#ifdef B200SPAI_HOST_EMU
+  return make_float2(a.x * b.x, a.y * b.y);
+#else
   float2 d;
   asm("mul.rn.f32x2 %0, %1, %2;"
       : "=l"(reinterpret_cast<unsigned long long&>(d))
       : "l"(reinterpret_cast<const unsigned long long&>(a)), "l"(reinterpret_cast<const unsigned long long&>(b)));
   return d;
+#endif
 }
 // gelu_as on a pair: the SAME operation sequence per element (every packed op rounds like its scalar form), so the
 // result has the bits of (gelu_as(x.x), gelu_as(x.y)) at about two thirds of the issue slots.
@@ -59,10 +62,15 @@ __device__ __forceinline__ float2 gelu_as2(float2 x) {
   const float2 d = ffma2(make_float2(0.3275911f, 0.3275911f), y, make_float2(1.0f, 1.0f));
   const float2 a = fmul2(fmul2(y, y), make_float2(-1.4426950408889634f, -1.4426950408889634f));
   float2 t, e;
+#ifdef B200SPAI_HOST_EMU
+  t = make_float2(1.0f / d.x, 1.0f / d.y);
+  e = make_float2(exp2f(a.x), exp2f(a.y));
+#else
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t.x) : "f"(d.x));
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t.y) : "f"(d.y));
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.x) : "f"(a.x));
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.y) : "f"(a.y));
+#endif
   float2 p = ffma2(make_float2(1.061405429f, 1.061405429f), t, make_float2(-1.453152027f, -1.453152027f));
   p = ffma2(p, t, make_float2(1.421413741f, 1.421413741f));
   p = ffma2(p, t, make_float2(-0.284496736f, -0.284496736f));
@@ -71,7 +79,6 @@ __device__ __forceinline__ float2 gelu_as2(float2 x) {
   const float2 c = make_float2(x.x >= 0.0f ? 1.0f - h.x : h.x, x.y >= 0.0f ? 1.0f - h.y : h.y);
   return fmul2(x, c);
 }
-#endif
 
 // y[j] = bias[j] + sum_k x[k] * W[k][j];  W [K][16] and bias [16] in shared memory (16-byte aligned).
 // Every lane reads the same addresses (broadcast LDS.128), 4 weights per load, 8 FFMA2 (= 16 FMA) per k.

@@ -31,9 +31,13 @@ constexpr int MMA_NE48 = 2 * 6 + 8;  // table entries of a 48->16->16->16 MLP (c
 constexpr int MMA_NE16 = 2 * 2 + 8;  // 16->16->16->16
 
 __device__ __forceinline__ uint32_t tf32_rna(float x) {
+#ifdef B200SPAI_HOST_EMU  // host build (tests/host_emu): round to nearest, ties away, on the bit pattern (finite inputs)
+  return (__float_as_uint(x) + 0x1000u) & 0xffffe000u;
+#else
   uint32_t r;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
   return r;
+#endif
 }
 
 // Activations: cvt.rna.tf32.f32 compiles to 4 instructions on sm_100a (FSETP |x| < inf, IADD 0x1000, SEL, LOP3); the
@@ -42,7 +46,11 @@ __device__ __forceinline__ uint32_t tf32_rna(float x) {
 // layer-1 inputs must not be hoisted out of the msg/edge loop (they would occupy 96 registers).
 __device__ __forceinline__ void tf32_split(float a, uint32_t& hi, uint32_t& lo) {
   uint32_t h, l;
+#ifdef B200SPAI_HOST_EMU
+  h = __float_as_uint(a) + 0x1000u;
+#else
   asm volatile("add.u32 %0, %1, 0x1000;" : "=r"(h) : "r"(__float_as_uint(a)));
+#endif
   h &= 0xffffe000u;
   l = (__float_as_uint(a - __uint_as_float(h)) + 0x1000u) & 0xffffe000u;
   hi = h;
@@ -50,9 +58,13 @@ __device__ __forceinline__ void tf32_split(float a, uint32_t& hi, uint32_t& lo) 
 }
 
 __device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+#ifdef B200SPAI_HOST_EMU  // warp-collective software mma with the PTX fragment layout (tests/host_emu/cuda_emu.h)
+  emu_mma_m16n8k8_tf32(c, a, b0, b1);
+#else
   asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
       : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+#endif
 }
 
 // Shared-memory image of one 3-Linear MLP: B fragments + C-fragment-ordered biases.

@@ -41,9 +41,13 @@ struct emu_dim3 { unsigned x = 1, y = 1, z = 1; };
 static thread_local emu_dim3 threadIdx, blockIdx;
 static emu_dim3 blockDim, gridDim;
 
+struct EmuWarpXch {
+  alignas(16) uint64_t w[32][4];  // one exchange slot per lane (shuffles: w[lane][0]; mma: A, B fragments)
+};
 struct EmuCta {
   std::unique_ptr<std::barrier<>> cta;
   std::vector<std::unique_ptr<std::barrier<>>> warps;
+  std::vector<EmuWarpXch> xch;
   float* smem = nullptr;
 };
 static EmuCta* emu_cta = nullptr;
@@ -51,6 +55,63 @@ static inline void __syncthreads() { emu_cta->cta->arrive_and_wait(); }
 static inline void __syncwarp() { emu_cta->warps[threadIdx.x >> 5]->arrive_and_wait(); }
 template <typename T>
 static inline T __ldg(const T* p) { return *p; }
+static inline uint32_t __float_as_uint(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
+static inline float __uint_as_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
+
+// Warp shuffles: every lane publishes its value in the warp's exchange block, the warp meets, every lane reads its source
+// lane, the warp meets again (the block is free for the next collective).  All 32 lanes must call (full mask).
+template <typename T>
+static inline T emu_shfl(T v, int src_lane) {
+  static_assert(sizeof(T) <= 8, "shuffle of at most 8 bytes");
+  EmuWarpXch& x = emu_cta->xch[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  std::memcpy(&x.w[lane][0], &v, sizeof(T));
+  __syncwarp();
+  T out;
+  std::memcpy(&out, &x.w[src_lane & 31][0], sizeof(T));
+  __syncwarp();
+  return out;
+}
+template <typename T>
+static inline T __shfl_xor_sync(unsigned, T v, int lane_mask, int width = 32) { (void)width; return emu_shfl(v, (int)(threadIdx.x & 31) ^ lane_mask); }
+template <typename T>
+static inline T __shfl_sync(unsigned, T v, int src, int width = 32) {
+  const int lane = threadIdx.x & 31;
+  return emu_shfl(v, (lane & ~(width - 1)) | (src & (width - 1)));
+}
+
+// mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 in software, with the fragment layout of the PTX ISA (lane = 4 g + t):
+//   A (16 x 8, row):  a0 = (g, t)  a1 = (g + 8, t)  a2 = (g, t + 4)  a3 = (g + 8, t + 4)
+//   B (8 x 8, col):   b0 = (k = t, n = g)  b1 = (k = t + 4, n = g)
+//   C / D (16 x 8):   c0 = (g, 2t)  c1 = (g, 2t + 1)  c2 = (g + 8, 2t)  c3 = (g + 8, 2t + 1)
+// Operands are taken as TF32 (low 13 mantissa bits ignored, as the hardware does); the 8 products of an output are summed
+// in double and added to the fp32 accumulator with one rounding (the hardware's internal order is unspecified).
+static inline void emu_mma_m16n8k8_tf32(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  EmuWarpXch& x = emu_cta->xch[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  uint32_t* mine = reinterpret_cast<uint32_t*>(&x.w[lane][0]);
+  for (int i = 0; i < 4; ++i) mine[i] = a[i] & 0xffffe000u;
+  mine[4] = b0 & 0xffffe000u;
+  mine[5] = b1 & 0xffffe000u;
+  __syncwarp();
+  auto A = [&](int row, int k) {  // element (row, k) of the 16 x 8 A tile
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(&x.w[4 * (row & 7) + (k & 3)][0]);
+    return (double)__uint_as_float(w[(row >> 3) + 2 * (k >> 2)]);
+  };
+  auto B = [&](int k, int n) {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(&x.w[4 * n + (k & 3)][0]);
+    return (double)__uint_as_float(w[4 + (k >> 2)]);
+  };
+  float out[4];
+  for (int i = 0; i < 4; ++i) {
+    const int row = g + 8 * (i >> 1), n = 2 * t + (i & 1);
+    double sum = 0.0;
+    for (int k = 0; k < 8; ++k) sum += A(row, k) * B(k, n);
+    out[i] = (float)((double)c[i] + sum);
+  }
+  __syncwarp();
+  for (int i = 0; i < 4; ++i) c[i] = out[i];
+}
 static inline float __fadd_rn(float a, float b) { return a + b; }
 static inline float __fmul_rn(float a, float b) { return a * b; }
 #define B2_DYN_SMEM(name) float* name = emu_cta->smem
@@ -63,6 +124,7 @@ static void emu_launch(K kernel, long long grid, int block, size_t smem_bytes, A
     EmuCta cta;
     cta.cta = std::make_unique<std::barrier<>>(block);
     for (int w = 0; w < (block + 31) / 32; ++w) cta.warps.push_back(std::make_unique<std::barrier<>>(std::min(32, block - 32 * w)));
+    cta.xch.resize((block + 31) / 32);
     void* raw = std::aligned_alloc(128, ((smem_bytes + 127) / 128 + 1) * 128);
     std::memset(raw, 0xff, ((smem_bytes + 127) / 128 + 1) * 128);  // NaN pattern: uninitialised shared memory must not go unnoticed
     cta.smem = static_cast<float*>(raw);

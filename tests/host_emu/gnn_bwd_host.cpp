@@ -8,6 +8,7 @@
 typedef b200spai_graph_s* b200spai_graph_t;
 typedef b200spai_gnn_s* b200spai_gnn_t;
 #include "gnn_kernels.cuh"
+#include "gnn_mma.cuh"
 #include "gnn_bwd.cuh"
 #include "gnn_train.cuh"
 
@@ -89,7 +90,7 @@ int emu_gnn_backward(long long N, long long E, int L, int node_in, int edge_in, 
 // The FFMA forward kernels (gnn_kernels.cuh) in the stage order of gnn.cu::gnn_stage: node encoder, L x (edge kernel, node
 // kernel) with ping-pong node features, decoder.  gelu_cfg: 0 = erff, 1 = rational erfc (B200SPAI_GNN_CFG 0 / 2).
 // Workspaces are allocated here: ef (tiled) and msg [Epad][16], x0 / x1 [N][16].
-template <int G>
+template <int G, bool MMA>
 static void emu_forward_impl(long long N, long long E, int L, int node_in, int edge_in, int bb, const float* blob, const int* perm,
                              const int* src, const int* dst, const int* segptr, const float* x, const float* edge_attr,
                              int sm_count, float* g_out, float* node_out) {
@@ -121,13 +122,19 @@ static void emu_forward_impl(long long N, long long E, int L, int node_in, int e
     P.edge_attr = edge_attr;
     P.edge_in = edge_in;
     grid = std::min<long long>((E + MP_THREADS - 1) / MP_THREADS, 2LL * sm_count);
-    if (stage == 1) B2_LAUNCH((gnn_edge_kernel<true, G>), grid, MP_THREADS, 0, nullptr, P);
-    else B2_LAUNCH((gnn_edge_kernel<false, G>), grid, MP_THREADS, 0, nullptr, P);
+    if (MMA) {   // the tensor-core kernels (the GPU default): a warp per 32 edges, 8 warps per CTA
+      if (stage == 1) B2_LAUNCH((gnn_edge_mma_kernel<true, G>), grid, MMA_THREADS, 0, nullptr, P);
+      else B2_LAUNCH((gnn_edge_mma_kernel<false, G>), grid, MMA_THREADS, 0, nullptr, P);
+    } else {
+      if (stage == 1) B2_LAUNCH((gnn_edge_kernel<true, G>), grid, MP_THREADS, 0, nullptr, P);
+      else B2_LAUNCH((gnn_edge_kernel<false, G>), grid, MP_THREADS, 0, nullptr, P);
+    }
     grid = std::min<long long>((N + 255) / 256, 4LL * sm_count);
     B2_LAUNCH(gnn_node_kernel<G>, grid, 256, 0, nullptr, P);
   }
   grid = std::min<long long>((E + 255) / 256, 2LL * sm_count);
-  B2_LAUNCH(gnn_dec_kernel<G>, grid, 256, 0, nullptr, src, dst, perm, ef.data(), (const float*)xb[L & 1], w_dec, E, bb, g_out);
+  if (MMA) B2_LAUNCH(gnn_dec_mma_kernel<G>, grid, MMA_THREADS, 0, nullptr, src, dst, perm, ef.data(), (const float*)xb[L & 1], w_dec, E, bb, g_out);
+  else B2_LAUNCH(gnn_dec_kernel<G>, grid, 256, 0, nullptr, src, dst, perm, ef.data(), (const float*)xb[L & 1], w_dec, E, bb, g_out);
   std::memcpy(node_out, xb[L & 1], (size_t)N * 16 * sizeof(float));
 }
 
@@ -137,8 +144,13 @@ int emu_gnn_forward(long long N, long long E, int L, int node_in, int edge_in, i
                     const int* perm, const int* src, const int* dst, const int* segptr, const float* x, const float* edge_attr,
                     int gelu_cfg, int sm_count, float* g_out, float* node_out) {
   if (blob_len != b200spai_gnn_s::expected_len(L) || N < 1 || E < 1) return -2;
-  if (gelu_cfg) emu_forward_impl<1>(N, E, L, node_in, edge_in, bb, blob, perm, src, dst, segptr, x, edge_attr, sm_count, g_out, node_out);
-  else emu_forward_impl<0>(N, E, L, node_in, edge_in, bb, blob, perm, src, dst, segptr, x, edge_attr, sm_count, g_out, node_out);
+  // gelu_cfg: bit 0 = rational-erfc GELU, bit 1 = tensor-core per-edge MLPs (3 = the GPU default, B200SPAI_GNN_CFG = 6)
+  switch (gelu_cfg & 3) {
+    case 0: emu_forward_impl<0, false>(N, E, L, node_in, edge_in, bb, blob, perm, src, dst, segptr, x, edge_attr, sm_count, g_out, node_out); break;
+    case 1: emu_forward_impl<1, false>(N, E, L, node_in, edge_in, bb, blob, perm, src, dst, segptr, x, edge_attr, sm_count, g_out, node_out); break;
+    case 2: emu_forward_impl<0, true>(N, E, L, node_in, edge_in, bb, blob, perm, src, dst, segptr, x, edge_attr, sm_count, g_out, node_out); break;
+    default: emu_forward_impl<1, true>(N, E, L, node_in, edge_in, bb, blob, perm, src, dst, segptr, x, edge_attr, sm_count, g_out, node_out); break;
+  }
   return 0;
 }
 

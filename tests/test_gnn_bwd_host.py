@@ -210,11 +210,14 @@ def test_backward_kernels_reproduce_reference_training_gradients(emu, name):
 
 
 @pytest.mark.parametrize("name,make", CASES, ids=[c[0] for c in CASES])
-@pytest.mark.parametrize("gelu_cfg", [0, 1], ids=["erff", "rational_erfc"])
-def test_forward_ffma_kernels_match_oracle(emu, name, make, gelu_cfg):
-    """The FFMA forward kernels (node encoder, edge kernel incl. the fused edge encoder, node kernel, decoder; the path
-    B200SPAI_GNN_CFG = 0 / 2 selects on the GPU) compiled for the host against the oracle's NodeEdgeProcessing: G within
-    1e-5 of max|G| (the bar of the GPU tests), final node features likewise."""
+@pytest.mark.parametrize("gelu_cfg", [0, 1, 2, 3], ids=["ffma_erff", "ffma_rational_erfc", "mma_erff", "mma_rational_erfc_default"])
+def test_forward_kernels_match_oracle(emu, name, make, gelu_cfg):
+    """The forward kernels compiled for the host against the oracle's NodeEdgeProcessing: G within 1e-5 of max|G| (the bar
+    of the GPU tests), final node features likewise.  FFMA variants (B200SPAI_GNN_CFG = 0 / 2): node encoder, edge kernel
+    incl. the fused edge encoder, node kernel, decoder.  Tensor-core variants (4 / 6 = the GPU default, csrc/gnn_mma.cuh):
+    the same source with `mma.sync.m16n8k8.tf32` done in software on the PTX fragment layout -- the 3xTF32 split, the
+    per-lane B-fragment tables, the C-fragment -> A-fragment chaining, the paired first Linear, the LayerNorm quad shuffles
+    and the packed GELU all run as written."""
     s, b = make()
     ws = systems.default_workspace(s, block_size=b)
     sd = {k: v.detach().clone() for k, v in ws.gnn.state_dict().items()}
